@@ -1,0 +1,191 @@
+/*
+ * sr_capi.h -- C-ABI of libsr_b200.so: the B200 (sm_100a) implementation of the dense stereo
+ * hot path of Bizilizi/stereo_reconstruction (src/WindowSearch + src/Reconstruction).
+ *
+ * This is the drop-in boundary.  The reference has no FFI: its "operator API" for this path
+ * is the C++ header surface
+ *     src/WindowSearch/BlockSearch.h:9-46      (class BlockSearch)
+ *     src/WindowSearch/LinearSearch.h:9-20     (class LinearSearch)
+ *     src/Reconstruction/reconstruction.h:13-34 (struct Vertex + free functions)
+ * The header-compatible C++ shims under stereo_reconstruction_b200/shim/ forward those classes
+ * and functions to the entry points below; each entry point cites the reference interface
+ * it replaces.  Plain pointers and sizes only.  All paths run on the GPU; there is no CPU
+ * fallback: every call fails with SR_E_CUDA when no device / kernel image is available.
+ *
+ * Threading: a sr_ctx owns one CUDA stream and its device/pinned buffers; it is not
+ * thread-safe, distinct contexts are independent.  Host pointers may be pageable or pinned
+ * (sr_host_alloc); pinned ones are DMA'd directly.
+ */
+#ifndef SR_CAPI_H
+#define SR_CAPI_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SR_OK 0
+#define SR_E_BADARG (-1)
+#define SR_E_SHAPE (-2)  /* the reference would throw cv::Exception / read out of bounds */
+#define SR_E_CUDA (-3)
+#define SR_E_NCCL (-4)
+#define SR_E_IO (-5)
+
+typedef struct sr_ctx sr_ctx;
+
+/* CV_8UC3 interleaved BGR image, row pitch in bytes (cv::Mat::data / ::step). */
+typedef struct {
+    const uint8_t* bgr;
+    int w, h;
+    size_t pitch;
+} sr_image;
+
+enum { SR_VARIANT_RIGHT = 0, SR_VARIANT_LEFT = 1, SR_VARIANT_LINEAR = 2 };
+enum { SR_COST_SSD_L2 = 0, SR_COST_SAD = 1, SR_COST_NCC = 2 };
+
+/* Parameters of one search.  For the reference-exact variants (cost == SR_COST_SSD_L2,
+ * subpixel == 0, lr_check == 0) the fields map 1:1 on the reference's arguments:
+ *   block, min_disp, max_disp  BlockSearch::BlockSearch(..., blockSize, minDisparity, maxDisparity)
+ *                              BlockSearch.cpp:6-13
+ *   smooth, var_block, thres   computeDisparityMapRight(smoothFactor, varBlock, thres) :88
+ *                              computeDisparityMapLeft(smoothFactor) :24
+ *                              LinearSearch::computeDisparityMap(smoothFactor) LinearSearch.cpp:10
+ * Extensions (no reference counterpart): cost = SAD / NCC, subpixel, lr_check. */
+typedef struct {
+    int variant;
+    int block;
+    int min_disp, max_disp;
+    double smooth;
+    int var_block;
+    double thres;
+    int cost;
+    int subpixel;
+    int lr_check;
+} sr_search_params;
+
+/* struct Vertex, reconstruction.h:13-22: Eigen Vector4f (16 B) + Vector4uc (4 B) + 12 B pad. */
+typedef struct {
+    float pos[4];
+    uint8_t rgba[4];
+    uint8_t pad_[12];
+} sr_vertex;
+
+/* ---- context ---------------------------------------------------------------------------- */
+int sr_ctx_create(int device, sr_ctx** out);
+void sr_ctx_destroy(sr_ctx* ctx);
+/* Message of the last failing call on ctx (or of sr_ctx_create when ctx == NULL). */
+const char* sr_last_error(const sr_ctx* ctx);
+const char* sr_version(void);
+/* Pinned host memory for callers that want direct DMA (e.g. a cv::MatAllocator). */
+int sr_host_alloc(void** p, size_t bytes);
+int sr_host_free(void* p);
+/* The context's CUDA stream (cudaStream_t) and a CUDA-event stopwatch on it. */
+void* sr_ctx_stream(sr_ctx* ctx);
+int sr_ctx_sync(sr_ctx* ctx);
+int sr_timer_start(sr_ctx* ctx);
+int sr_timer_stop(sr_ctx* ctx, float* ms);          /* records, synchronises, returns elapsed ms */
+/* Number of kernels this library launched on ctx since creation. */
+uint64_t sr_kernel_launches(const sr_ctx* ctx);
+/* Name of the search kernel family the last sr_search_* call dispatched to
+ * ("tile", "direct", "linear", ...), for tests and profiles. */
+const char* sr_last_kernel(const sr_ctx* ctx);
+
+/* ---- WindowSearch: one-shot host-pointer calls -------------------------------------------- */
+
+/* Replaces BlockSearch(left,right,block,minD,maxD).computeDisparityMapRight / Left
+ * (BlockSearch.cpp:88-179 / :24-86) and LinearSearch(left,right).computeDisparityMap
+ * (LinearSearch.cpp:10-59), selected by p->variant.
+ *   disp_out   CV_64F map, h2 x w2 (RIGHT, LINEAR) or h1 x w1 (LEFT), row pitch in bytes
+ *   max_block  (optional) the "max block size" the reference prints (BlockSearch.cpp:177)
+ * With p->subpixel the map holds d* + parabola offset; with p->lr_check inconsistent pixels
+ * are set to 0.  Errors: SR_E_SHAPE where the reference throws or reads out of bounds. */
+int sr_block_search(sr_ctx* ctx, const sr_image* left, const sr_image* right,
+                    const sr_search_params* p, double* disp_out, size_t out_pitch, int* max_block);
+
+/* n independent pairs of identical shape (config 5: batch sharded by pair); pairs are
+ * pipelined H2D / compute / D2H on internal streams.  disp_out[i] as in sr_block_search. */
+int sr_block_search_batch(sr_ctx* ctx, int n, const sr_image* left, const sr_image* right,
+                          const sr_search_params* p, double* const* disp_out, size_t out_pitch);
+
+/* ---- WindowSearch: device-resident form (what the one-shot call is made of) ------------- */
+typedef struct sr_pair sr_pair;
+int sr_pair_create(sr_ctx* ctx, int w1, int h1, int w2, int h2, sr_pair** out);
+void sr_pair_destroy(sr_ctx* ctx, sr_pair* pair);
+int sr_pair_upload(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_image* right);
+/* Kernels only, asynchronous on the context stream; result stays in HBM.
+ * rows [row0,row1) of the output are computed (pass 0,h for the full image; used for
+ * row-band sharding -- a band needs smooth == 1). */
+int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1);
+int sr_search_download(sr_ctx* ctx, sr_pair* pair, double* disp_out, size_t out_pitch, int row0, int row1);
+/* Device pointer (double*, tightly packed rows of the output width) of the last result. */
+void* sr_search_result_dev(sr_ctx* ctx, sr_pair* pair);
+int sr_search_max_block(sr_ctx* ctx, sr_pair* pair, int* max_block);
+/* Effective (reference-semantics) number of (pixel, candidate) evaluations of the last run
+ * restricted to its rows: sum over non-black pixels of the candidates before the break
+ * (BlockSearch.cpp:147-149). */
+int sr_search_effective_evals(sr_ctx* ctx, sr_pair* pair, uint64_t* evals);
+
+/* ---- Reconstruction ------------------------------------------------------------------------ */
+/* removeDisparityOutliers(disp, k, thrFront, thrBack), reconstruction.cpp:5-18.  In place,
+ * CV_32FC1 h x w, row pitch in bytes. */
+int sr_remove_outliers(sr_ctx* ctx, float* disp, int w, int h, size_t pitch, int ksize,
+                       float thr_front, float thr_back);
+/* cv::blur(disp, Size(k,k)) alone (reconstruction.cpp:8), tightly packed output. */
+int sr_box_blur(sr_ctx* ctx, const float* src, float* dst, int w, int h, int ksize);
+/* scaleDisparityMap(disp, f), reconstruction.cpp:21-27. */
+int sr_scale(sr_ctx* ctx, float* disp, int w, int h, size_t pitch, float f);
+/* convertDisparityToDepth(disp, focal, baseline), reconstruction.cpp:30-43. */
+int sr_disparity_to_depth(sr_ctx* ctx, const float* disp, float* depth, int w, int h,
+                          float focal, float baseline);
+/* Back-projection loop of reconstruction(), reconstruction.cpp:169-196.  fx,fy,cx,cy =
+ * K(0,0), K(1,1), K(0,2), K(1,2) of the (column-major) Eigen Matrix3f. */
+int sr_backproject(sr_ctx* ctx, const uint8_t* bgr, size_t pitch, const float* depth, int w, int h,
+                   float fx, float fy, float cx, float cy, sr_vertex* out);
+/* Face list of WriteMesh in the reference's order, reconstruction.cpp:92-113
+ * (CheckTriangularValidity :46-69).  tri holds up to 6*(w-1)*(h-1) indices. */
+int sr_mesh_faces(sr_ctx* ctx, const sr_vertex* v, int w, int h, float thr, uint32_t* tri, uint32_t* n_faces);
+/* Fused device pipeline of main.cpp:53-65 on a float disparity map: [outlier removal ->]
+ * depth -> back-projection -> face list, one upload, no intermediate host round trip.
+ * ksize <= 0 skips removeDisparityOutliers.  Any output pointer may be NULL. */
+int sr_reconstruct(sr_ctx* ctx, const uint8_t* bgr, size_t pitch, const float* disp, int w, int h,
+                   int ksize, float thr_front, float thr_back, float focal, float baseline,
+                   float fx, float fy, float cx, float cy, float thr_mesh,
+                   float* disp_filtered, float* depth, sr_vertex* vertices, uint32_t* tri, uint32_t* n_faces);
+/* Search result (already in HBM) -> [u8 quantisation of main.cpp:41-50] -> the pipeline above,
+ * with no host round trip of the disparity map.  quantize_u8 != 0 reproduces the 8-bit PNG
+ * hand-off (rint half-even, saturate). */
+int sr_pair_reconstruct(sr_ctx* ctx, sr_pair* pair, int quantize_u8,
+                        int ksize, float thr_front, float thr_back, float focal, float baseline,
+                        float fx, float fy, float cx, float cy, float thr_mesh,
+                        float* disp_filtered, float* depth, sr_vertex* vertices, uint32_t* tri, uint32_t* n_faces);
+/* WriteMesh(vertices, w, h, filename, thr), reconstruction.cpp:72-149: validity on the GPU,
+ * COFF text on the host.  Returns SR_E_IO where the reference returns false. */
+int sr_write_mesh(sr_ctx* ctx, const sr_vertex* v, int w, int h, const char* filename, float thr);
+
+/* ---- neighbours of the path ------------------------------------------------- */
+/* cv::warpPerspective(src, dst, M, size, INTER_NEAREST) on CV_64F, rectification.cpp:82-87. */
+int sr_warp_nearest_f64(sr_ctx* ctx, const double* src, int sw, int sh, double* dst, int dw, int dh,
+                        const double M[9]);
+/* evaldisp, utils.cpp:123-168.  Counts exact; serr is a double-precision sum. */
+typedef struct { int n, bad, invalid; double serr; float bad_pct, invalid_pct, total_bad_pct, avg_err; } sr_eval;
+int sr_evaldisp(sr_ctx* ctx, const float* disp, const float* gt, const uint8_t* mask, int w, int h,
+                float badthresh, float maxdisp, int rounddisp, sr_eval* out);
+/* Middlebury PFM / ASCII PLY writers (host). */
+int sr_write_pfm(const char* path, const float* data, int w, int h);
+int sr_write_ply(const char* path, const sr_vertex* v, int w, int h);
+
+/* ---- multi-GPU: row bands gathered to rank 0 over NCCL (config 4) -------------------------- */
+/* unique_id: 128 bytes from sr_comm_unique_id on rank 0, distributed by the caller. */
+int sr_comm_unique_id(void* id128);
+int sr_comm_init(sr_ctx* ctx, int rank, int nranks, const void* id128);
+int sr_comm_destroy(sr_ctx* ctx);
+/* Balanced band of output rows for `rank` of `nranks` (by effective evaluations). */
+int sr_band_rows(int h, int rank, int nranks, int* row0, int* row1);
+/* Every rank computes its band of the same pair; bands are gathered into rank 0's result
+ * buffer with grouped ncclSend/ncclRecv.  Asynchronous on the context stream. */
+int sr_search_run_banded(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,243 @@
+"""ctypes binding of libsr_b200.so (the C-ABI declared in include/sr_capi.h).
+
+There is no CPU fallback: loading fails loudly when the shared library is missing, and every
+call fails with SR_E_CUDA when no B200 is present.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsr_b200.so")
+
+OK, E_BADARG, E_SHAPE, E_CUDA, E_NCCL, E_IO = 0, -1, -2, -3, -4, -5
+VARIANT_RIGHT, VARIANT_LEFT, VARIANT_LINEAR = 0, 1, 2
+COST_SSD_L2, COST_SAD, COST_NCC = 0, 1, 2
+
+VERTEX_DTYPE = np.dtype({"names": ["pos", "rgba"], "formats": [(np.float32, 4), (np.uint8, 4)],
+                         "offsets": [0, 16], "itemsize": 32})
+
+
+class SrImage(C.Structure):
+    _fields_ = [("bgr", C.c_void_p), ("w", C.c_int), ("h", C.c_int), ("pitch", C.c_size_t)]
+
+
+class SrSearchParams(C.Structure):
+    _fields_ = [("variant", C.c_int), ("block", C.c_int), ("min_disp", C.c_int), ("max_disp", C.c_int),
+                ("smooth", C.c_double), ("var_block", C.c_int), ("thres", C.c_double), ("cost", C.c_int),
+                ("subpixel", C.c_int), ("lr_check", C.c_int)]
+
+
+class SrEval(C.Structure):
+    _fields_ = [("n", C.c_int), ("bad", C.c_int), ("invalid", C.c_int), ("serr", C.c_double),
+                ("bad_pct", C.c_float), ("invalid_pct", C.c_float), ("total_bad_pct", C.c_float),
+                ("avg_err", C.c_float)]
+
+
+class SrError(RuntimeError):
+    """Non-zero status from the C-ABI (the C++ shim throws std::runtime_error / cv::Exception)."""
+
+    def __init__(self, code, msg):
+        super().__init__(f"libsr_b200 error {code}: {msg}")
+        self.code = code
+
+
+# every symbol include/sr_capi.h declares (tests check that the library exports all of them)
+SYMBOLS = [
+    "sr_ctx_create", "sr_ctx_destroy", "sr_last_error", "sr_version", "sr_host_alloc", "sr_host_free",
+    "sr_ctx_stream", "sr_ctx_sync", "sr_timer_start", "sr_timer_stop", "sr_kernel_launches", "sr_last_kernel",
+    "sr_block_search", "sr_block_search_batch", "sr_pair_create", "sr_pair_destroy", "sr_pair_upload",
+    "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block",
+    "sr_search_effective_evals", "sr_remove_outliers", "sr_box_blur", "sr_scale", "sr_disparity_to_depth",
+    "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
+    "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_comm_unique_id", "sr_comm_init",
+    "sr_comm_destroy", "sr_band_rows", "sr_search_run_banded",
+]
+
+_lib = None
+
+
+def lib():
+    """Loads libsr_b200.so (built by __graft_entry__.build() / csrc/Makefile)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(there is no CPU fallback)")
+        l = C.CDLL(LIB_PATH)
+        l.sr_last_error.restype = C.c_char_p
+        l.sr_last_error.argtypes = [C.c_void_p]
+        l.sr_version.restype = C.c_char_p
+        l.sr_last_kernel.restype = C.c_char_p
+        l.sr_last_kernel.argtypes = [C.c_void_p]
+        l.sr_kernel_launches.restype = C.c_uint64
+        l.sr_kernel_launches.argtypes = [C.c_void_p]
+        l.sr_ctx_stream.restype = C.c_void_p
+        l.sr_ctx_stream.argtypes = [C.c_void_p]
+        l.sr_search_result_dev.restype = C.c_void_p
+        l.sr_search_result_dev.argtypes = [C.c_void_p, C.c_void_p]
+        l.sr_ctx_destroy.restype = None
+        l.sr_ctx_destroy.argtypes = [C.c_void_p]
+        l.sr_pair_destroy.restype = None
+        l.sr_pair_destroy.argtypes = [C.c_void_p, C.c_void_p]
+        _lib = l
+    return _lib
+
+
+def image(a):
+    """numpy HxWx3 uint8 (BGR, any row stride) -> (keep-alive array, SrImage)."""
+    a = np.asarray(a)
+    if a.dtype != np.uint8 or a.ndim != 3 or a.shape[2] != 3:
+        raise SrError(E_BADARG, "image must be HxWx3 uint8 (CV_8UC3)")
+    if a.strides[2] != 1 or a.strides[1] != 3:
+        a = np.ascontiguousarray(a)
+    return a, SrImage(a.ctypes.data, a.shape[1], a.shape[0], a.strides[0])
+
+
+class Context:
+    """Owns one sr_ctx (one CUDA stream + buffers on one GPU)."""
+
+    def __init__(self, device=0):
+        self._l = lib()
+        h = C.c_void_p()
+        rc = self._l.sr_ctx_create(int(device), C.byref(h))
+        if rc != OK:
+            raise SrError(rc, self._l.sr_last_error(None).decode())
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self._l.sr_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, rc):
+        if rc != OK:
+            raise SrError(rc, self._l.sr_last_error(self.h).decode())
+
+    @property
+    def launches(self):
+        return int(self._l.sr_kernel_launches(self.h))
+
+    @property
+    def last_kernel(self):
+        return self._l.sr_last_kernel(self.h).decode()
+
+    def sync(self):
+        self.check(self._l.sr_ctx_sync(self.h))
+
+    def timer_start(self):
+        self.check(self._l.sr_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self.check(self._l.sr_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+
+_default_ctx = {}
+
+
+def default_context(device=0):
+    if device not in _default_ctx:
+        _default_ctx[device] = Context(device)
+    return _default_ctx[device]
+
+
+def pinned_empty(shape, dtype):
+    """numpy array backed by pinned host memory (sr_host_alloc); freed with free_pinned."""
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = C.c_void_p()
+    rc = lib().sr_host_alloc(C.byref(p), C.c_size_t(max(n, 1)))
+    if rc != OK:
+        raise SrError(rc, "sr_host_alloc failed")
+    buf = (C.c_uint8 * max(n, 1)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    arr.flags.writeable = True
+    return arr, p
+
+
+def free_pinned(p):
+    lib().sr_host_free(p)
+
+
+class Pair:
+    """Device-resident stereo pair (sr_pair)."""
+
+    def __init__(self, ctx, w1, h1, w2, h2):
+        self.ctx = ctx
+        h = C.c_void_p()
+        ctx.check(ctx._l.sr_pair_create(ctx.h, w1, h1, w2, h2, C.byref(h)))
+        self.h = h
+        self.w1, self.h1, self.w2, self.h2 = w1, h1, w2, h2
+
+    def close(self):
+        if getattr(self, "h", None) and self.ctx.h:
+            self.ctx._l.sr_pair_destroy(self.ctx.h, self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, left, right):
+        la, li = image(left)
+        ra, ri = image(right)
+        self.ctx.check(self.ctx._l.sr_pair_upload(self.ctx.h, self.h, C.byref(li), C.byref(ri)))
+        self.ctx.sync()  # la/ra may be temporaries
+
+    def run(self, params, row0=0, row1=None):
+        if row1 is None:
+            row1 = self.h1 if params.variant == VARIANT_LEFT else self.h2
+        self.ctx.check(self.ctx._l.sr_search_run(self.ctx.h, self.h, C.byref(params), int(row0), int(row1)))
+
+    def run_banded(self, params):
+        self.ctx.check(self.ctx._l.sr_search_run_banded(self.ctx.h, self.h, C.byref(params)))
+
+    def download(self, params, out=None, row0=0, row1=None):
+        oh, ow = (self.h1, self.w1) if params.variant == VARIANT_LEFT else (self.h2, self.w2)
+        if row1 is None:
+            row1 = oh
+        if out is None:
+            out = np.zeros((oh, ow), np.float64)
+        self.ctx.check(self.ctx._l.sr_search_download(self.ctx.h, self.h, C.c_void_p(out.ctypes.data),
+                                                      C.c_size_t(out.strides[0]), int(row0), int(row1)))
+        return out
+
+    def max_block(self):
+        v = C.c_int()
+        self.ctx.check(self.ctx._l.sr_search_max_block(self.ctx.h, self.h, C.byref(v)))
+        return v.value
+
+    def effective_evals(self):
+        v = C.c_uint64()
+        self.ctx.check(self.ctx._l.sr_search_effective_evals(self.ctx.h, self.h, C.byref(v)))
+        return int(v.value)
+
+
+def search_params(variant=VARIANT_RIGHT, block=17, min_disp=0, max_disp=200, smooth=1.0, var_block=False,
+                  thres=19.0, cost=COST_SSD_L2, subpixel=False, lr_check=False):
+    return SrSearchParams(int(variant), int(block), int(min_disp), int(max_disp), float(smooth), int(bool(var_block)),
+                          float(thres), int(cost), int(bool(subpixel)), int(bool(lr_check)))
+
+
+def block_search(ctx, left, right, params, out=None, return_max_block=False):
+    """One-shot host call (sr_block_search): H2D, kernels, D2H."""
+    la, li = image(left)
+    ra, ri = image(right)
+    oh, ow = (li.h, li.w) if params.variant == VARIANT_LEFT else (ri.h, ri.w)
+    if out is None:
+        out = np.zeros((oh, ow), np.float64)
+    mb = C.c_int(0)
+    ctx.check(ctx._l.sr_block_search(ctx.h, C.byref(li), C.byref(ri), C.byref(params), C.c_void_p(out.ctypes.data),
+                                     C.c_size_t(out.strides[0]), C.byref(mb)))
+    return (out, mb.value) if return_max_block else out

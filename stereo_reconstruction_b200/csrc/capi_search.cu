@@ -1,0 +1,169 @@
+// capi_search.cu -- WindowSearch entry points of the C-ABI (dispatch, download, one-shot calls).
+#include <cstring>
+#include "sr_internal.cuh"
+
+static int rows_fit(int h1, int h2, int half) {
+    // BlockSearch.cpp:151-154: the left ROI [y-up, y+down) must lie inside the left image,
+    // otherwise the reference throws cv::Exception.
+    int height = h1 < h2 ? h1 : h2;
+    for (int y = (height - half - 2 > 0 ? height - half - 2 : 0); y < height; y++) {
+        int down = h2 - y - 1 < half ? h2 - y - 1 : half;
+        if (y + down > h1) return 0;
+    }
+    return 1;
+}
+
+static int validate(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p) {
+    if (!ctx || !pair || !p) return sr_fail(ctx, SR_E_BADARG, "NULL argument");
+    if (p->block < 1) return sr_fail(ctx, SR_E_BADARG, "block size %d < 1", p->block);
+    if (p->cost != SR_COST_SSD_L2 && p->cost != SR_COST_SAD && p->cost != SR_COST_NCC)
+        return sr_fail(ctx, SR_E_BADARG, "unknown cost %d", p->cost);
+    if (p->variant != SR_VARIANT_RIGHT && p->variant != SR_VARIANT_LEFT && p->variant != SR_VARIANT_LINEAR)
+        return sr_fail(ctx, SR_E_BADARG, "unknown variant %d", p->variant);
+    return SR_OK;
+}
+
+extern "C" {
+
+int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1) {
+    int rc = validate(ctx, pair, p);
+    if (rc != SR_OK) return rc;
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    pair->evals_valid = false;
+    if (p->variant == SR_VARIANT_LEFT) {
+        if (p->cost != SR_COST_SSD_L2 || p->subpixel || p->lr_check)
+            return sr_fail(ctx, SR_E_BADARG, "the Left variant is reference-exact only (SSD, no extensions)");
+        if ((p->block & 1) == 0) return sr_fail(ctx, SR_E_SHAPE, "Left variant with an even block overruns the ROI (cv::Exception in the reference)");
+        pair->ow = pair->w1; pair->oh = pair->h1;
+        pair->last_row0 = 0; pair->last_row1 = pair->h1;
+        ctx->last_kernel = "left";
+        return sr_launch_search_left(ctx, pair, p->block, p->max_disp, p->smooth);
+    }
+    if (p->variant == SR_VARIANT_LINEAR) {
+        if (pair->h1 < pair->h2 || pair->w1 < pair->w2)
+            return sr_fail(ctx, SR_E_SHAPE, "LinearSearch reads leftImage(i,j) for every right pixel: needs h1>=h2, w1>=w2");
+        pair->ow = pair->w2; pair->oh = pair->h2;
+        pair->last_row0 = 0; pair->last_row1 = pair->h2;
+        ctx->last_kernel = "linear";
+        return sr_launch_search_linear(ctx, pair, p->smooth);
+    }
+    // ---- Right variant (BlockSearch.cpp:88-179) and its extension costs ----
+    if (p->min_disp < 0) return sr_fail(ctx, SR_E_SHAPE, "min_disp < 0 makes the left ROI start at a negative column");
+    if (p->cost == SR_COST_NCC || p->subpixel || p->lr_check) return sr_search_run_ext(ctx, pair, p, row0, row1);
+    SearchGeom g;
+    g.w1 = pair->w1; g.h1 = pair->h1; g.w2 = pair->w2; g.h2 = pair->h2;
+    g.height = g.h1 < g.h2 ? g.h1 : g.h2;
+    g.block = p->block; g.half = (p->block - 1) / 2;
+    g.dlo = p->min_disp; g.dhi = p->max_disp;
+    if (g.dhi > g.w1) g.dhi = g.w1;  // no candidate beyond: x + d + r < w1
+    if (g.dhi < g.dlo) g.dhi = g.dlo;
+    g.row0 = row0 < 0 ? 0 : row0; g.row1 = row1 > g.h2 ? g.h2 : row1;
+    if (g.row1 < g.row0) g.row1 = g.row0;
+    if (!p->var_block && !rows_fit(g.h1, g.h2, g.half))
+        return sr_fail(ctx, SR_E_SHAPE, "left image too short for the window rows (h1=%d, h2=%d): cv::Exception in the reference", g.h1, g.h2);
+    bool smoothing = p->smooth != 1.0 && g.dlo == 0;
+    if (smoothing && (g.row0 != 0))
+        return sr_fail(ctx, SR_E_BADARG, "row bands need smooth == 1 (the smoothing rule is a raster dependency)");
+    pair->ow = g.w2; pair->oh = g.h2;
+    pair->last_row0 = g.row0; pair->last_row1 = g.row1;
+    int init[2] = {p->block, SR_OK};
+    SR_CUDA(ctx, cudaMemcpyAsync(pair->maxblock, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+    bool degenerate = g.half == 0 || g.w2 == 1 || g.h2 == 1;  // empty windows: every cost is NaN
+    int handled = 0;
+    if (!p->var_block && !degenerate) {
+        SearchGeom gt = g;
+        if (smoothing) gt.dlo = 1 > g.dlo ? 1 : g.dlo;
+        if (gt.dhi < gt.dlo) gt.dhi = gt.dlo;
+        handled = sr_launch_search_tile(ctx, pair, gt, p->cost, 0);
+        if (handled < 0) return handled;
+        if (handled) {
+            ctx->last_kernel = "tile";
+            if (smoothing && (rc = sr_launch_cost0(ctx, pair, g, p->cost)) != SR_OK) return rc;
+            rc = sr_launch_resolve_right(ctx, pair, g, p->smooth, 0, smoothing ? 1 : 0);
+        }
+    }
+    if (!handled) {
+        ctx->last_kernel = "direct";
+        if ((rc = sr_launch_search_direct(ctx, pair, g, p->cost, p->var_block, p->thres, 1)) != SR_OK) return rc;
+        rc = sr_launch_resolve_right(ctx, pair, g, p->smooth, 1, 1);
+    }
+    if (rc != SR_OK) return rc;
+    return sr_launch_count_evals(ctx, pair, g) == SR_OK ? (pair->evals_valid = true, SR_OK) : SR_E_CUDA;
+}
+
+void* sr_search_result_dev(sr_ctx* ctx, sr_pair* pair) { return pair ? (void*)pair->out : nullptr; }
+
+int sr_search_download(sr_ctx* ctx, sr_pair* pair, double* disp_out, size_t out_pitch, int row0, int row1) {
+    if (!ctx || !pair || !disp_out) return sr_fail(ctx, SR_E_BADARG, "sr_search_download: NULL argument");
+    if (row0 < 0) row0 = 0;
+    if (row1 > pair->oh) row1 = pair->oh;
+    if (row1 <= row0) return SR_OK;
+    size_t rowb = (size_t)pair->ow * sizeof(double);
+    if (out_pitch < rowb) return sr_fail(ctx, SR_E_BADARG, "output pitch %zu smaller than a row (%zu)", out_pitch, rowb);
+    int rows = row1 - row0;
+    const double* src = pair->out + (size_t)row0 * pair->ow;
+    double* dst = (double*)((char*)disp_out + (size_t)row0 * out_pitch);
+    cudaPointerAttributes attr;
+    bool pinned = cudaPointerGetAttributes(&attr, disp_out) == cudaSuccess &&
+                  (attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged);
+    cudaGetLastError();
+    if (pinned) {
+        SR_CUDA(ctx, cudaMemcpy2DAsync(dst, out_pitch, src, rowb, rowb, rows, cudaMemcpyDeviceToHost, ctx->stream));
+        SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    } else {
+        double* st = (double*)sr_pinned(ctx, 2, rowb * rows);
+        if (!st) return SR_E_CUDA;
+        SR_CUDA(ctx, cudaMemcpyAsync(st, src, rowb * rows, cudaMemcpyDeviceToHost, ctx->stream));
+        SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (out_pitch == rowb) memcpy(dst, st, rowb * rows);
+        else for (int y = 0; y < rows; y++) memcpy((char*)dst + (size_t)y * out_pitch, (char*)st + (size_t)y * rowb, rowb);
+    }
+    int status[2];
+    SR_CUDA(ctx, cudaMemcpy(status, pair->maxblock, sizeof status, cudaMemcpyDeviceToHost));
+    if (status[1] != SR_OK) return sr_fail(ctx, status[1], "the grown window runs past the left image (cv::Exception in the reference)");
+    return SR_OK;
+}
+
+int sr_search_max_block(sr_ctx* ctx, sr_pair* pair, int* max_block) {
+    if (!ctx || !pair || !max_block) return SR_E_BADARG;
+    SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    SR_CUDA(ctx, cudaMemcpy(max_block, pair->maxblock, sizeof(int), cudaMemcpyDeviceToHost));
+    return SR_OK;
+}
+
+int sr_search_effective_evals(sr_ctx* ctx, sr_pair* pair, uint64_t* evals) {
+    if (!ctx || !pair || !evals) return SR_E_BADARG;
+    if (!pair->evals_valid) return sr_fail(ctx, SR_E_BADARG, "no evaluation count for the last run");
+    SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    unsigned long long v = 0;
+    SR_CUDA(ctx, cudaMemcpy(&v, pair->evals, 8, cudaMemcpyDeviceToHost));
+    *evals = v;
+    return SR_OK;
+}
+
+int sr_block_search(sr_ctx* ctx, const sr_image* left, const sr_image* right, const sr_search_params* p,
+                    double* disp_out, size_t out_pitch, int* max_block) {
+    if (!ctx || !left || !right || !p || !disp_out) return sr_fail(ctx, SR_E_BADARG, "sr_block_search: NULL argument");
+    if (!left->bgr || !right->bgr || left->w <= 0 || left->h <= 0 || right->w <= 0 || right->h <= 0)
+        return sr_fail(ctx, SR_E_BADARG, "sr_block_search: empty image");
+    // one cached pair object per context, re-created when the shape changes
+    sr_pair* pair = ctx->batch_pairs.empty() ? nullptr : ctx->batch_pairs[0];
+    if (pair && (pair->w1 != left->w || pair->h1 != left->h || pair->w2 != right->w || pair->h2 != right->h)) {
+        for (sr_pair* q : ctx->batch_pairs) sr_pair_destroy(ctx, q);
+        ctx->batch_pairs.clear();
+        pair = nullptr;
+    }
+    int rc;
+    if (!pair) {
+        if ((rc = sr_pair_create(ctx, left->w, left->h, right->w, right->h, &pair)) != SR_OK) return rc;
+        ctx->batch_pairs.push_back(pair);
+    }
+    if ((rc = sr_pair_upload(ctx, pair, left, right)) != SR_OK) return rc;
+    int oh = p->variant == SR_VARIANT_LEFT ? left->h : right->h;
+    if ((rc = sr_search_run(ctx, pair, p, 0, oh)) != SR_OK) return rc;
+    if ((rc = sr_search_download(ctx, pair, disp_out, out_pitch, 0, oh)) != SR_OK) return rc;
+    if (max_block) return sr_search_max_block(ctx, pair, max_block);
+    return SR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,210 @@
+// resolve.cu -- turns the per-pixel search records into the reference's CV_64F disparity map,
+// including the smoothFactor rule of BlockSearch.cpp:160-165.
+//
+// In the Right variant the rule compares the neighbour's stored disparity with
+// (double)(pointX - correspondX) = -d, so it only ever fires for d == 0 next to a stored 0
+// ("hard parts").  Per pixel that leaves three booleans a_k = "d = 0 wins when its
+// cost was multiplied k times by smoothFactor" (k = 0,1,2), evaluated in fp64 exactly as the
+// reference does (sqrt(ssd)/N, then *s, *s), and one alternative value (the first minimum over
+// d >= 1, or -x when nothing is a candidate).  The raster dependency is then a carry chain
+//     Z(y,x) = Z(y,x-1) ? F1(y,x) : F0(y,x),   F0 = Zup ? a1 : a0,  F1 = Zup ? a2 : a1
+// resolved row by row with bit-parallel carry propagation (one 32-pixel word per thread).
+#include "sr_internal.cuh"
+
+struct PixRec {
+    bool skip;                  // black pixel / unvisited row -> 0.0
+    unsigned long long c0, cr;  // SR_NONE64 when absent
+    int dr;
+    int n;                      // window pixel count N
+};
+
+__device__ __forceinline__ PixRec load_rec(int from_direct, int have_c0, size_t i, int x, int y,
+                                           const unsigned long long* best, const unsigned long long* c0,
+                                           const unsigned long long* cr, const int* dr, const int* nwin,
+                                           const uint32_t* Rp, int pitchR, const SearchGeom& g) {
+    PixRec r;
+    if (from_direct) {
+        r.n = nwin[i];
+        r.skip = r.n < 0;
+        r.c0 = c0[i]; r.cr = cr[i]; r.dr = dr[i];
+    } else {
+        r.skip = y >= g.height || (__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) == 0;
+        int l = min(x, g.half), rr = min(g.w2 - x - 1, g.half), u = min(y, g.half), dn = min(g.h2 - y - 1, g.half);
+        r.n = (l + rr) * (u + dn);
+        unsigned long long b = best[i];
+        r.cr = b == SR_NONE64 ? SR_NONE64 : (b >> 32);
+        r.dr = (int)(b & 0xFFFFFFFFull);
+        r.c0 = have_c0 ? c0[i] : SR_NONE64;
+    }
+    return r;
+}
+
+// smooth == 1 (or no d == 0 candidate in range): pointwise.
+__global__ void resolve_plain_kernel(SearchGeom g, int from_direct, int have_c0, const unsigned long long* __restrict__ best,
+                                     const unsigned long long* __restrict__ c0, const unsigned long long* __restrict__ cr,
+                                     const int* __restrict__ dr, const int* __restrict__ nwin,
+                                     const uint32_t* __restrict__ Rp, int pitchR, double* __restrict__ out) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = g.row0 + blockIdx.y;
+    if (x >= g.w2 || y >= g.row1) return;
+    size_t i = (size_t)y * g.w2 + x;
+    PixRec r = load_rec(from_direct, have_c0, i, x, y, best, c0, cr, dr, nwin, Rp, pitchR, g);
+    double v;
+    if (r.skip) v = 0.0;
+    else if (r.n == 0) v = (double)(0 - x);  // 0/0 = NaN never beats DBL_MAX (:168)
+    else if (r.c0 != SR_NONE64 && (r.cr == SR_NONE64 || r.c0 <= r.cr)) v = 0.0;  // d=0 first, strict <
+    else if (r.cr != SR_NONE64) v = (double)r.dr;
+    else v = (double)(0 - x);  // no candidate survived the break (:111,:174)
+    out[i] = v;
+}
+
+// Phase A of the smoothing pass: bit planes a0,a1,a2 (ballot words) and the alternative value.
+__global__ void smooth_prepare_kernel(SearchGeom g, int from_direct, double s, const unsigned long long* __restrict__ best,
+                                      const unsigned long long* __restrict__ c0, const unsigned long long* __restrict__ cr,
+                                      const int* __restrict__ dr, const int* __restrict__ nwin,
+                                      const uint32_t* __restrict__ Rp, int pitchR, uint32_t* __restrict__ bits,
+                                      int words, double* __restrict__ alt) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim.x multiple of 32, grid covers words*32
+    int y = g.row0 + blockIdx.y;
+    bool a0 = false, a1 = false, a2 = false;
+    if (x < g.w2) {
+        size_t i = (size_t)y * g.w2 + x;
+        PixRec r = load_rec(from_direct, 1, i, x, y, best, c0, cr, dr, nwin, Rp, pitchR, g);
+        double v;  // value when d = 0 does not win
+        if (r.skip) { v = 0.0; }
+        else if (r.n == 0 || r.cr == SR_NONE64) v = (r.n != 0 && r.c0 != SR_NONE64) ? 0.0 : (double)(0 - x);
+        else v = (double)r.dr;
+        if (!r.skip && r.n != 0 && r.c0 != SR_NONE64 && r.cr != SR_NONE64) {
+            double n = (double)r.n;
+            double d0 = __ddiv_rn(sqrt((double)r.c0), n);
+            double dd = __ddiv_rn(sqrt((double)r.cr), n);
+            double d1 = __dmul_rn(d0, s), d2 = __dmul_rn(d1, s);
+            // reference order: d=0 sets best unless NaN; the rest replaces it only if dd < best
+            a0 = !(dd < d0); a1 = !(dd < d1); a2 = !(dd < d2);
+            // a NaN d0*s^k (s = NaN/inf corner) never becomes best: then the rest wins
+            if (d0 != d0) a0 = false;
+            if (d1 != d1) a1 = false;
+            if (d2 != d2) a2 = false;
+        }
+        if (v == 0.0) a0 = a1 = a2 = true;  // the stored value is 0 either way
+        alt[i] = v;
+    }
+    uint32_t w0 = __ballot_sync(0xffffffffu, a0), w1 = __ballot_sync(0xffffffffu, a1), w2 = __ballot_sync(0xffffffffu, a2);
+    if ((threadIdx.x & 31) == 0) {
+        int wi = x >> 5;
+        if (wi < words) {
+            size_t o = ((size_t)(y - g.row0) * words + wi) * 3;
+            bits[o] = w0; bits[o + 1] = w1; bits[o + 2] = w2;
+        }
+    }
+}
+
+// carry chain inside one 32-bit word: z_x = cin_x ? F1_x : F0_x with cin_x = z_{x-1}.
+__device__ __forceinline__ uint32_t chain_word(uint32_t F0, uint32_t F1, uint32_t cin, bool monotone) {
+    if (monotone) {
+        // F0 <= F1 bitwise: generate = F0, propagate = F1 & ~F0 -> binary adder carries
+        unsigned long long sum = (unsigned long long)F0 + (unsigned long long)F1 + cin;
+        uint32_t carry_in = (uint32_t)sum ^ F0 ^ F1;  // carry into each bit
+        return (F0 & F1) | ((F0 ^ F1) & carry_in);    // carry out of each bit
+    }
+    uint32_t z = 0, c = cin;
+    for (int b = 0; b < 32; b++) {
+        c = c ? (F1 >> b) & 1u : (F0 >> b) & 1u;
+        z |= c << b;
+    }
+    return z;
+}
+
+// Phase B: one CTA walks the rows; thread t owns word t (+ k*blockDim) of every row.
+// Requires row0 == 0 semantics: the row above the first computed row is taken from zprev
+// (all-ones = "stored 0" never applies at y == 0 since the rule needs y >= 1).
+#define SMOOTH_THREADS 1024
+__global__ void __launch_bounds__(SMOOTH_THREADS) smooth_raster_kernel(int rows, int words, int first_row_has_up,
+                                                                       const uint32_t* __restrict__ bits,
+                                                                       uint32_t* __restrict__ zbits, int monotone) {
+    __shared__ uint32_t sg[SMOOTH_THREADS / 32], sp[SMOOTH_THREADS / 32], scin[SMOOTH_THREADS / 32];
+    __shared__ uint32_t chunk_carry;
+    int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    int nchunks = (words + SMOOTH_THREADS - 1) / SMOOTH_THREADS;
+    for (int y = 0; y < rows; y++) {
+        if (t == 0) chunk_carry = 0;  // x == 0 has no left neighbour: treated as "not zero"
+        __syncthreads();
+        for (int ch = 0; ch < nchunks; ch++) {
+            int wi = ch * SMOOTH_THREADS + t;
+            uint32_t F0 = 0, F1 = 0;
+            if (wi < words) {
+                const uint32_t* b = bits + ((size_t)y * words + wi) * 3;
+                uint32_t a0 = b[0], a1 = b[1], a2 = b[2];
+                uint32_t up = (y > 0 || first_row_has_up) ? (y > 0 ? zbits[(size_t)(y - 1) * words + wi] : 0u) : 0u;
+                F0 = (up & a1) | (~up & a0);
+                F1 = (up & a2) | (~up & a1);
+            }
+            // word summary: carry out (bit 31 of z) for cin = 0 / 1
+            uint32_t g0 = chain_word(F0, F1, 0, monotone) >> 31, g1 = chain_word(F0, F1, 1, monotone) >> 31;
+            uint32_t G = __ballot_sync(0xffffffffu, g0), P = __ballot_sync(0xffffffffu, g1);  // per-warp 32-word functions
+            // warp summary over its 32 words (functions compose like words of F0/F1 bits)
+            if (lane == 0) {
+                sg[warp] = chain_word(G, P, 0, monotone) >> 31;
+                sp[warp] = chain_word(G, P, 1, monotone) >> 31;
+            }
+            __syncthreads();
+            if (warp == 0) {
+                uint32_t G2 = __ballot_sync(0xffffffffu, sg[lane]), P2 = __ballot_sync(0xffffffffu, sp[lane]);
+                uint32_t zz = chain_word(G2, P2, chunk_carry, monotone);  // carry out of each warp
+                uint32_t cin_w = (zz << 1) | chunk_carry;                  // carry into each warp
+                scin[lane] = (cin_w >> lane) & 1u;
+                __syncwarp();
+                if (lane == 0) chunk_carry = zz >> 31;
+            }
+            __syncthreads();
+            uint32_t zwarp = chain_word(G, P, scin[warp], monotone);  // carry out of each word of this warp
+            uint32_t cin_words = (zwarp << 1) | scin[warp];
+            uint32_t cin = (cin_words >> lane) & 1u;
+            if (wi < words) zbits[(size_t)y * words + wi] = chain_word(F0, F1, cin, monotone);
+            __syncthreads();
+        }
+        __threadfence_block();
+    }
+}
+
+__global__ void smooth_expand_kernel(SearchGeom g, int words, const uint32_t* __restrict__ zbits,
+                                     const double* __restrict__ alt, double* __restrict__ out) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = g.row0 + blockIdx.y;
+    if (x >= g.w2 || y >= g.row1) return;
+    size_t i = (size_t)y * g.w2 + x;
+    uint32_t z = (zbits[(size_t)(y - g.row0) * words + (x >> 5)] >> (x & 31)) & 1u;
+    out[i] = z ? 0.0 : alt[i];
+}
+
+int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, double smooth, int from_direct, int have_c0) {
+    int rows = g.row1 - g.row0;
+    if (rows <= 0) return SR_OK;
+    dim3 grid(cdiv(g.w2, 128), rows);
+    bool plain = smooth == 1.0 || !have_c0;
+    if (plain) {
+        resolve_plain_kernel<<<grid, 128, 0, ctx->stream>>>(g, from_direct, have_c0, pair->best, pair->c0, pair->cr, pair->dr,
+                                                            pair->nwin, pair->R.px, pair->R.pitch, pair->out);
+        SR_LAUNCHED(ctx);
+        return SR_OK;
+    }
+    int words = cdiv(g.w2, 32);
+    if (!pair->bits) {
+        size_t maxwords = (size_t)cdiv(pair->w1 > pair->w2 ? pair->w1 : pair->w2, 32) * (pair->h1 > pair->h2 ? pair->h1 : pair->h2);
+        SR_CUDA(ctx, cudaMalloc((void**)&pair->bits, maxwords * 4 * sizeof(uint32_t)));
+        SR_CUDA(ctx, cudaMalloc((void**)&pair->alt, pair->npx_cap * sizeof(double)));
+    }
+    uint32_t* zb = pair->bits + (size_t)rows * words * 3;
+    dim3 gridw(words, rows);
+    smooth_prepare_kernel<<<dim3(cdiv(words * 32, 128), rows), 128, 0, ctx->stream>>>(
+        g, from_direct, smooth, pair->best, pair->c0, pair->cr, pair->dr, pair->nwin, pair->R.px, pair->R.pitch, pair->bits,
+        words, pair->alt);
+    SR_LAUNCHED(ctx);
+    // s <= 1 makes a0 <= a1 <= a2 (more multiplications -> smaller cost): adder-style carries
+    int monotone = (smooth >= 0.0 && smooth <= 1.0) ? 1 : 0;
+    smooth_raster_kernel<<<1, SMOOTH_THREADS, 0, ctx->stream>>>(rows, words, 0, pair->bits, zb, monotone);
+    SR_LAUNCHED(ctx);
+    smooth_expand_kernel<<<grid, 128, 0, ctx->stream>>>(g, words, zb, pair->alt, pair->out);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}

@@ -1,0 +1,236 @@
+// sr_core.cu -- context, error handling, buffers, image packing, pair objects.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include "sr_internal.cuh"
+
+static thread_local std::string g_create_err;
+
+int sr_fail(sr_ctx* ctx, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf; else g_create_err = buf;
+    return code;
+}
+
+int sr_cuda_check(sr_ctx* ctx, cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return SR_OK;
+    return sr_fail(ctx, SR_E_CUDA, "CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+}
+
+void* sr_scratch(sr_ctx* ctx, int slot, size_t bytes) {
+    DevBuf& b = ctx->scratch[slot];
+    if (b.cap >= bytes && b.p) return b.p;
+    if (b.p) { cudaStreamSynchronize(ctx->stream); cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+    size_t cap = bytes + (bytes >> 3) + 256;
+    cudaError_t e = cudaMalloc(&b.p, cap);
+    if (e != cudaSuccess) { sr_cuda_check(ctx, e, "cudaMalloc(scratch)"); b.p = nullptr; return nullptr; }
+    b.cap = cap;
+    return b.p;
+}
+
+void* sr_pinned(sr_ctx* ctx, int slot, size_t bytes) {
+    if (ctx->pinned_cap[slot] >= bytes && ctx->pinned[slot]) return ctx->pinned[slot];
+    if (ctx->pinned[slot]) { cudaStreamSynchronize(ctx->stream); cudaFreeHost(ctx->pinned[slot]); ctx->pinned[slot] = nullptr; }
+    size_t cap = bytes + (bytes >> 3) + 4096;
+    cudaError_t e = cudaMallocHost(&ctx->pinned[slot], cap);
+    if (e != cudaSuccess) { sr_cuda_check(ctx, e, "cudaMallocHost"); ctx->pinned[slot] = nullptr; ctx->pinned_cap[slot] = 0; return nullptr; }
+    ctx->pinned_cap[slot] = cap;
+    return ctx->pinned[slot];
+}
+
+extern "C" {
+
+const char* sr_version(void) { return "stereo_reconstruction_b200 0.1 (sm_100a)"; }
+
+int sr_ctx_create(int device, sr_ctx** out) {
+    if (!out) return sr_fail(nullptr, SR_E_BADARG, "sr_ctx_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return sr_fail(nullptr, SR_E_CUDA, "sr_ctx_create: no CUDA device (%s); this library has no CPU fallback",
+                       e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    if (device < 0 || device >= n) return sr_fail(nullptr, SR_E_BADARG, "sr_ctx_create: device %d out of range (%d devices)", device, n);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return sr_cuda_check(nullptr, e, "cudaGetDeviceProperties");
+    if (prop.major != 10)
+        return sr_fail(nullptr, SR_E_CUDA, "sr_ctx_create: device %d is sm_%d%d; this library carries sm_100a code only", device, prop.major, prop.minor);
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return sr_cuda_check(nullptr, e, "cudaSetDevice");
+    sr_ctx* c = new sr_ctx();
+    c->device = device;
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&c->aux[0], cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&c->aux[1], cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess) {
+        int rc = sr_cuda_check(nullptr, e, "stream/event creation");
+        delete c;
+        return rc;
+    }
+    *out = c;
+    return SR_OK;
+}
+
+void sr_ctx_destroy(sr_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (sr_pair* p : ctx->batch_pairs) sr_pair_destroy(ctx, p);
+    ctx->batch_pairs.clear();
+    sr_comm_destroy(ctx);
+    for (auto& b : ctx->scratch) if (b.p) cudaFree(b.p);
+    for (auto& p : ctx->pinned) if (p) cudaFreeHost(p);
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->aux[0]);
+    cudaStreamDestroy(ctx->aux[1]);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* sr_last_error(const sr_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int sr_host_alloc(void** p, size_t bytes) {
+    if (!p) return SR_E_BADARG;
+    return cudaMallocHost(p, bytes ? bytes : 1) == cudaSuccess ? SR_OK : SR_E_CUDA;
+}
+int sr_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? SR_OK : SR_E_CUDA; }
+
+void* sr_ctx_stream(sr_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+int sr_ctx_sync(sr_ctx* ctx) {
+    if (!ctx) return SR_E_BADARG;
+    SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SR_OK;
+}
+int sr_timer_start(sr_ctx* ctx) {
+    if (!ctx) return SR_E_BADARG;
+    SR_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    return SR_OK;
+}
+int sr_timer_stop(sr_ctx* ctx, float* ms) {
+    if (!ctx || !ms) return SR_E_BADARG;
+    SR_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    SR_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+    SR_CUDA(ctx, cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    return SR_OK;
+}
+uint64_t sr_kernel_launches(const sr_ctx* ctx) { return ctx ? ctx->launches : 0; }
+const char* sr_last_kernel(const sr_ctx* ctx) { return ctx ? ctx->last_kernel : ""; }
+
+}  // extern "C"
+
+// ---- packing: BGR u8 (pitch) -> one uint32 per pixel, padded rows ---------------------------
+__global__ void pack_bgr_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, int w, int h,
+                                uint32_t* __restrict__ dst, int pitch_px, int padl) {
+    // one thread per destination pixel of the padded row (padding written as 0)
+    int xp = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = blockIdx.y;
+    if (xp >= pitch_px) return;
+    int x = xp - padl;
+    uint32_t v = 0;
+    if (x >= 0 && x < w) {
+        const uint8_t* p = raw + (size_t)y * raw_pitch + 3 * (size_t)x;
+        v = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
+    }
+    dst[(size_t)y * pitch_px + xp] = v;
+}
+
+int sr_launch_pack(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int h, PackedImage* img) {
+    dim3 grid(cdiv(img->pitch, 256), h);
+    pack_bgr_kernel<<<grid, 256, 0, ctx->stream>>>(raw, raw_pitch, w, h, img->base, img->pitch, SR_PADL);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
+static int alloc_packed(sr_ctx* ctx, PackedImage* img, int w, int h, int padr) {
+    img->w = w; img->h = h;
+    img->pitch = ((SR_PADL + w + padr + 31) / 32) * 32;
+    SR_CUDA(ctx, cudaMalloc((void**)&img->base, (size_t)img->pitch * h * sizeof(uint32_t)));
+    img->px = img->base + SR_PADL;
+    return SR_OK;
+}
+
+extern "C" {
+
+// Right padding of the packed left image: enough for max_disp up to SR_MAX_DISP_PAD plus a tile.
+#define SR_TILE_OVERSHOOT 640
+
+int sr_pair_create(sr_ctx* ctx, int w1, int h1, int w2, int h2, sr_pair** out) {
+    if (!ctx || !out) return SR_E_BADARG;
+    *out = nullptr;
+    if (w1 <= 0 || h1 <= 0 || w2 <= 0 || h2 <= 0) return sr_fail(ctx, SR_E_BADARG, "sr_pair_create: empty image");
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    sr_pair* p = new sr_pair();
+    p->w1 = w1; p->h1 = h1; p->w2 = w2; p->h2 = h2;
+    int rc;
+    // the left image is read at x + d: pad by the widest candidate range we can meet (the
+    // range is clipped to the image width by the break rule) plus one tile of overshoot
+    p->pad_disp = w1 + w2;
+    if ((rc = alloc_packed(ctx, &p->L, w1, h1, w2 + SR_TILE_OVERSHOOT + 64)) != SR_OK ||
+        (rc = alloc_packed(ctx, &p->R, w2, h2, w1 + SR_TILE_OVERSHOOT + 64)) != SR_OK) {
+        sr_pair_destroy(ctx, p);
+        return rc;
+    }
+    size_t npx = (size_t)(w1 > w2 ? w1 : w2) * (size_t)(h1 > h2 ? h1 : h2);
+    p->npx_cap = npx;
+    cudaError_t e;
+    if ((e = cudaMalloc((void**)&p->rawL, (size_t)w1 * h1 * 3)) != cudaSuccess ||
+        (e = cudaMalloc((void**)&p->rawR, (size_t)w2 * h2 * 3)) != cudaSuccess ||
+        (e = cudaMalloc((void**)&p->best, npx * 8)) != cudaSuccess ||
+        (e = cudaMalloc((void**)&p->c0, npx * 8)) != cudaSuccess ||
+        (e = cudaMalloc((void**)&p->out, npx * 8)) != cudaSuccess ||
+        (e = cudaMalloc((void**)&p->maxblock, 16)) != cudaSuccess) {
+        int r = sr_cuda_check(ctx, e, "cudaMalloc(pair)");
+        sr_pair_destroy(ctx, p);
+        return r;
+    }
+    p->evals = (unsigned long long*)(p->maxblock + 2);
+    *out = p;
+    return SR_OK;
+}
+
+void sr_pair_destroy(sr_ctx* ctx, sr_pair* p) {
+    if (!p) return;
+    if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
+    cudaFree(p->L.base); cudaFree(p->R.base); cudaFree(p->rawL); cudaFree(p->rawR);
+    cudaFree(p->best); cudaFree(p->c0); cudaFree(p->cr); cudaFree(p->dr); cudaFree(p->nwin);
+    cudaFree(p->bits); cudaFree(p->alt); cudaFree(p->out); cudaFree(p->outf); cudaFree(p->maxblock);
+    delete p;
+}
+
+static int upload_one(sr_ctx* ctx, const sr_image* im, uint8_t* raw, PackedImage* pk, int slot) {
+    size_t row = (size_t)im->w * 3;
+    if (im->pitch < row) return sr_fail(ctx, SR_E_BADARG, "image pitch %zu smaller than a row (%zu)", im->pitch, row);
+    cudaPointerAttributes attr;
+    bool pinned = cudaPointerGetAttributes(&attr, im->bgr) == cudaSuccess &&
+                  (attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged);
+    cudaGetLastError();
+    if (pinned) {
+        SR_CUDA(ctx, cudaMemcpy2DAsync(raw, row, im->bgr, im->pitch, row, im->h, cudaMemcpyHostToDevice, ctx->stream));
+    } else {
+        // pageable source: stage through the context's pinned buffer (one memcpy, one DMA)
+        uint8_t* st = (uint8_t*)sr_pinned(ctx, slot, row * im->h);
+        if (!st) return SR_E_CUDA;
+        if (im->pitch == row) memcpy(st, im->bgr, row * im->h);
+        else for (int y = 0; y < im->h; y++) memcpy(st + (size_t)y * row, im->bgr + (size_t)y * im->pitch, row);
+        SR_CUDA(ctx, cudaMemcpyAsync(raw, st, row * im->h, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    return sr_launch_pack(ctx, raw, row, im->w, im->h, pk);
+}
+
+int sr_pair_upload(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_image* right) {
+    if (!ctx || !pair || !left || !right || !left->bgr || !right->bgr) return sr_fail(ctx, SR_E_BADARG, "sr_pair_upload: NULL argument");
+    if (left->w != pair->w1 || left->h != pair->h1 || right->w != pair->w2 || right->h != pair->h2)
+        return sr_fail(ctx, SR_E_BADARG, "sr_pair_upload: image sizes differ from the pair's");
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    // the staging buffers are reused: make sure the previous upload's DMA has drained
+    SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    int rc = upload_one(ctx, left, pair->rawL, &pair->L, 0);
+    if (rc != SR_OK) return rc;
+    return upload_one(ctx, right, pair->rawR, &pair->R, 1);
+}
+
+}  // extern "C"

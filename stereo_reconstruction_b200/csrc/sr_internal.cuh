@@ -1,0 +1,110 @@
+// sr_internal.cuh -- shared declarations of libsr_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/sr_capi.h"
+
+#define SR_NONE64 0xFFFFFFFFFFFFFFFFull
+
+// Left padding (pixels) of the packed images: tiles start at column -16 (see search_tile.cu).
+#define SR_PADL 32
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct sr_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t aux[2] = {nullptr, nullptr};  // copy streams of the batch pipeline
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    const char* last_kernel = "";
+    DevBuf scratch[8];        // grow-only device scratch, reused across calls
+    void* pinned[4] = {nullptr, nullptr, nullptr, nullptr};
+    size_t pinned_cap[4] = {0, 0, 0, 0};
+    std::vector<sr_pair*> batch_pairs;
+    void* nccl_comm = nullptr;
+    int rank = 0, nranks = 1;
+};
+
+// Packed image: one uint32 per pixel (B | G<<8 | R<<16, top byte 0), SR_PADL pixels of left
+// padding and right padding so that every tile / candidate load stays inside the row.
+struct PackedImage {
+    uint32_t* base = nullptr;  // allocation
+    uint32_t* px = nullptr;    // pointer to pixel (0,0)
+    int w = 0, h = 0;
+    int pitch = 0;             // pixels per row (multiple of 32)
+};
+
+struct sr_pair {
+    int w1 = 0, h1 = 0, w2 = 0, h2 = 0;
+    uint8_t *rawL = nullptr, *rawR = nullptr;  // BGR as uploaded, tight pitch 3*w
+    PackedImage L, R;
+    int pad_disp = 0;          // right padding of L covers this many disparities
+    // per-pixel records of the reference-side (output) image
+    int ow = 0, oh = 0;        // output size (RIGHT/LINEAR: w2 x h2; LEFT: w1 x h1)
+    unsigned long long* best = nullptr;   // (cost << 32 | d) first minimum over the searched range
+    unsigned long long* c0 = nullptr;     // cost at d == 0 (SR_NONE64 when not a candidate)
+    unsigned long long* cr = nullptr;     // wide-cost first minimum (direct kernels)
+    int* dr = nullptr;
+    int* nwin = nullptr;                  // window pixel count; -1 = skipped (black) pixel
+    uint32_t* bits = nullptr;             // bit planes for the smoothing pass
+    double* alt = nullptr;
+    double* out = nullptr;                // result, ow x oh, tight
+    float* outf = nullptr;                // float copy for the reconstruction pipeline
+    int* maxblock = nullptr;              // device scalar
+    unsigned long long* evals = nullptr;  // device scalar
+    size_t npx_cap = 0;
+    int last_row0 = 0, last_row1 = 0;
+    bool evals_valid = false;
+};
+
+int sr_fail(sr_ctx* ctx, int code, const char* fmt, ...);
+int sr_cuda_check(sr_ctx* ctx, cudaError_t e, const char* what);
+void* sr_scratch(sr_ctx* ctx, int slot, size_t bytes);  // nullptr on failure (error set)
+void* sr_pinned(sr_ctx* ctx, int slot, size_t bytes);
+
+#define SR_CUDA(ctx, call)                                              \
+    do {                                                                \
+        cudaError_t e__ = (call);                                       \
+        if (e__ != cudaSuccess) return sr_cuda_check(ctx, e__, #call);  \
+    } while (0)
+#define SR_LAUNCHED(ctx)                                                        \
+    do {                                                                        \
+        (ctx)->launches++;                                                      \
+        cudaError_t e__ = cudaGetLastError();                                   \
+        if (e__ != cudaSuccess) return sr_cuda_check(ctx, e__, "kernel launch"); \
+    } while (0)
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// ---- launchers implemented in the .cu files (all asynchronous on ctx->stream) ----
+int sr_launch_pack(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int h, PackedImage* img);
+
+struct SearchGeom {
+    int w1, h1, w2, h2, height;  // height = min(h1,h2)
+    int block, half;             // blockSize_ and (block-1)/2
+    int dlo, dhi;                // candidate range [dlo, dhi)
+    int row0, row1;              // output rows to compute
+};
+// Fast path: fixed window, SSD/SAD, first minimum over [dlo,dhi) -> pair->best.
+// Returns 1 when it handled the request, 0 when the shape is not supported (caller falls back).
+int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref);
+// Universal path: per-pixel windows (var_block), any size; wide costs -> c0/cr/dr/nwin.
+int sr_launch_search_direct(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int var_block,
+                            double thres, int want_c0);
+// cost at d == 0 for the fixed window -> pair->c0
+int sr_launch_cost0(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost);
+// best/c0 (tile path) or c0/cr/dr/nwin (direct path) -> pair->out, reference rules.
+int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, double smooth, int from_direct,
+                            int have_c0);
+int sr_launch_search_left(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, double smooth);
+int sr_launch_search_linear(sr_ctx* ctx, sr_pair* pair, double smooth);
+int sr_launch_count_evals(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g);
+// NCC / sub-pixel / LR-check extension path (search_ext.cu)
+int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1);

@@ -1,0 +1,97 @@
+"""Parity of the CUDA WindowSearch path (through the C-ABI) with the CPU oracle and the committed
+cv2-executed golden vectors.  Bar: bit-exact (integer disparities stored as CV_64F)."""
+import numpy as np
+import pytest
+
+from conftest import golden_cases
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def sr():
+    import stereo_reconstruction_b200 as s
+    return s
+
+
+@pytest.fixture(scope="module")
+def ctx(sr):
+    return sr.capi.default_context()
+
+
+def synth(orc, w, h, min_d, max_d, seed=0xB200, pair=0, quant=False):
+    return orc.synth_pair(seed, pair, w, h, min_d, max_d, quant)
+
+
+@pytest.mark.parametrize("name,z", golden_cases("right"), ids=lambda v: v if isinstance(v, str) else "")
+def test_right_golden(sr, ctx, name, z):
+    bs = sr.BlockSearch(z["left"], z["right"], int(z["block"]), int(z["min_d"]), int(z["max_d"]), ctx=ctx)
+    out = bs.computeDisparityMapRight(float(z["smooth"]), bool(z["var_block"]), float(z["thres"]))
+    np.testing.assert_array_equal(out, z["out"])
+    assert bs.maxBlockSize == int(z["max_block"])
+
+
+@pytest.mark.parametrize("block", [3, 5, 7, 8, 9, 11, 13, 15, 17, 19, 21])
+@pytest.mark.parametrize("smooth", [1.0, 0.9])
+def test_right_vs_oracle_synth(sr, ctx, orc, block, smooth):
+    w, h, D = 700, 150, 70
+    L, R = synth(orc, w, h, 0, D)
+    want = orc.block_search_right_fast(L, R, block, 0, D, smooth)
+    got = sr.BlockSearch(L, R, block, 0, D, ctx=ctx).computeDisparityMapRight(smooth)
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("cost", [0, 1])
+@pytest.mark.parametrize("quant", [False, True])
+def test_right_ties_and_sad(sr, ctx, orc, cost, quant):
+    """4-level quantised images make ties frequent: first minimum (smallest d) must win."""
+    w, h, D = 530, 97, 40
+    L, R = synth(orc, w, h, 0, D, seed=7, quant=quant)
+    R[10:20, 30:50] = 0  # black pixels are skipped (BlockSearch.cpp:105)
+    want = orc.block_search_right_fast(L, R, 9, 0, D, 1.0, cost=cost)
+    got = sr.BlockSearch(L, R, 9, 0, D, cost=cost, ctx=ctx).computeDisparityMapRight(1.0)
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("w1,h1,w2,h2", [(300, 80, 280, 80), (280, 80, 300, 80), (300, 90, 300, 80), (64, 33, 64, 33), (17, 9, 17, 9)])
+def test_right_unequal_sizes(sr, ctx, orc, w1, h1, w2, h2):
+    rng = np.random.default_rng(3)
+    L = rng.integers(0, 256, (h1, w1, 3), dtype=np.uint8)
+    R = rng.integers(0, 256, (h2, w2, 3), dtype=np.uint8)
+    for smooth in (1.0, 0.8):
+        want = orc.block_search_right_fast(L, R, 7, 0, 50, smooth)
+        got = sr.BlockSearch(L, R, 7, 0, 50, ctx=ctx).computeDisparityMapRight(smooth)
+        np.testing.assert_array_equal(got, want)
+
+
+def test_right_min_disp_and_wide_range(sr, ctx, orc):
+    L, R = synth(orc, 400, 60, 5, 300)
+    for mn, mx in ((5, 300), (0, 1), (3, 4), (390, 500), (0, 1000)):
+        want = orc.block_search_right_fast(L, R, 9, mn, mx, 0.9)
+        got = sr.BlockSearch(L, R, 9, mn, mx, ctx=ctx).computeDisparityMapRight(0.9)
+        np.testing.assert_array_equal(got, want, err_msg=f"range {mn},{mx}")
+
+
+def test_right_row_band(sr, ctx, orc):
+    """Row bands (config 4 sharding): a band equals the same rows of the full map."""
+    L, R = synth(orc, 600, 120, 0, 64)
+    want = orc.block_search_right_fast(L, R, 9, 0, 64, 1.0)
+    pair = sr.capi.Pair(ctx, 600, 120, 600, 120)
+    pair.upload(L, R)
+    p = sr.capi.search_params(block=9, min_disp=0, max_disp=64, smooth=1.0)
+    for r0, r1 in ((0, 40), (40, 95), (95, 120), (7, 8)):
+        pair.run(p, r0, r1)
+        got = pair.download(p, row0=r0, row1=r1)
+        np.testing.assert_array_equal(got[r0:r1], want[r0:r1])
+
+
+def test_errors(sr, ctx):
+    L = np.zeros((40, 60, 3), np.uint8)
+    R = np.zeros((50, 60, 3), np.uint8)
+    with pytest.raises(sr.capi.SrError) as e:  # h1 < h2: the reference throws cv::Exception
+        sr.BlockSearch(L, R, 9, 0, 16, ctx=ctx).computeDisparityMapRight(1.0)
+    assert e.value.code == sr.capi.E_SHAPE
+    with pytest.raises(sr.capi.SrError):
+        sr.BlockSearch(L, L, 0, 0, 16, ctx=ctx).computeDisparityMapRight(1.0)
+    with pytest.raises(sr.capi.SrError):
+        sr.BlockSearch(L[:, :, :2], L, 9, 0, 16, ctx=ctx).computeDisparityMapRight(1.0)
