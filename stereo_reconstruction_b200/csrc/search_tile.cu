@@ -1,0 +1,287 @@
+// search_tile.cu -- the fused cost + winner-take-all kernel (BlockSearch.cpp:100-175, fixed window).
+//
+// Work decomposition (B200: 148 SMs, 64K registers and up to 227 KB shared memory per SM):
+//   CTA    = one column tile (496 output columns) x one band of rows; NW warps, loops over passes
+//            of 4*NW candidate disparities.
+//   warp   = 4 consecutive disparities (one aligned group) of the pass, all 512 tile columns.
+//   thread = XT=16 consecutive image columns x DT=4 disparities: 64 vertical column sums in
+//            registers (the cost volume never leaves the register file).
+// Per output row:  (1) vertical sliding update of the 64 column sums: add the pointwise cost of the
+//   row entering the window, subtract the row leaving it (packed BGRx pixels: VABSDIFF4 + IDP.4A);
+//   (2) horizontal window sums by an in-register sliding sum over the thread's 16 columns plus
+//   2h-1 halo columns fetched from the next lane with SHFL; (3) first-minimum WTA on the key
+//   cost*64 + d_local (smallest d wins ties, BlockSearch.cpp:168), min over the thread's 4
+//   disparities in registers, over the CTA's warps through shared memory, over passes in a
+//   CTA-private read-modify-write of the (cost<<32 | d) record in HBM/L2.
+// Image rows are staged once per CTA and pass into a shared-memory ring (cp.async, 16 B chunks,
+// XOR-swizzled so that the 64 B lane stride of the LDS.128 reads is conflict free).
+//
+// Window geometry of the reference: rows [y-u, y+dn), cols [x-l, x+r) with l=min(x,h),
+// r=min(w2-x-1,h), u=min(y,h), dn=min(h2-y-1,h)  ==  the fixed window [x-h,x+h) x [y-h,y+h) with
+// the pointwise cost forced to 0 outside columns [0,w2-1) and rows [0,h2-1).
+#include "sr_internal.cuh"
+
+namespace {
+
+constexpr int XT = 16;            // columns per thread
+constexpr int DT = 4;             // disparities per thread
+constexpr int TILE_OUT = 31 * XT; // 496 output columns per CTA (lane 31 only feeds lane 30's halo)
+constexpr int RSEG = 512;         // right-image pixels per ring row
+constexpr int LSEG = 576;         // left-image pixels per ring row (512 + 4*NW(max 16) )
+constexpr int PF = 2;             // rows prefetched ahead
+
+__device__ __forceinline__ int swz(int c) { return c ^ ((c >> 3) & 3); }  // 16-byte chunk swizzle
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+template <int COST>
+__device__ __forceinline__ uint32_t pcost_add(uint32_t l, uint32_t r, uint32_t acc) {
+    if (COST == SR_COST_SAD) {
+        uint32_t o;
+        asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(o) : "r"(l), "r"(r), "r"(acc));
+        return o;
+    }
+    uint32_t ad = __vabsdiffu4(l, r);
+    return __dp4a(ad, ad, acc);
+}
+
+struct TileArgs {
+    const uint32_t* L; int pitchL;
+    const uint32_t* R; int pitchR;
+    unsigned long long* best;
+    int w1, h1, w2, h2;
+    int half;
+    int dlo, dhi;        // candidate range
+    int dbase;           // dlo rounded down to a multiple of 4
+    int npass;
+    int row0, row1;      // output rows (already clipped to min(h1,h2))
+    int band;            // rows per CTA band
+};
+
+template <int H2, int COST, int NW>
+__global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
+    constexpr int NSLOT = H2 + PF;
+    constexpr int HALO = H2 - 1;
+    extern __shared__ __align__(128) uint32_t smem[];
+    uint32_t* ring = smem;                                   // NSLOT x (RSEG + LSEG)
+    uint32_t* keysm = smem + NSLOT * (RSEG + LSEG);          // 2 x NW x 512
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int h = a.half;
+    const int CB = -XT + TILE_OUT * (int)blockIdx.x;         // first own column of lane 0
+    const int yb0 = a.row0 + a.band * (int)blockIdx.y;
+    const int yb1 = min(yb0 + a.band, a.row1);
+    if (yb0 >= yb1) return;
+    const int cb = CB + XT * lane;                            // this thread's own columns [cb, cb+16)
+
+    // own columns that contribute (inside [0, w2-1)); others are forced to 0
+    uint32_t colmask = 0;
+#pragma unroll
+    for (int j = 0; j < XT; j++) colmask |= (uint32_t)(cb + j >= 0 && cb + j < a.w2 - 1) << j;
+    // per-output candidate limit: d < min(dhi, w1 - x - r(x))  (break rule, BlockSearch.cpp:148)
+    int dlim_min = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < XT; j++) {
+        int x = cb + h + j;
+        if (x >= 0 && x < a.w2) dlim_min = min(dlim_min, min(a.dhi, a.w1 - x - min(a.w2 - x - 1, h)));
+    }
+
+    for (int pass = 0; pass < a.npass; pass++) {
+        const int dcta = a.dbase + pass * (DT * NW);         // first disparity of the pass (multiple of 4)
+        const int d0 = dcta + DT * warp;                      // this warp's 4 disparities
+        const int nactive = min(NW, (a.dhi - dcta + DT - 1) / DT);  // warps with at least one d < dhi
+        const bool active = warp < nactive;
+        const bool needmask = d0 < a.dlo || d0 + DT - 1 >= dlim_min;
+        const int y_start = yb0 - (H2 - 1);
+
+        uint32_t col[XT][DT];
+#pragma unroll
+        for (int j = 0; j < XT; j++)
+#pragma unroll
+            for (int t = 0; t < DT; t++) col[j][t] = 0;
+
+        auto row_ok = [&](int r) { return r >= 0 && r < a.h2 - 1; };
+        auto issue_row = [&](int r) {
+            if (row_ok(r)) {
+                uint32_t* slot = ring + (size_t)(((r % NSLOT) + NSLOT) % NSLOT) * (RSEG + LSEG);
+                for (int c = tid; c < (RSEG + LSEG) / 4; c += NW * 32) {
+                    if (c < RSEG / 4)
+                        cp_async16(slot + 4 * swz(c), a.R + (size_t)r * a.pitchR + CB + 4 * c);
+                    else {
+                        int cl = c - RSEG / 4;
+                        cp_async16(slot + RSEG + 4 * swz(cl), a.L + (size_t)r * a.pitchL + CB + dcta + 4 * cl);
+                    }
+                }
+            }
+            cp_async_commit();
+        };
+        // vertical update with image row r: SIGN = +1 add, -1 subtract
+        auto vertical = [&](int r, bool add) {
+            const uint32_t* slot = ring + (size_t)(((r % NSLOT) + NSLOT) % NSLOT) * (RSEG + LSEG);
+            const uint4* rs = reinterpret_cast<const uint4*>(slot);
+            const uint4* ls = reinterpret_cast<const uint4*>(slot + RSEG);
+            uint4 la = ls[swz(4 * lane + warp)];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                uint4 lb = ls[swz(4 * lane + warp + k + 1)];
+                uint4 rr = rs[swz(4 * lane + k)];
+                uint32_t l7[7] = {la.x, la.y, la.z, la.w, lb.x, lb.y, lb.z};
+                uint32_t r4[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+                for (int jj = 0; jj < 4; jj++)
+#pragma unroll
+                    for (int t = 0; t < DT; t++) {
+                        if (add) col[4 * k + jj][t] = pcost_add<COST>(l7[jj + t], r4[jj], col[4 * k + jj][t]);
+                        else col[4 * k + jj][t] -= pcost_add<COST>(l7[jj + t], r4[jj], 0u);
+                    }
+                la = lb;
+            }
+            if (colmask != 0xFFFFu) {
+#pragma unroll
+                for (int j = 0; j < XT; j++)
+                    if (!((colmask >> j) & 1u)) {
+#pragma unroll
+                        for (int t = 0; t < DT; t++) col[j][t] = 0;
+                    }
+            }
+        };
+        // CTA-wide reduction of the keys of output row y and merge into the HBM record
+        auto reduce_row = [&](int y) {
+            const uint32_t* kb = keysm + (size_t)(y & 1) * NW * 512;
+            int q = tid;  // one output column per thread (NW*32 >= 496 requires NW == 16; else loop)
+            for (; q < TILE_OUT; q += NW * 32) {
+                int x = CB + h + q;
+                if (x < 0 || x >= a.w2) continue;
+                int word = 4 * swz(q >> 2) + (q & 3);
+                uint32_t k = 0xFFFFFFFFu;
+                for (int w = 0; w < nactive; w++) k = min(k, kb[w * 512 + word]);
+                unsigned long long rec = SR_NONE64;
+                if (k != 0xFFFFFFFFu) rec = ((unsigned long long)(k >> 6) << 32) | (unsigned)(dcta + (int)(k & 63u));
+                unsigned long long* p = a.best + (size_t)y * a.w2 + x;
+                if (pass > 0) { unsigned long long old = *p; rec = old < rec ? old : rec; }  // ties keep the smaller d
+                *p = rec;
+            }
+        };
+
+        // prologue: rows of the first PF iterations
+#pragma unroll
+        for (int i = 0; i < PF; i++) issue_row(y_start + i + h - 1);
+
+        for (int y = y_start; y < yb1; y++) {
+            cp_async_wait<PF - 1>();
+            __syncthreads();
+            issue_row(y + PF + h - 1);
+            if (y - 1 >= yb0) reduce_row(y - 1);
+            if (!active) continue;
+            const int rin = y + h - 1;
+            if (row_ok(rin)) vertical(rin, true);
+            if (y >= yb0) {
+                uint32_t keys[XT];
+#pragma unroll
+                for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
+#pragma unroll
+                for (int t = 0; t < DT; t++) {
+                    uint32_t win[XT + HALO];
+#pragma unroll
+                    for (int i = 0; i < XT; i++) win[i] = col[i][t];
+#pragma unroll
+                    for (int i = 0; i < HALO; i++) win[XT + i] = __shfl_down_sync(0xffffffffu, col[i][t], 1);
+                    uint32_t S = 0;
+#pragma unroll
+                    for (int i = 0; i < H2; i++) S += win[i];
+                    const uint32_t dl = (uint32_t)(DT * warp + t);
+                    const int d = d0 + t;
+#pragma unroll
+                    for (int j = 0; j < XT; j++) {
+                        uint32_t key = S * 64u + dl;
+                        if (needmask) {
+                            int x = cb + h + j;
+                            int lim = min(a.dhi, a.w1 - x - min(a.w2 - x - 1, h));
+                            if (d < a.dlo || d >= lim) key = 0xFFFFFFFFu;
+                        }
+                        keys[j] = min(keys[j], key);
+                        if (j + 1 < XT) S += win[j + H2] - win[j];
+                    }
+                }
+                uint4* kw = reinterpret_cast<uint4*>(keysm + (size_t)(y & 1) * NW * 512 + warp * 512);
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    kw[swz(4 * lane + k)] = make_uint4(keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
+            }
+            const int rout = y - h;
+            if (y >= yb0 && y + 1 < yb1 && row_ok(rout)) vertical(rout, false);
+        }
+        cp_async_wait<0>();
+        __syncthreads();
+        reduce_row(yb1 - 1);
+        __syncthreads();  // the key buffers and the ring are reused by the next pass
+    }
+}
+
+template <int H2, int COST>
+int launch(sr_ctx* ctx, const TileArgs& a, int ntx, int nbands) {
+    constexpr int NW = 16;
+    size_t smem = ((size_t)(H2 + PF) * (RSEG + LSEG) + 2 * NW * 512) * sizeof(uint32_t);
+    static bool configured = false;
+    if (!configured) {
+        SR_CUDA(ctx, cudaFuncSetAttribute(search_tile_kernel<H2, COST, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    search_tile_kernel<H2, COST, NW><<<dim3(ntx, nbands), NW * 32, smem, ctx->stream>>>(a);
+    SR_LAUNCHED(ctx);
+    return 1;
+}
+
+template <int COST>
+int dispatch_h2(sr_ctx* ctx, const TileArgs& a, int ntx, int nbands) {
+    switch (2 * a.half) {
+        case 2: return launch<2, COST>(ctx, a, ntx, nbands);
+        case 4: return launch<4, COST>(ctx, a, ntx, nbands);
+        case 6: return launch<6, COST>(ctx, a, ntx, nbands);
+        case 8: return launch<8, COST>(ctx, a, ntx, nbands);
+        case 10: return launch<10, COST>(ctx, a, ntx, nbands);
+        case 12: return launch<12, COST>(ctx, a, ntx, nbands);
+        case 14: return launch<14, COST>(ctx, a, ntx, nbands);
+        case 16: return launch<16, COST>(ctx, a, ntx, nbands);
+        default: return 0;
+    }
+}
+
+}  // namespace
+
+int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref) {
+    if (left_ref) return 0;
+    if (g.half < 1 || g.half > 8) return 0;
+    if (cost != SR_COST_SSD_L2 && cost != SR_COST_SAD) return 0;
+    int r1 = g.row1 < g.height ? g.row1 : g.height;
+    if (r1 <= g.row0) return 1;            // nothing to compute: the resolve pass fills the rows
+    TileArgs a;
+    a.L = pair->L.px; a.pitchL = pair->L.pitch; a.R = pair->R.px; a.pitchR = pair->R.pitch;
+    a.best = pair->best;
+    a.w1 = g.w1; a.h1 = g.h1; a.w2 = g.w2; a.h2 = g.h2; a.half = g.half;
+    a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
+    a.npass = (g.dhi - a.dbase + 63) / 64;
+    a.row0 = g.row0; a.row1 = r1;
+    int ntx = (g.w2 + XT - g.half + TILE_OUT - 1) / TILE_OUT;
+    int rows = r1 - g.row0;
+    if (a.npass <= 0) {
+        // empty candidate range: every record is "none"
+        SR_CUDA(ctx, cudaMemsetAsync(pair->best + (size_t)g.row0 * g.w2, 0xFF, (size_t)rows * g.w2 * 8, ctx->stream));
+        return 1;
+    }
+    int sms = 148;
+    int nbands = sms / ntx;
+    if (nbands < 1) nbands = 1;
+    int minband = 4 * g.half + 8;            // keep the vertical warm-up (2h-1 rows) a small fraction
+    if (nbands > (rows + minband - 1) / minband) nbands = (rows + minband - 1) / minband;
+    a.band = (rows + nbands - 1) / nbands;
+    nbands = (rows + a.band - 1) / a.band;
+    if (cost == SR_COST_SAD) return dispatch_h2<SR_COST_SAD>(ctx, a, ntx, nbands);
+    return dispatch_h2<SR_COST_SSD_L2>(ctx, a, ntx, nbands);
+}

@@ -1,7 +1,6 @@
 // stubs.cu -- entry points not implemented yet (fail loudly, never fall back).
 #include "sr_internal.cuh"
 #define NOTYET(ctx, name) return sr_fail(ctx, SR_E_BADARG, name ": not implemented yet")
-int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref) { return 0; }
 int sr_launch_search_left(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, double smooth) { NOTYET(ctx, "left variant"); }
 int sr_launch_search_linear(sr_ctx* ctx, sr_pair* pair, double smooth) { NOTYET(ctx, "linear variant"); }
 int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1) { NOTYET(ctx, "extension costs"); }
