@@ -13,8 +13,10 @@
 //   cost*64 + d_local (smallest d wins ties, BlockSearch.cpp:168), min over the thread's 4
 //   disparities in registers, over the CTA's warps through shared memory, over passes in a
 //   CTA-private read-modify-write of the (cost<<32 | d) record in HBM/L2.
-// Image rows are staged once per CTA and pass into a shared-memory ring (cp.async, 16 B chunks,
-// XOR-swizzled so that the 64 B lane stride of the LDS.128 reads is conflict free).
+// Image rows are staged once per CTA and pass into a shared-memory ring (cp.async, 16 B chunks).
+// Shared-memory rows are padded by one 16 B chunk after every 4 chunks (one thread's 16 pixels):
+// the 64 B lane stride of the LDS.128 reads becomes 80 B, which is bank-conflict free, and every
+// read address is "lane base + warp-uniform offset".
 //
 // Window geometry of the reference: rows [y-u, y+dn), cols [x-l, x+r) with l=min(x,h),
 // r=min(w2-x-1,h), u=min(y,h), dn=min(h2-y-1,h)  ==  the fixed window [x-h,x+h) x [y-h,y+h) with
@@ -23,14 +25,18 @@
 
 namespace {
 
-constexpr int XT = 16;            // columns per thread
-constexpr int DT = 4;             // disparities per thread
-constexpr int TILE_OUT = 31 * XT; // 496 output columns per CTA (lane 31 only feeds lane 30's halo)
-constexpr int RSEG = 512;         // right-image pixels per ring row
-constexpr int LSEG = 576;         // left-image pixels per ring row (512 + 4*NW(max 16) )
-constexpr int PF = 2;             // rows prefetched ahead
+constexpr int XT = 16;             // columns per thread
+constexpr int DT = 4;              // disparities per thread
+constexpr int TILE_OUT = 31 * XT;  // 496 output columns per CTA (lane 31 only feeds lane 30's halo)
+constexpr int RCH = 128;           // right-image 16 B chunks per ring row (512 pixels)
+constexpr int LCH = 144;           // left-image chunks per ring row (512 + 4*16 pixels)
+constexpr int RPOS = RCH + RCH / 4;  // padded chunk positions
+constexpr int LPOS = LCH + LCH / 4;
+constexpr int SLOT_U4 = RPOS + LPOS;  // uint4 per ring slot
+constexpr int KEY_U4 = 160;           // uint4 per warp key row (128 chunks padded)
+constexpr int PF = 2;                 // rows prefetched ahead
 
-__device__ __forceinline__ int swz(int c) { return c ^ ((c >> 3) & 3); }  // 16-byte chunk swizzle
+__device__ __forceinline__ int padpos(int c) { return c + (c >> 2); }
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     unsigned s = (unsigned)__cvta_generic_to_shared(smem);
@@ -51,6 +57,38 @@ __device__ __forceinline__ uint32_t pcost_add(uint32_t l, uint32_t r, uint32_t a
     return __dp4a(ad, ad, acc);
 }
 
+// vertical update of the 64 column sums with one staged image row (ADD: row enters the window).
+// rs / ls: this lane's base inside the slot (right segment / left segment), lo[i]: warp-uniform
+// padded offsets of the 5 left chunks.
+template <int COST, bool ADD>
+__device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], const uint4* rs, const uint4* ls,
+                                                const int (&lo)[5], uint32_t colmask) {
+    uint4 la = ls[lo[0]];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        uint4 lb = ls[lo[k + 1]];
+        uint4 rr = rs[k];
+        uint32_t l7[7] = {la.x, la.y, la.z, la.w, lb.x, lb.y, lb.z};
+        uint32_t r4[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+        for (int jj = 0; jj < 4; jj++)
+#pragma unroll
+            for (int t = 0; t < DT; t++) {
+                if (ADD) col[4 * k + jj][t] = pcost_add<COST>(l7[jj + t], r4[jj], col[4 * k + jj][t]);
+                else col[4 * k + jj][t] -= pcost_add<COST>(l7[jj + t], r4[jj], 0u);
+            }
+        la = lb;
+    }
+    if (colmask != 0xFFFFu) {
+#pragma unroll
+        for (int j = 0; j < XT; j++)
+            if (!((colmask >> j) & 1u)) {
+#pragma unroll
+                for (int t = 0; t < DT; t++) col[j][t] = 0;
+            }
+    }
+}
+
 struct TileArgs {
     const uint32_t* L; int pitchL;
     const uint32_t* R; int pitchR;
@@ -62,23 +100,56 @@ struct TileArgs {
     int npass;
     int row0, row1;      // output rows (already clipped to min(h1,h2))
     int band;            // rows per CTA band
+    uint32_t k64;        // == 64, passed as data so that key = S*64+d stays one IMAD (FMA pipe)
 };
+
+// horizontal window sums + in-thread WTA for one output row.  MASKED: candidates outside
+// [dlo, dlim(x)) are discarded (tiles that touch the break rule or the range ends).
+template <int H2, bool MASKED>
+__device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32_t (&keys)[XT], uint32_t k64,
+                                           uint32_t dl0, int d0, int x0, const TileArgs& a) {
+    constexpr int HALO = H2 - 1;
+#pragma unroll
+    for (int t = 0; t < DT; t++) {
+        uint32_t win[XT + HALO];
+#pragma unroll
+        for (int i = 0; i < XT; i++) win[i] = col[i][t];
+#pragma unroll
+        for (int i = 0; i < HALO; i++) win[XT + i] = __shfl_down_sync(0xffffffffu, col[i][t], 1);
+        uint32_t S = 0;
+#pragma unroll
+        for (int i = 0; i < H2; i++) S += win[i];
+        const uint32_t dl = dl0 + t;
+#pragma unroll
+        for (int j = 0; j < XT; j++) {
+            uint32_t key = S * k64 + dl;
+            if (MASKED) {
+                int x = x0 + j, d = d0 + t;
+                int lim = min(a.dhi, a.w1 - x - min(a.w2 - x - 1, a.half));
+                if (d < a.dlo || d >= lim) key = 0xFFFFFFFFu;
+            }
+            keys[j] = min(keys[j], key);
+            if (j + 1 < XT) S += win[j + H2] - win[j];
+        }
+    }
+}
 
 template <int H2, int COST, int NW>
 __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     constexpr int NSLOT = H2 + PF;
-    constexpr int HALO = H2 - 1;
-    extern __shared__ __align__(128) uint32_t smem[];
-    uint32_t* ring = smem;                                   // NSLOT x (RSEG + LSEG)
-    uint32_t* keysm = smem + NSLOT * (RSEG + LSEG);          // 2 x NW x 512
+    extern __shared__ __align__(128) uint4 smem4[];
+    uint4* ring = smem4;                          // NSLOT x SLOT_U4
+    uint4* keysm = smem4 + NSLOT * SLOT_U4;       // 2 x NW x KEY_U4
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler
     const int h = a.half;
-    const int CB = -XT + TILE_OUT * (int)blockIdx.x;         // first own column of lane 0
+    const int CB = -XT + TILE_OUT * (int)blockIdx.x;          // first own column of lane 0
     const int yb0 = a.row0 + a.band * (int)blockIdx.y;
     const int yb1 = min(yb0 + a.band, a.row1);
     if (yb0 >= yb1) return;
-    const int cb = CB + XT * lane;                            // this thread's own columns [cb, cb+16)
+    const int cb = CB + XT * lane;                             // this thread's own columns [cb, cb+16)
+    const uint32_t k64 = a.k64;
 
     // own columns that contribute (inside [0, w2-1)); others are forced to 0
     uint32_t colmask = 0;
@@ -91,14 +162,21 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
         int x = cb + h + j;
         if (x >= 0 && x < a.w2) dlim_min = min(dlim_min, min(a.dhi, a.w1 - x - min(a.w2 - x - 1, h)));
     }
+    // lane bases inside a slot / key row (5 chunk positions per lane: 4 data + 1 pad)
+    const int lane_u4 = 5 * lane;
+    int lo[5];
+#pragma unroll
+    for (int i = 0; i < 5; i++) lo[i] = padpos(warp + i);      // warp-uniform left-chunk offsets
+    const int y_start = yb0 - (H2 - 1);
+    auto row_ok = [&](int r) { return r >= 0 && r < a.h2 - 1; };
+    auto slot_of = [&](int r) { return ((r % NSLOT) + NSLOT) % NSLOT; };
 
     for (int pass = 0; pass < a.npass; pass++) {
-        const int dcta = a.dbase + pass * (DT * NW);         // first disparity of the pass (multiple of 4)
-        const int d0 = dcta + DT * warp;                      // this warp's 4 disparities
+        const int dcta = a.dbase + pass * (DT * NW);           // first disparity of the pass (multiple of 4)
+        const int d0 = dcta + DT * warp;                        // this warp's 4 disparities
         const int nactive = min(NW, (a.dhi - dcta + DT - 1) / DT);  // warps with at least one d < dhi
         const bool active = warp < nactive;
-        const bool needmask = d0 < a.dlo || d0 + DT - 1 >= dlim_min;
-        const int y_start = yb0 - (H2 - 1);
+        const bool needmask = __any_sync(0xffffffffu, d0 < a.dlo || d0 + DT - 1 >= dlim_min);
 
         uint32_t col[XT][DT];
 #pragma unroll
@@ -106,61 +184,27 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
 #pragma unroll
             for (int t = 0; t < DT; t++) col[j][t] = 0;
 
-        auto row_ok = [&](int r) { return r >= 0 && r < a.h2 - 1; };
         auto issue_row = [&](int r) {
             if (row_ok(r)) {
-                uint32_t* slot = ring + (size_t)(((r % NSLOT) + NSLOT) % NSLOT) * (RSEG + LSEG);
-                for (int c = tid; c < (RSEG + LSEG) / 4; c += NW * 32) {
-                    if (c < RSEG / 4)
-                        cp_async16(slot + 4 * swz(c), a.R + (size_t)r * a.pitchR + CB + 4 * c);
-                    else {
-                        int cl = c - RSEG / 4;
-                        cp_async16(slot + RSEG + 4 * swz(cl), a.L + (size_t)r * a.pitchL + CB + dcta + 4 * cl);
-                    }
+                uint4* slot = ring + slot_of(r) * SLOT_U4;
+                const uint32_t* rsrc = a.R + (size_t)r * a.pitchR + CB;
+                const uint32_t* lsrc = a.L + (size_t)r * a.pitchL + CB + dcta;
+                for (int c = tid; c < RCH + LCH; c += NW * 32) {
+                    if (c < RCH) cp_async16(slot + padpos(c), rsrc + 4 * c);
+                    else cp_async16(slot + RPOS + padpos(c - RCH), lsrc + 4 * (c - RCH));
                 }
             }
             cp_async_commit();
         };
-        // vertical update with image row r: SIGN = +1 add, -1 subtract
-        auto vertical = [&](int r, bool add) {
-            const uint32_t* slot = ring + (size_t)(((r % NSLOT) + NSLOT) % NSLOT) * (RSEG + LSEG);
-            const uint4* rs = reinterpret_cast<const uint4*>(slot);
-            const uint4* ls = reinterpret_cast<const uint4*>(slot + RSEG);
-            uint4 la = ls[swz(4 * lane + warp)];
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                uint4 lb = ls[swz(4 * lane + warp + k + 1)];
-                uint4 rr = rs[swz(4 * lane + k)];
-                uint32_t l7[7] = {la.x, la.y, la.z, la.w, lb.x, lb.y, lb.z};
-                uint32_t r4[4] = {rr.x, rr.y, rr.z, rr.w};
-#pragma unroll
-                for (int jj = 0; jj < 4; jj++)
-#pragma unroll
-                    for (int t = 0; t < DT; t++) {
-                        if (add) col[4 * k + jj][t] = pcost_add<COST>(l7[jj + t], r4[jj], col[4 * k + jj][t]);
-                        else col[4 * k + jj][t] -= pcost_add<COST>(l7[jj + t], r4[jj], 0u);
-                    }
-                la = lb;
-            }
-            if (colmask != 0xFFFFu) {
-#pragma unroll
-                for (int j = 0; j < XT; j++)
-                    if (!((colmask >> j) & 1u)) {
-#pragma unroll
-                        for (int t = 0; t < DT; t++) col[j][t] = 0;
-                    }
-            }
-        };
         // CTA-wide reduction of the keys of output row y and merge into the HBM record
         auto reduce_row = [&](int y) {
-            const uint32_t* kb = keysm + (size_t)(y & 1) * NW * 512;
-            int q = tid;  // one output column per thread (NW*32 >= 496 requires NW == 16; else loop)
-            for (; q < TILE_OUT; q += NW * 32) {
+            const uint32_t* kb = reinterpret_cast<const uint32_t*>(keysm + (y & 1) * NW * KEY_U4);
+            for (int q = tid; q < TILE_OUT; q += NW * 32) {
                 int x = CB + h + q;
                 if (x < 0 || x >= a.w2) continue;
-                int word = 4 * swz(q >> 2) + (q & 3);
+                int word = q + 4 * (q >> 4);
                 uint32_t k = 0xFFFFFFFFu;
-                for (int w = 0; w < nactive; w++) k = min(k, kb[w * 512 + word]);
+                for (int w = 0; w < nactive; w++) k = min(k, kb[w * (KEY_U4 * 4) + word]);
                 unsigned long long rec = SR_NONE64;
                 if (k != 0xFFFFFFFFu) rec = ((unsigned long long)(k >> 6) << 32) | (unsigned)(dcta + (int)(k & 63u));
                 unsigned long long* p = a.best + (size_t)y * a.w2 + x;
@@ -173,49 +217,37 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
 #pragma unroll
         for (int i = 0; i < PF; i++) issue_row(y_start + i + h - 1);
 
+        int s_in = slot_of(y_start + h - 1), s_out = slot_of(y_start - h);
         for (int y = y_start; y < yb1; y++) {
             cp_async_wait<PF - 1>();
             __syncthreads();
             issue_row(y + PF + h - 1);
             if (y - 1 >= yb0) reduce_row(y - 1);
-            if (!active) continue;
-            const int rin = y + h - 1;
-            if (row_ok(rin)) vertical(rin, true);
-            if (y >= yb0) {
-                uint32_t keys[XT];
+            if (active) {
+                const int rin = y + h - 1;
+                if (row_ok(rin)) {
+                    const uint4* sl = ring + s_in * SLOT_U4 + lane_u4;
+                    vertical_update<COST, true>(col, sl, sl + RPOS, lo, colmask);
+                }
+                if (y >= yb0) {
+                    uint32_t keys[XT];
 #pragma unroll
-                for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
+                    for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
+                    if (needmask) window_wta<H2, true>(col, keys, k64, (uint32_t)(DT * warp), d0, cb + h, a);
+                    else window_wta<H2, false>(col, keys, k64, (uint32_t)(DT * warp), d0, cb + h, a);
+                    uint4* kw = keysm + ((y & 1) * NW + warp) * KEY_U4 + lane_u4;
 #pragma unroll
-                for (int t = 0; t < DT; t++) {
-                    uint32_t win[XT + HALO];
-#pragma unroll
-                    for (int i = 0; i < XT; i++) win[i] = col[i][t];
-#pragma unroll
-                    for (int i = 0; i < HALO; i++) win[XT + i] = __shfl_down_sync(0xffffffffu, col[i][t], 1);
-                    uint32_t S = 0;
-#pragma unroll
-                    for (int i = 0; i < H2; i++) S += win[i];
-                    const uint32_t dl = (uint32_t)(DT * warp + t);
-                    const int d = d0 + t;
-#pragma unroll
-                    for (int j = 0; j < XT; j++) {
-                        uint32_t key = S * 64u + dl;
-                        if (needmask) {
-                            int x = cb + h + j;
-                            int lim = min(a.dhi, a.w1 - x - min(a.w2 - x - 1, h));
-                            if (d < a.dlo || d >= lim) key = 0xFFFFFFFFu;
-                        }
-                        keys[j] = min(keys[j], key);
-                        if (j + 1 < XT) S += win[j + H2] - win[j];
+                    for (int k = 0; k < 4; k++)
+                        kw[k] = make_uint4(keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
+                    const int rout = y - h;
+                    if (y + 1 < yb1 && row_ok(rout)) {
+                        const uint4* sl = ring + s_out * SLOT_U4 + lane_u4;
+                        vertical_update<COST, false>(col, sl, sl + RPOS, lo, colmask);
                     }
                 }
-                uint4* kw = reinterpret_cast<uint4*>(keysm + (size_t)(y & 1) * NW * 512 + warp * 512);
-#pragma unroll
-                for (int k = 0; k < 4; k++)
-                    kw[swz(4 * lane + k)] = make_uint4(keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
             }
-            const int rout = y - h;
-            if (y >= yb0 && y + 1 < yb1 && row_ok(rout)) vertical(rout, false);
+            s_in = s_in + 1 == NSLOT ? 0 : s_in + 1;
+            s_out = s_out + 1 == NSLOT ? 0 : s_out + 1;
         }
         cp_async_wait<0>();
         __syncthreads();
@@ -227,7 +259,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
 template <int H2, int COST>
 int launch(sr_ctx* ctx, const TileArgs& a, int ntx, int nbands) {
     constexpr int NW = 16;
-    size_t smem = ((size_t)(H2 + PF) * (RSEG + LSEG) + 2 * NW * 512) * sizeof(uint32_t);
+    size_t smem = ((size_t)(H2 + PF) * SLOT_U4 + 2 * NW * KEY_U4) * sizeof(uint4);
     static bool configured = false;
     if (!configured) {
         SR_CUDA(ctx, cudaFuncSetAttribute(search_tile_kernel<H2, COST, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -267,7 +299,7 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     a.w1 = g.w1; a.h1 = g.h1; a.w2 = g.w2; a.h2 = g.h2; a.half = g.half;
     a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
     a.npass = (g.dhi - a.dbase + 63) / 64;
-    a.row0 = g.row0; a.row1 = r1;
+    a.row0 = g.row0; a.row1 = r1; a.k64 = 64;
     int ntx = (g.w2 + XT - g.half + TILE_OUT - 1) / TILE_OUT;
     int rows = r1 - g.row0;
     if (a.npass <= 0) {
