@@ -11,6 +11,8 @@
 // resolved row by row with bit-parallel carry propagation (one 32-pixel word per thread).
 #include "sr_internal.cuh"
 
+struct Planes { const uint32_t* planes; size_t stride; int npass, dbase; };
+
 struct PixRec {
     bool skip;                  // black pixel / unvisited row -> 0.0
     unsigned long long c0, cr;  // SR_NONE64 when absent
@@ -19,7 +21,7 @@ struct PixRec {
 };
 
 __device__ __forceinline__ PixRec load_rec(int from_direct, int have_c0, size_t i, int x, int y,
-                                           const unsigned long long* best, const unsigned long long* c0,
+                                           Planes pl, const unsigned long long* c0,
                                            const unsigned long long* cr, const int* dr, const int* nwin,
                                            const uint32_t* Rp, int pitchR, const SearchGeom& g) {
     PixRec r;
@@ -31,16 +33,22 @@ __device__ __forceinline__ PixRec load_rec(int from_direct, int have_c0, size_t 
         r.skip = y >= g.height || (__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) == 0;
         int l = min(x, g.half), rr = min(g.w2 - x - 1, g.half), u = min(y, g.half), dn = min(g.h2 - y - 1, g.half);
         r.n = (l + rr) * (u + dn);
-        unsigned long long b = best[i];
-        r.cr = b == SR_NONE64 ? SR_NONE64 : (b >> 32);
-        r.dr = (int)(b & 0xFFFFFFFFull);
+        // first minimum over the passes' key planes (cost*64 + d_local; passes ascend in d,
+        // strict < keeps the smaller d on ties)
+        uint32_t bc = 0xFFFFFFFFu; int bd = 0;
+        for (int p = 0; p < pl.npass; p++) {
+            uint32_t k = __ldg(pl.planes + (size_t)p * pl.stride + i);
+            if (k != 0xFFFFFFFFu && (k >> 6) < bc) { bc = k >> 6; bd = pl.dbase + 64 * p + (int)(k & 63u); }
+        }
+        r.cr = bc == 0xFFFFFFFFu ? SR_NONE64 : (unsigned long long)bc;
+        r.dr = bd;
         r.c0 = have_c0 ? c0[i] : SR_NONE64;
     }
     return r;
 }
 
 // smooth == 1 (or no d == 0 candidate in range): pointwise.
-__global__ void resolve_plain_kernel(SearchGeom g, int from_direct, int have_c0, const unsigned long long* __restrict__ best,
+__global__ void resolve_plain_kernel(SearchGeom g, int from_direct, int have_c0, Planes best,
                                      const unsigned long long* __restrict__ c0, const unsigned long long* __restrict__ cr,
                                      const int* __restrict__ dr, const int* __restrict__ nwin,
                                      const uint32_t* __restrict__ Rp, int pitchR, double* __restrict__ out) {
@@ -59,7 +67,7 @@ __global__ void resolve_plain_kernel(SearchGeom g, int from_direct, int have_c0,
 }
 
 // Phase A of the smoothing pass: bit planes a0,a1,a2 (ballot words) and the alternative value.
-__global__ void smooth_prepare_kernel(SearchGeom g, int from_direct, double s, const unsigned long long* __restrict__ best,
+__global__ void smooth_prepare_kernel(SearchGeom g, int from_direct, double s, Planes best,
                                       const unsigned long long* __restrict__ c0, const unsigned long long* __restrict__ cr,
                                       const int* __restrict__ dr, const int* __restrict__ nwin,
                                       const uint32_t* __restrict__ Rp, int pitchR, uint32_t* __restrict__ bits,
@@ -180,10 +188,11 @@ __global__ void smooth_expand_kernel(SearchGeom g, int words, const uint32_t* __
 int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, double smooth, int from_direct, int have_c0) {
     int rows = g.row1 - g.row0;
     if (rows <= 0) return SR_OK;
+    Planes pl{pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase};
     dim3 grid(cdiv(g.w2, 128), rows);
     bool plain = smooth == 1.0 || !have_c0;
     if (plain) {
-        resolve_plain_kernel<<<grid, 128, 0, ctx->stream>>>(g, from_direct, have_c0, pair->best, pair->c0, pair->cr, pair->dr,
+        resolve_plain_kernel<<<grid, 128, 0, ctx->stream>>>(g, from_direct, have_c0, pl, pair->c0, pair->cr, pair->dr,
                                                             pair->nwin, pair->R.px, pair->R.pitch, pair->out);
         SR_LAUNCHED(ctx);
         return SR_OK;
@@ -197,7 +206,7 @@ int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, dou
     uint32_t* zb = pair->bits + (size_t)rows * words * 3;
     dim3 gridw(words, rows);
     smooth_prepare_kernel<<<dim3(cdiv(words * 32, 128), rows), 128, 0, ctx->stream>>>(
-        g, from_direct, smooth, pair->best, pair->c0, pair->cr, pair->dr, pair->nwin, pair->R.px, pair->R.pitch, pair->bits,
+        g, from_direct, smooth, pl, pair->c0, pair->cr, pair->dr, pair->nwin, pair->R.px, pair->R.pitch, pair->bits,
         words, pair->alt);
     SR_LAUNCHED(ctx);
     // s <= 1 makes a0 <= a1 <= a2 (more multiplications -> smaller cost): adder-style carries

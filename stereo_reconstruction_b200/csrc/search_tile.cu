@@ -92,7 +92,8 @@ __device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], const u
 struct TileArgs {
     const uint32_t* L; int pitchL;
     const uint32_t* R; int pitchR;
-    unsigned long long* best;
+    uint32_t* planes;    // one u32 key plane (cost*64 + d_local) per pass of 64 disparities
+    size_t plane_stride; // elements per plane
     int w1, h1, w2, h2;
     int half;
     int dlo, dhi;        // candidate range
@@ -137,6 +138,7 @@ __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32
 template <int H2, int COST, int NW>
 __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     constexpr int NSLOT = H2 + PF;
+    static_assert(RCH + LCH <= NW * 32, "one staged chunk per thread");
     extern __shared__ __align__(128) uint4 smem4[];
     uint4* ring = smem4;                          // NSLOT x SLOT_U4
     uint4* keysm = smem4 + NSLOT * SLOT_U4;       // 2 x NW x KEY_U4
@@ -168,10 +170,14 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
 #pragma unroll
     for (int i = 0; i < 5; i++) lo[i] = padpos(warp + i);      // warp-uniform left-chunk offsets
     const int y_start = yb0 - (H2 - 1);
+    // this thread's chunk of every staged row (RCH + LCH <= NW*32 chunks per row)
+    const int ld_dst = tid < RCH ? padpos(tid) : RPOS + padpos(tid - RCH);
+    const int ld_src = CB + 4 * (tid < RCH ? tid : tid - RCH);
     auto row_ok = [&](int r) { return r >= 0 && r < a.h2 - 1; };
     auto slot_of = [&](int r) { return ((r % NSLOT) + NSLOT) % NSLOT; };
 
-    for (int pass = 0; pass < a.npass; pass++) {
+    {
+        const int pass = (int)blockIdx.z;
         const int dcta = a.dbase + pass * (DT * NW);           // first disparity of the pass (multiple of 4)
         const int d0 = dcta + DT * warp;                        // this warp's 4 disparities
         const int nactive = min(NW, (a.dhi - dcta + DT - 1) / DT);  // warps with at least one d < dhi
@@ -185,31 +191,28 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
             for (int t = 0; t < DT; t++) col[j][t] = 0;
 
         auto issue_row = [&](int r) {
-            if (row_ok(r)) {
-                uint4* slot = ring + slot_of(r) * SLOT_U4;
-                const uint32_t* rsrc = a.R + (size_t)r * a.pitchR + CB;
-                const uint32_t* lsrc = a.L + (size_t)r * a.pitchL + CB + dcta;
-                for (int c = tid; c < RCH + LCH; c += NW * 32) {
-                    if (c < RCH) cp_async16(slot + padpos(c), rsrc + 4 * c);
-                    else cp_async16(slot + RPOS + padpos(c - RCH), lsrc + 4 * (c - RCH));
-                }
+            if (row_ok(r) && tid < RCH + LCH) {
+                uint4* dst = ring + slot_of(r) * SLOT_U4 + ld_dst;
+                const uint32_t* src = (tid < RCH ? a.R + (size_t)r * a.pitchR : a.L + (size_t)r * a.pitchL + dcta) + ld_src;
+                cp_async16(dst, src);
             }
             cp_async_commit();
         };
-        // CTA-wide reduction of the keys of output row y and merge into the HBM record
+        // CTA-wide reduction of the keys of output row y -> this pass's key plane
+        uint32_t* plane = a.planes + (size_t)pass * a.plane_stride;
         auto reduce_row = [&](int y) {
             const uint32_t* kb = reinterpret_cast<const uint32_t*>(keysm + (y & 1) * NW * KEY_U4);
             for (int q = tid; q < TILE_OUT; q += NW * 32) {
                 int x = CB + h + q;
                 if (x < 0 || x >= a.w2) continue;
                 int word = q + 4 * (q >> 4);
+                uint32_t kk[NW];
+#pragma unroll
+                for (int w = 0; w < NW; w++) kk[w] = kb[w * (KEY_U4 * 4) + word];
                 uint32_t k = 0xFFFFFFFFu;
-                for (int w = 0; w < nactive; w++) k = min(k, kb[w * (KEY_U4 * 4) + word]);
-                unsigned long long rec = SR_NONE64;
-                if (k != 0xFFFFFFFFu) rec = ((unsigned long long)(k >> 6) << 32) | (unsigned)(dcta + (int)(k & 63u));
-                unsigned long long* p = a.best + (size_t)y * a.w2 + x;
-                if (pass > 0) { unsigned long long old = *p; rec = old < rec ? old : rec; }  // ties keep the smaller d
-                *p = rec;
+#pragma unroll
+                for (int w = 0; w < NW; w++) k = min(k, kk[w]);
+                plane[(size_t)y * a.w2 + x] = k;
             }
         };
 
@@ -225,7 +228,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
             if (y - 1 >= yb0) reduce_row(y - 1);
             if (active) {
                 const int rin = y + h - 1;
-                if (row_ok(rin)) {
+                if (row_ok(rin) && colmask != 0) {
                     const uint4* sl = ring + s_in * SLOT_U4 + lane_u4;
                     vertical_update<COST, true>(col, sl, sl + RPOS, lo, colmask);
                 }
@@ -240,11 +243,16 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
                     for (int k = 0; k < 4; k++)
                         kw[k] = make_uint4(keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
                     const int rout = y - h;
-                    if (y + 1 < yb1 && row_ok(rout)) {
+                    if (y + 1 < yb1 && row_ok(rout) && colmask != 0) {
                         const uint4* sl = ring + s_out * SLOT_U4 + lane_u4;
                         vertical_update<COST, false>(col, sl, sl + RPOS, lo, colmask);
                     }
                 }
+            }
+            else if (y >= yb0) {
+                uint4* kw = keysm + ((y & 1) * NW + warp) * KEY_U4 + lane_u4;
+#pragma unroll
+                for (int k = 0; k < 4; k++) kw[k] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
             }
             s_in = s_in + 1 == NSLOT ? 0 : s_in + 1;
             s_out = s_out + 1 == NSLOT ? 0 : s_out + 1;
@@ -252,7 +260,6 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
         cp_async_wait<0>();
         __syncthreads();
         reduce_row(yb1 - 1);
-        __syncthreads();  // the key buffers and the ring are reused by the next pass
     }
 }
 
@@ -265,7 +272,7 @@ int launch(sr_ctx* ctx, const TileArgs& a, int ntx, int nbands) {
         SR_CUDA(ctx, cudaFuncSetAttribute(search_tile_kernel<H2, COST, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = true;
     }
-    search_tile_kernel<H2, COST, NW><<<dim3(ntx, nbands), NW * 32, smem, ctx->stream>>>(a);
+    search_tile_kernel<H2, COST, NW><<<dim3(ntx, nbands, a.npass), NW * 32, smem, ctx->stream>>>(a);
     SR_LAUNCHED(ctx);
     return 1;
 }
@@ -292,10 +299,9 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     if (g.half < 1 || g.half > 8) return 0;
     if (cost != SR_COST_SSD_L2 && cost != SR_COST_SAD) return 0;
     int r1 = g.row1 < g.height ? g.row1 : g.height;
-    if (r1 <= g.row0) return 1;            // nothing to compute: the resolve pass fills the rows
+    if (r1 <= g.row0) { pair->npass = 0; return 1; }  // nothing to compute: the resolve pass fills the rows
     TileArgs a;
     a.L = pair->L.px; a.pitchL = pair->L.pitch; a.R = pair->R.px; a.pitchR = pair->R.pitch;
-    a.best = pair->best;
     a.w1 = g.w1; a.h1 = g.h1; a.w2 = g.w2; a.h2 = g.h2; a.half = g.half;
     a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
     a.npass = (g.dhi - a.dbase + 63) / 64;
@@ -304,16 +310,29 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     int rows = r1 - g.row0;
     if (a.npass <= 0) {
         // empty candidate range: every record is "none"
-        SR_CUDA(ctx, cudaMemsetAsync(pair->best + (size_t)g.row0 * g.w2, 0xFF, (size_t)rows * g.w2 * 8, ctx->stream));
+        pair->npass = 0;
         return 1;
     }
-    int sms = 148;
-    int nbands = sms / ntx;
-    if (nbands < 1) nbands = 1;
-    int minband = 4 * g.half + 8;            // keep the vertical warm-up (2h-1 rows) a small fraction
-    if (nbands > (rows + minband - 1) / minband) nbands = (rows + minband - 1) / minband;
-    a.band = (rows + nbands - 1) / nbands;
-    nbands = (rows + a.band - 1) / a.band;
+    // one u32 key plane per pass (merged by the resolve kernels): no read-modify-write in the hot loop
+    pair->npass = a.npass; pair->plane_dbase = a.dbase;
+    pair->planes = (uint32_t*)sr_scratch(ctx, 0, (size_t)a.npass * pair->npx_cap * sizeof(uint32_t));
+    if (!pair->planes) return SR_E_CUDA;
+    a.planes = pair->planes; a.plane_stride = pair->npx_cap;
+    // bands: CTAs = ntx * npass * nbands, one CTA per SM at a time; minimise waves * (band + warm-up rows)
+    const int sms = 148;
+    int maxnb = rows / (2 * g.half + 2);
+    if (maxnb < 1) maxnb = 1;
+    if (maxnb > 256) maxnb = 256;
+    long bestcost = -1;
+    int nbands = 1;
+    for (int nb = 1; nb <= maxnb; nb++) {
+        int band = (rows + nb - 1) / nb;
+        int nbe = (rows + band - 1) / band;
+        long ctas = (long)ntx * a.npass * nbe;
+        long waves = (ctas + sms - 1) / sms;
+        long c = waves * (band + 2 * g.half - 1 + 2);
+        if (bestcost < 0 || c < bestcost) { bestcost = c; nbands = nbe; a.band = band; }
+    }
     if (cost == SR_COST_SAD) return dispatch_h2<SR_COST_SAD>(ctx, a, ntx, nbands);
     return dispatch_h2<SR_COST_SSD_L2>(ctx, a, ntx, nbands);
 }

@@ -48,6 +48,8 @@ struct sr_pair {
     int pad_disp = 0;          // right padding of L covers this many disparities
     // per-pixel records of the reference-side (output) image
     int ow = 0, oh = 0;        // output size (RIGHT/LINEAR: w2 x h2; LEFT: w1 x h1)
+    uint32_t* planes = nullptr;           // tile kernel: per-pass key planes (ctx scratch), cost*64 + d_local
+    int npass = 0, plane_dbase = 0;
     unsigned long long* best = nullptr;   // (cost << 32 | d) first minimum over the searched range
     unsigned long long* c0 = nullptr;     // cost at d == 0 (SR_NONE64 when not a candidate)
     unsigned long long* cr = nullptr;     // wide-cost first minimum (direct kernels)
