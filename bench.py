@@ -1,0 +1,327 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the stereo hot path (BASELINE.json metric: million disparity
+evaluations per second, MDE/s).
+
+A step = one pass of the hot path (block-matching search, cost + WTA + resolve to the CV_64F map)
+over one synthetic rectified pair.  Default workload = BASELINE.json configs[3]:
+3840x2160, 512 disparities, 9x9 block, SAD; at N>1 the pair is row-band sharded and the bands are
+gathered to rank 0 over NCCL ("scaling": "strong").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload 4k512|1080p256|720p128|adirondack]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference ...      # the reference CPU algorithm (oracle port) on host cores
+
+Prints ONE JSON line on rank 0.  `value` = effective evaluations (reference semantics: candidates
+before the break rule) of the whole pair / device time per step with inputs resident in HBM;
+`e2e` = the same through the public host-pointer API (pinned host buffers, H2D + D2H inside).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (w, h, max_disp, block, cost)   -- BASELINE.json configs
+    "4k512": (3840, 2160, 512, 9, "sad"),       # configs[3]
+    "1080p256": (1920, 1080, 256, 9, "ssd"),    # configs[2] (one point of the sweep)
+    "720p128": (1280, 720, 128, 7, "sad"),      # configs[4] (one pair)
+    "adirondack": (1436, 992, 145, 17, "ssd"),  # configs[0] shape (synthetic content)
+}
+# algorithmic integer ops per evaluation: pointwise cost + 2 sliding sums + WTA
+OPS_PER_EVAL = {"ssd": 8, "sad": 7}
+# dram__bytes_read.sum + dram__bytes_write.sum of the search kernel from the committed ncu capture
+# (profiles/), per launch, keyed by workload; None = not captured for this workload
+NCU_TRAFFIC = {}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="4k512", choices=sorted(WORKLOADS))
+    ap.add_argument("--cost", default=None, choices=["ssd", "sad"])
+    ap.add_argument("--block", type=int, default=None)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.lines = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def _oracle_sample(orc, L, R, block, D, ocost, mid, rows):
+    """Runs the CPU port on `rows` output rows starting at `mid`, on a crop that carries the
+    window halo (so the port's per-call setup is proportional to the sample, not the image)."""
+    pad = block
+    y0 = max(mid - pad, 0)
+    y1 = min(mid + rows + pad, L.shape[0])
+    t0 = time.perf_counter()
+    orc.block_search_right_fast(L[y0:y1], R[y0:y1], block, 0, D, 1.0, cost=ocost, rows=(mid - y0, mid - y0 + rows))
+    return time.perf_counter() - t0
+
+
+def run_reference(args, rank, world):
+    """The reference's own CPU algorithm for the path (oracle/: box-sum + OpenMP restatement of
+    BlockSearch::computeDisparityMapRight, bit-identical to the literal loop) on all host cores.
+    The reference binary itself cannot be built here (OpenCV C++/Eigen/Ceres absent), see DESIGN.md."""
+    if rank != 0:
+        return
+    from oracle import orc
+    from stereo_reconstruction_b200 import synth
+    w, h, D, block, cost = WORKLOADS[args.workload]
+    cost = args.cost or cost
+    block = args.block or block
+    L, R = orc.synth_pair(0xB200, 0, w, h, 0, D)
+    ocost = orc.COST_SAD if cost == "sad" else orc.COST_SSD_L2
+    cores = os.cpu_count() or 1
+    mid = block
+    unit = 16 * cores                                            # the port parallelises over 16-row chunks
+    cal = min(unit, h - 2 * block)
+    _oracle_sample(orc, L, R, block, D, ocost, mid, 2)
+    per_row = _oracle_sample(orc, L, R, block, D, ocost, mid, cal) / cal
+    budget = 150.0 / max(args.steps + args.warmup, 1)            # whole run within a few minutes
+    rows = int(min(3.0, budget) / max(per_row, 1e-6))
+    rows = max(min(cal, h - 2 * block), min(h - 2 * block, (rows // unit) * unit))
+    for _ in range(args.warmup):
+        _oracle_sample(orc, L, R, block, D, ocost, mid, rows)
+    ts = [_oracle_sample(orc, L, R, block, D, ocost, mid, rows) for _ in range(args.steps)]
+    ev = synth.effective_evals(w, w, rows, block, 0, D)
+    sec = float(np.mean(ts))
+    val = ev / sec / 1e6
+    sample = f"{rows} of {h} rows of the {w}x{h} pair per step (rows {mid}..{mid + rows}), {cost.upper()} {block}x{block}, D={D}"
+    line = {"impl": "reference", "metric": "disparity_evals_per_s", "value": val, "unit": "MDE/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: synthetic {w}x{h} pair, {D} disparities, {block}x{block} {cost.upper()}",
+                       "sample": sample},
+            "cpu_baseline": {"value": val, "unit": "MDE/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "MDE/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(args, L, R, w, h, D, block, cost):
+    from oracle import orc
+    from stereo_reconstruction_b200 import synth
+    ocost = orc.COST_SAD if cost == "sad" else orc.COST_SSD_L2
+    mid = block
+    unit = 16 * (os.cpu_count() or 1)                            # the port parallelises over 16-row chunks
+    cal = min(unit, h - 2 * block)
+    _oracle_sample(orc, L, R, block, D, ocost, mid, 2)
+    per_row = _oracle_sample(orc, L, R, block, D, ocost, mid, cal) / cal
+    rows = int(args.cpu_seconds / max(per_row, 1e-6))
+    rows = max(min(cal, h - 2 * block), min(h - 2 * block, (rows // unit) * unit))
+    sec = _oracle_sample(orc, L, R, block, D, ocost, mid, rows)
+    reps = 1
+    while sec * reps < 0.8 * args.cpu_seconds and reps < 64:      # small workloads: repeat the sample
+        sec = (sec * reps + _oracle_sample(orc, L, R, block, D, ocost, mid, rows)) / (reps + 1)
+        reps += 1
+    ev = synth.effective_evals(w, w, rows, block, 0, D)
+    return {"value": ev / sec / 1e6, "unit": "MDE/s", "cores": os.cpu_count() or 1, "kind": "port",
+            "sample": f"rows {mid}..{mid + rows} of the same pair ({rows}/{h} rows, {reps} x {sec:.2f} s), box-sum + OpenMP port of "
+                      f"BlockSearch::computeDisparityMapRight, all host threads"}
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    import torch
+    import torch.distributed as dist
+    import stereo_reconstruction_b200 as s
+    from stereo_reconstruction_b200 import sharding, synth
+    capi = s.capi
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    w, h, D, block, cost = WORKLOADS[args.workload]
+    cost = args.cost or cost
+    block = args.block or block
+    ctx = capi.Context(local_rank)
+    ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
+
+    L, R = synth.synth_pair(0xB200, 0, w, h, 0, D)
+    # pinned host copies for the end-to-end leg
+    Lp, lp_h = capi.pinned_empty(L.shape, np.uint8); Lp[...] = L
+    Rp, rp_h = capi.pinned_empty(R.shape, np.uint8); Rp[...] = R
+    outp, out_h = capi.pinned_empty((h, w), np.float64)
+    params = capi.search_params(block=block, min_disp=0, max_disp=D, smooth=1.0,
+                                cost=capi.COST_SAD if cost == "sad" else capi.COST_SSD_L2)
+    pair = capi.Pair(ctx, w, h, w, h)
+    pair.upload(Lp, Rp)
+    r0, r1 = sharding.band_rows(h, rank, world)
+    full = sharding.result_tensor(pair, dev)
+    total_evals = synth.effective_evals(w, w, h, block, 0, D)
+
+    def barrier():
+        ctx.sync()
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+
+    def step_resident():
+        pair.run(params, r0, r1)
+        if world > 1:
+            with torch.cuda.stream(ext):
+                sharding.gather_bands(full, h, rank, world)
+
+    def step_e2e():
+        if world == 1:
+            capi.block_search(ctx, Lp, Rp, params, out=outp)          # sr_block_search: H2D + kernels + D2H
+        else:
+            pair.upload(Lp, Rp)
+            pair.run(params, r0, r1)
+            with torch.cuda.stream(ext):
+                sharding.gather_bands(full, h, rank, world)
+            if rank == 0:
+                pair.download(params, out=outp)
+            ctx.sync()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    peak_dual, peak_single = ctx.int_peak()
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    launches0 = ctx.launches
+    barrier()
+    step_ms, kern_ms = [], []
+    for _ in range(args.steps):
+        ctx.l2_flush()                       # between timed iterations: write 384 MB > 126 MB L2
+        ctx.timer_start()
+        step_resident()
+        step_ms.append(ctx.timer_stop())
+        if ctx.last_kernel == "tile":
+            kern_ms.append(ctx.search_kernel_ms())
+    barrier()
+    launches = ctx.launches - launches0 - args.steps * 0   # memset of the flush is not a kernel of ours
+    t_total = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_total, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t_total.item()) / args.steps
+
+    # end to end through the host-pointer API
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    e2e_t = []
+    for _ in range(max(3, min(args.steps, 10))):
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        step_e2e()
+        e2e_t.append(time.perf_counter() - t0)
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    t_e2e = torch.tensor([float(np.mean(e2e_t))], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+    e2e_s = float(t_e2e.item())
+
+    # parity spot check against nothing here (tests do that); report result checksum for reproducibility
+    if rank == 0:
+        res = pair.download(params)
+        checksum = float(res.sum())
+        band_evals = synth.effective_evals(w, w, r1 - r0, block, 0, D)
+        k_ms = float(np.mean(kern_ms)) if kern_ms else None
+        ops = OPS_PER_EVAL[cost]
+        roofline = None
+        if k_ms:
+            achieved = band_evals * ops / (k_ms * 1e-3) / 1e12
+            in_bytes = 2 * w * (r1 - r0) * 3 + w * (r1 - r0) * 8   # algorithmic: BGR in (both images) + CV_64F out
+            roofline = {"bound": "alu", "achieved": achieved, "peak": peak_dual / 1e12, "unit": "Tint-op/s",
+                        "frac": achieved / (peak_dual / 1e12),
+                        "traffic": NCU_TRAFFIC.get(args.workload),
+                        "kernel": "search_tile_kernel", "kernel_ms": k_ms, "ops_per_eval": ops,
+                        "evals_per_launch": band_evals, "kernel_MDE_per_s": band_evals / (k_ms * 1e-3) / 1e6,
+                        "peak_source": "measured live: VABSDIFF4+IDP.4A dual-pipe issue (sr_int_peak)",
+                        "peak_single_pipe": peak_single / 1e12, "frac_of_single_pipe": achieved / (peak_single / 1e12),
+                        "hbm": {"algorithmic_GBps": in_bytes / (k_ms * 1e-3) / 1e9, "peak_GBps": 6547.2,
+                                "note": "14 B/pixel algorithmic; the kernel is ALU-bound (SURVEY.md 8d)"}}
+        line = {
+            "metric": "disparity_evals_per_s", "value": total_evals / (ms_per_step * 1e-3) / 1e6, "unit": "MDE/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: synthetic {w}x{h} rectified pair, {D} disparities, {block}x{block} "
+                                   f"{cost.upper()}, smooth 1.0 (BASELINE.json configs)",
+                       "sharding": "row bands + NCCL gather to rank 0" if world > 1 else "single GPU",
+                       "l2": "384 MB written between timed iterations", "evals": "effective (reference break rule)",
+                       "nominal_MDE": w * h * D / 1e6, "effective_MDE": total_evals / 1e6},
+            "pairs_per_s": 1e3 / ms_per_step,
+            "nominal_value": w * h * D / (ms_per_step * 1e-3) / 1e6,
+            "e2e": {"value": total_evals / e2e_s / 1e6, "unit": "MDE/s", "ms_per_step": e2e_s * 1e3,
+                    "h2d_bytes_per_step": int(2 * w * h * 3 * world), "d2h_bytes_per_step": int(w * h * 8),
+                    "api": "sr_block_search (pinned host buffers)" if world == 1 else "sr_pair_upload + sr_search_run(band) + NCCL gather + sr_search_download"},
+            "gpu_launches": int(launches),
+            "kernel_family": ctx.last_kernel,
+            "clocks": clocks,
+            "roofline": roofline,
+            "result_checksum": checksum,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args, L, R, w, h, D, block, cost)
+        print(json.dumps(line), flush=True)
+    barrier()
+    capi.free_pinned(lp_h); capi.free_pinned(rp_h); capi.free_pinned(out_h)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

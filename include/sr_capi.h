@@ -84,6 +84,12 @@ void* sr_ctx_stream(sr_ctx* ctx);
 int sr_ctx_sync(sr_ctx* ctx);
 int sr_timer_start(sr_ctx* ctx);
 int sr_timer_stop(sr_ctx* ctx, float* ms);          /* records, synchronises, returns elapsed ms */
+/* Measurement helpers (bench.py): write a buffer larger than L2 on the context stream; device time
+ * of the dominant search kernel of the last sr_search_run; live integer-issue peak in lane-ops/s
+ * (dual = VABSDIFF4 + IDP.4A on both pipes, single = INT pipe alone). */
+int sr_l2_flush(sr_ctx* ctx);
+int sr_search_kernel_ms(sr_ctx* ctx, float* ms);
+int sr_int_peak(sr_ctx* ctx, double* dual_ops_per_s, double* single_ops_per_s);
 /* Number of kernels this library launched on ctx since creation. */
 uint64_t sr_kernel_launches(const sr_ctx* ctx);
 /* Name of the search kernel family the last sr_search_* call dispatched to
@@ -174,16 +180,10 @@ int sr_evaldisp(sr_ctx* ctx, const float* disp, const float* gt, const uint8_t* 
 int sr_write_pfm(const char* path, const float* data, int w, int h);
 int sr_write_ply(const char* path, const sr_vertex* v, int w, int h);
 
-/* ---- multi-GPU: row bands gathered to rank 0 over NCCL (config 4) -------------------------- */
-/* unique_id: 128 bytes from sr_comm_unique_id on rank 0, distributed by the caller. */
-int sr_comm_unique_id(void* id128);
-int sr_comm_init(sr_ctx* ctx, int rank, int nranks, const void* id128);
-int sr_comm_destroy(sr_ctx* ctx);
-/* Balanced band of output rows for `rank` of `nranks` (by effective evaluations). */
+/* ---- multi-GPU (config 4) ------------------------------------------------------------------ */
+/* Balanced band of output rows for `rank` of `nranks`.  Ranks run sr_search_run on their band and
+ * the caller gathers the bands to rank 0 over NCCL (stereo_reconstruction_b200/sharding.py). */
 int sr_band_rows(int h, int rank, int nranks, int* row0, int* row1);
-/* Every rank computes its band of the same pair; bands are gathered into rank 0's result
- * buffer with grouped ncclSend/ncclRecv.  Asynchronous on the context stream. */
-int sr_search_run_banded(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p);
 
 #ifdef __cplusplus
 }

@@ -51,8 +51,8 @@ SYMBOLS = [
     "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block",
     "sr_search_effective_evals", "sr_remove_outliers", "sr_box_blur", "sr_scale", "sr_disparity_to_depth",
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
-    "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_comm_unique_id", "sr_comm_init",
-    "sr_comm_destroy", "sr_band_rows", "sr_search_run_banded",
+    "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
+    "sr_search_kernel_ms", "sr_int_peak",
 ]
 
 _lib = None
@@ -141,6 +141,24 @@ class Context:
         self.check(self._l.sr_timer_stop(self.h, C.byref(ms)))
         return ms.value
 
+    def l2_flush(self):
+        self.check(self._l.sr_l2_flush(self.h))
+
+    def search_kernel_ms(self):
+        ms = C.c_float()
+        self.check(self._l.sr_search_kernel_ms(self.h, C.byref(ms)))
+        return ms.value
+
+    def int_peak(self):
+        """(dual-pipe, single-pipe) measured integer issue peaks in lane-ops/s."""
+        a, b = C.c_double(), C.c_double()
+        self.check(self._l.sr_int_peak(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    @property
+    def stream(self):
+        return int(self._l.sr_ctx_stream(self.h))
+
 
 _default_ctx = {}
 
@@ -200,8 +218,9 @@ class Pair:
             row1 = self.h1 if params.variant == VARIANT_LEFT else self.h2
         self.ctx.check(self.ctx._l.sr_search_run(self.ctx.h, self.h, C.byref(params), int(row0), int(row1)))
 
-    def run_banded(self, params):
-        self.ctx.check(self.ctx._l.sr_search_run_banded(self.ctx.h, self.h, C.byref(params)))
+    def result_ptr(self):
+        """Device pointer of the CV_64F result (tight rows of the output width)."""
+        return int(self.ctx._l.sr_search_result_dev(self.ctx.h, self.h))
 
     def download(self, params, out=None, row0=0, row1=None):
         oh, ow = (self.h1, self.w1) if params.variant == VARIANT_LEFT else (self.h2, self.w2)
@@ -222,6 +241,14 @@ class Pair:
         v = C.c_uint64()
         self.ctx.check(self.ctx._l.sr_search_effective_evals(self.ctx.h, self.h, C.byref(v)))
         return int(v.value)
+
+
+def band_rows(h, rank, nranks):
+    r0, r1 = C.c_int(), C.c_int()
+    rc = lib().sr_band_rows(int(h), int(rank), int(nranks), C.byref(r0), C.byref(r1))
+    if rc != OK:
+        raise SrError(rc, "sr_band_rows: bad arguments")
+    return r0.value, r1.value
 
 
 def search_params(variant=VARIANT_RIGHT, block=17, min_disp=0, max_disp=200, smooth=1.0, var_block=False,

@@ -88,7 +88,9 @@ int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row
         rc = sr_launch_resolve_right(ctx, pair, g, p->smooth, 1, 1);
     }
     if (rc != SR_OK) return rc;
-    return sr_launch_count_evals(ctx, pair, g) == SR_OK ? (pair->evals_valid = true, SR_OK) : SR_E_CUDA;
+    pair->last_geom = g;
+    pair->evals_valid = true;  // counted on demand (sr_search_effective_evals)
+    return SR_OK;
 }
 
 void* sr_search_result_dev(sr_ctx* ctx, sr_pair* pair) { return pair ? (void*)pair->out : nullptr; }
@@ -134,6 +136,8 @@ int sr_search_max_block(sr_ctx* ctx, sr_pair* pair, int* max_block) {
 int sr_search_effective_evals(sr_ctx* ctx, sr_pair* pair, uint64_t* evals) {
     if (!ctx || !pair || !evals) return SR_E_BADARG;
     if (!pair->evals_valid) return sr_fail(ctx, SR_E_BADARG, "no evaluation count for the last run");
+    int rc = sr_launch_count_evals(ctx, pair, pair->last_geom);
+    if (rc != SR_OK) return rc;
     SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     unsigned long long v = 0;
     SR_CUDA(ctx, cudaMemcpy(&v, pair->evals, 8, cudaMemcpyDeviceToHost));

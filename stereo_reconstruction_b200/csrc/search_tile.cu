@@ -272,8 +272,11 @@ int launch(sr_ctx* ctx, const TileArgs& a, int ntx, int nbands) {
         SR_CUDA(ctx, cudaFuncSetAttribute(search_tile_kernel<H2, COST, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = true;
     }
+    SR_CUDA(ctx, cudaEventRecord(ctx->kev0, ctx->stream));
     search_tile_kernel<H2, COST, NW><<<dim3(ntx, nbands, a.npass), NW * 32, smem, ctx->stream>>>(a);
     SR_LAUNCHED(ctx);
+    SR_CUDA(ctx, cudaEventRecord(ctx->kev1, ctx->stream));
+    ctx->kev_valid = true;
     return 1;
 }
 

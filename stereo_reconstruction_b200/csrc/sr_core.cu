@@ -65,7 +65,8 @@ int sr_ctx_create(int device, sr_ctx** out) {
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&c->aux[0], cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&c->aux[1], cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess) {
+        (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
+        (e = cudaEventCreate(&c->kev0)) != cudaSuccess || (e = cudaEventCreate(&c->kev1)) != cudaSuccess) {
         int rc = sr_cuda_check(nullptr, e, "stream/event creation");
         delete c;
         return rc;
@@ -80,11 +81,12 @@ void sr_ctx_destroy(sr_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (sr_pair* p : ctx->batch_pairs) sr_pair_destroy(ctx, p);
     ctx->batch_pairs.clear();
-    sr_comm_destroy(ctx);
     for (auto& b : ctx->scratch) if (b.p) cudaFree(b.p);
     for (auto& p : ctx->pinned) if (p) cudaFreeHost(p);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
+    cudaEventDestroy(ctx->kev0);
+    cudaEventDestroy(ctx->kev1);
     cudaStreamDestroy(ctx->aux[0]);
     cudaStreamDestroy(ctx->aux[1]);
     cudaStreamDestroy(ctx->stream);

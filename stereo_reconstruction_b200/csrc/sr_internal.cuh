@@ -21,6 +21,8 @@ struct sr_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t aux[2] = {nullptr, nullptr};  // copy streams of the batch pipeline
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t kev0 = nullptr, kev1 = nullptr;  // around the dominant search kernel of the last run
+    bool kev_valid = false;
     std::string err;
     uint64_t launches = 0;
     const char* last_kernel = "";
@@ -39,6 +41,13 @@ struct PackedImage {
     uint32_t* px = nullptr;    // pointer to pixel (0,0)
     int w = 0, h = 0;
     int pitch = 0;             // pixels per row (multiple of 32)
+};
+
+struct SearchGeom {
+    int w1, h1, w2, h2, height;  // height = min(h1,h2)
+    int block, half;             // blockSize_ and (block-1)/2
+    int dlo, dhi;                // candidate range [dlo, dhi)
+    int row0, row1;              // output rows to compute
 };
 
 struct sr_pair {
@@ -64,6 +73,7 @@ struct sr_pair {
     size_t npx_cap = 0;
     int last_row0 = 0, last_row1 = 0;
     bool evals_valid = false;
+    SearchGeom last_geom;
 };
 
 int sr_fail(sr_ctx* ctx, int code, const char* fmt, ...);
@@ -88,12 +98,6 @@ static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 // ---- launchers implemented in the .cu files (all asynchronous on ctx->stream) ----
 int sr_launch_pack(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int h, PackedImage* img);
 
-struct SearchGeom {
-    int w1, h1, w2, h2, height;  // height = min(h1,h2)
-    int block, half;             // blockSize_ and (block-1)/2
-    int dlo, dhi;                // candidate range [dlo, dhi)
-    int row0, row1;              // output rows to compute
-};
 // Fast path: fixed window, SSD/SAD, first minimum over [dlo,dhi) -> pair->best.
 // Returns 1 when it handled the request, 0 when the shape is not supported (caller falls back).
 int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref);

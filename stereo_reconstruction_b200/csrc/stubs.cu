@@ -5,6 +5,12 @@ int sr_launch_search_left(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, d
 int sr_launch_search_linear(sr_ctx* ctx, sr_pair* pair, double smooth) { NOTYET(ctx, "linear variant"); }
 int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1) { NOTYET(ctx, "extension costs"); }
 extern "C" {
+int sr_band_rows(int h, int rank, int nranks, int* row0, int* row1) {
+    if (h < 0 || nranks < 1 || rank < 0 || rank >= nranks || !row0 || !row1) return SR_E_BADARG;
+    *row0 = (int)((long long)h * rank / nranks);
+    *row1 = (int)((long long)h * (rank + 1) / nranks);
+    return SR_OK;
+}
 int sr_block_search_batch(sr_ctx* ctx, int n, const sr_image* left, const sr_image* right, const sr_search_params* p, double* const* disp_out, size_t out_pitch) { NOTYET(ctx, "sr_block_search_batch"); }
 int sr_remove_outliers(sr_ctx* ctx, float* disp, int w, int h, size_t pitch, int ksize, float thr_front, float thr_back) { NOTYET(ctx, "sr_remove_outliers"); }
 int sr_box_blur(sr_ctx* ctx, const float* src, float* dst, int w, int h, int ksize) { NOTYET(ctx, "sr_box_blur"); }
@@ -19,9 +25,4 @@ int sr_warp_nearest_f64(sr_ctx* ctx, const double* src, int sw, int sh, double* 
 int sr_evaldisp(sr_ctx* ctx, const float* disp, const float* gt, const uint8_t* mask, int w, int h, float badthresh, float maxdisp, int rounddisp, sr_eval* out) { NOTYET(ctx, "sr_evaldisp"); }
 int sr_write_pfm(const char* path, const float* data, int w, int h) { return SR_E_IO; }
 int sr_write_ply(const char* path, const sr_vertex* v, int w, int h) { return SR_E_IO; }
-int sr_comm_unique_id(void* id128) { return SR_E_NCCL; }
-int sr_comm_init(sr_ctx* ctx, int rank, int nranks, const void* id128) { NOTYET(ctx, "sr_comm_init"); }
-int sr_comm_destroy(sr_ctx* ctx) { return SR_OK; }
-int sr_band_rows(int h, int rank, int nranks, int* row0, int* row1) { return SR_E_BADARG; }
-int sr_search_run_banded(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p) { NOTYET(ctx, "sr_search_run_banded"); }
 }
