@@ -1,0 +1,80 @@
+// capi_batch.cu -- sr_block_search_batch: n independent pairs of one shape (config 5), pipelined
+// H2D + pack (copy stream 0) / search kernels (compute stream) / D2H (copy stream 1) over a ring
+// of device-resident pair objects.  With pinned host buffers the three stages overlap fully.
+#include "sr_internal.cuh"
+
+namespace {
+constexpr int NB = 3;  // pairs in flight
+struct StreamSwap {
+    sr_ctx* c; cudaStream_t saved;
+    StreamSwap(sr_ctx* ctx, cudaStream_t s) : c(ctx), saved(ctx->stream) { ctx->stream = s; }
+    ~StreamSwap() { c->stream = saved; }
+};
+}  // namespace
+
+extern "C" int sr_block_search_batch(sr_ctx* ctx, int n, const sr_image* left, const sr_image* right, const sr_search_params* p,
+                                     double* const* disp_out, size_t out_pitch) {
+    if (!ctx || !left || !right || !p || !disp_out || n < 0) return sr_fail(ctx, SR_E_BADARG, "sr_block_search_batch: bad argument");
+    if (n == 0) return SR_OK;
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    int w1 = left[0].w, h1 = left[0].h, w2 = right[0].w, h2 = right[0].h;
+    for (int i = 0; i < n; i++)
+        if (left[i].w != w1 || left[i].h != h1 || right[i].w != w2 || right[i].h != h2 || !left[i].bgr || !right[i].bgr || !disp_out[i])
+            return sr_fail(ctx, SR_E_BADARG, "sr_block_search_batch: pair %d has a different shape or a NULL buffer", i);
+    // ring of pair objects cached on the context
+    bool ok = (int)ctx->batch_pairs.size() >= NB;
+    for (sr_pair* q : ctx->batch_pairs) ok = ok && q->w1 == w1 && q->h1 == h1 && q->w2 == w2 && q->h2 == h2;
+    if (!ok) {
+        SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        for (sr_pair* q : ctx->batch_pairs) sr_pair_destroy(ctx, q);
+        ctx->batch_pairs.clear();
+        for (int i = 0; i < NB; i++) {
+            sr_pair* q = nullptr;
+            int rc = sr_pair_create(ctx, w1, h1, w2, h2, &q);
+            if (rc != SR_OK) return rc;
+            ctx->batch_pairs.push_back(q);
+        }
+    }
+    cudaEvent_t up[NB], comp[NB], down[NB];
+    for (int i = 0; i < NB; i++) {
+        SR_CUDA(ctx, cudaEventCreateWithFlags(&up[i], cudaEventDisableTiming));
+        SR_CUDA(ctx, cudaEventCreateWithFlags(&comp[i], cudaEventDisableTiming));
+        SR_CUDA(ctx, cudaEventCreateWithFlags(&down[i], cudaEventDisableTiming));
+    }
+    int oh = p->variant == SR_VARIANT_LEFT ? h1 : h2, ow = p->variant == SR_VARIANT_LEFT ? w1 : w2;
+    size_t rowb = (size_t)ow * sizeof(double);
+    int rc = SR_OK;
+    cudaStream_t compute = ctx->stream;
+    for (int i = 0; i < n && rc == SR_OK; i++) {
+        int s = i % NB;
+        sr_pair* pair = ctx->batch_pairs[s];
+        if (i >= NB) {  // the slot's previous search must be done with the images, its result downloaded
+            cudaStreamWaitEvent(ctx->aux[0], comp[s], 0);
+            cudaStreamWaitEvent(compute, down[s], 0);
+        }
+        {
+            StreamSwap sw(ctx, ctx->aux[0]);
+            rc = sr_pair_upload(ctx, pair, &left[i], &right[i]);
+        }
+        if (rc != SR_OK) break;
+        cudaEventRecord(up[s], ctx->aux[0]);
+        cudaStreamWaitEvent(compute, up[s], 0);
+        rc = sr_search_run(ctx, pair, p, 0, oh);
+        if (rc != SR_OK) break;
+        cudaEventRecord(comp[s], compute);
+        cudaStreamWaitEvent(ctx->aux[1], comp[s], 0);
+        if (out_pitch < rowb) { rc = sr_fail(ctx, SR_E_BADARG, "output pitch smaller than a row"); break; }
+        cudaError_t e = cudaMemcpy2DAsync(disp_out[i], out_pitch, pair->out, rowb, rowb, oh, cudaMemcpyDeviceToHost, ctx->aux[1]);
+        if (e != cudaSuccess) { rc = sr_cuda_check(ctx, e, "cudaMemcpy2DAsync(batch D2H)"); break; }
+        cudaEventRecord(down[s], ctx->aux[1]);
+    }
+    cudaStreamSynchronize(ctx->aux[0]);
+    cudaStreamSynchronize(compute);
+    cudaStreamSynchronize(ctx->aux[1]);
+    for (int i = 0; i < NB; i++) { cudaEventDestroy(up[i]); cudaEventDestroy(comp[i]); cudaEventDestroy(down[i]); }
+    if (rc == SR_OK) {
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) rc = sr_cuda_check(ctx, e, "batch pipeline");
+    }
+    return rc;
+}

@@ -1,0 +1,110 @@
+// misc.cu -- neighbours of the hot path: nearest-neighbour homography warp of the
+// CV_64F disparity map (rectification.cpp:82-87) and evaldisp (utils.cpp:123-168).
+#include <cmath>
+#include "sr_internal.cuh"
+
+// cv::warpPerspective(src, dst, M, size, INTER_NEAREST), constant-0 border: dst(x,y) =
+// src(rint(X/W), rint(Y/W)) with [X Y W] = M^-1 [x y 1], evaluated in double like OpenCV.
+__global__ void warp_nearest_kernel(const double* __restrict__ src, int sw, int sh, double* __restrict__ dst, int dw, int dh,
+                                    double m0, double m1, double m2, double m3, double m4, double m5, double m6, double m7,
+                                    double m8) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= dw) return;
+    double X = __dadd_rn(__dadd_rn(__dmul_rn(m0, x), __dmul_rn(m1, y)), m2);
+    double Y = __dadd_rn(__dadd_rn(__dmul_rn(m3, x), __dmul_rn(m4, y)), m5);
+    double W = __dadd_rn(__dadd_rn(__dmul_rn(m6, x), __dmul_rn(m7, y)), m8);
+    W = W != 0 ? __ddiv_rn(1.0, W) : 0;
+    double fx = fmax(-2147483648.0, fmin(2147483647.0, __dmul_rn(X, W)));
+    double fy = fmax(-2147483648.0, fmin(2147483647.0, __dmul_rn(Y, W)));
+    long long ix = __double2ll_rn(fx), iy = __double2ll_rn(fy);
+    dst[(size_t)y * dw + x] = (ix >= 0 && ix < sw && iy >= 0 && iy < sh) ? src[(size_t)iy * sw + ix] : 0.0;
+}
+
+static bool invert3(const double m[9], double o[9]) {
+    double c0 = m[4] * m[8] - m[5] * m[7], c1 = m[5] * m[6] - m[3] * m[8], c2 = m[3] * m[7] - m[4] * m[6];
+    double det = m[0] * c0 + m[1] * c1 + m[2] * c2;
+    if (det == 0) return false;
+    double id = 1.0 / det;
+    o[0] = c0 * id; o[1] = (m[2] * m[7] - m[1] * m[8]) * id; o[2] = (m[1] * m[5] - m[2] * m[4]) * id;
+    o[3] = c1 * id; o[4] = (m[0] * m[8] - m[2] * m[6]) * id; o[5] = (m[2] * m[3] - m[0] * m[5]) * id;
+    o[6] = c2 * id; o[7] = (m[1] * m[6] - m[0] * m[7]) * id; o[8] = (m[0] * m[4] - m[1] * m[3]) * id;
+    return true;
+}
+
+// evaldisp: one thread per pixel, integer counts by atomics, serr as a double sum
+__global__ void evaldisp_kernel(const float* __restrict__ disp, const float* __restrict__ gt, const uint8_t* __restrict__ mask,
+                                size_t n, float badthresh, float maxdisp, int rounddisp, int* __restrict__ counts,
+                                double* __restrict__ serr) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int cn = 0, cbad = 0, cinv = 0;
+    double e = 0;
+    if (i < n) {
+        float g = gt[i];
+        if (g != INFINITY && mask[i] == 255) {   // utils.cpp:139, :148
+            float d = disp[i];
+            bool valid = d != 0;
+            if (valid) d = fmaxf(0.0f, fminf(maxdisp, d));
+            if (valid && rounddisp) d = roundf(d);
+            float err = fabsf(d - g);
+            cn = 1;
+            if (valid) { e = (double)err; cbad = err > badthresh; } else cinv = 1;
+        }
+    }
+    for (int o = 16; o; o >>= 1) {
+        cn += __shfl_down_sync(0xffffffffu, cn, o);
+        cbad += __shfl_down_sync(0xffffffffu, cbad, o);
+        cinv += __shfl_down_sync(0xffffffffu, cinv, o);
+        e += __shfl_down_sync(0xffffffffu, e, o);
+    }
+    if ((threadIdx.x & 31) == 0 && cn) {
+        atomicAdd(counts, cn); atomicAdd(counts + 1, cbad); atomicAdd(counts + 2, cinv); atomicAdd(serr, e);
+    }
+}
+
+extern "C" {
+
+int sr_warp_nearest_f64(sr_ctx* ctx, const double* src, int sw, int sh, double* dst, int dw, int dh, const double M[9]) {
+    if (!ctx || !src || !dst || !M || sw <= 0 || sh <= 0 || dw <= 0 || dh <= 0) return sr_fail(ctx, SR_E_BADARG, "sr_warp_nearest_f64: bad argument");
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    double m[9];
+    if (!invert3(M, m)) for (double& v : m) v = 0;
+    double* ds = (double*)sr_scratch(ctx, 11, (size_t)sw * sh * 8);
+    double* dd = (double*)sr_scratch(ctx, 12, (size_t)dw * dh * 8);
+    if (!ds || !dd) return SR_E_CUDA;
+    SR_CUDA(ctx, cudaMemcpyAsync(ds, src, (size_t)sw * sh * 8, cudaMemcpyHostToDevice, ctx->stream));
+    warp_nearest_kernel<<<dim3(cdiv(dw, 128), dh), 128, 0, ctx->stream>>>(ds, sw, sh, dd, dw, dh, m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], m[8]);
+    SR_LAUNCHED(ctx);
+    SR_CUDA(ctx, cudaMemcpyAsync(dst, dd, (size_t)dw * dh * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    return sr_ctx_sync(ctx);
+}
+
+int sr_evaldisp(sr_ctx* ctx, const float* disp, const float* gt, const uint8_t* mask, int w, int h, float badthresh,
+                float maxdisp, int rounddisp, sr_eval* out) {
+    if (!ctx || !disp || !gt || !mask || !out || w <= 0 || h <= 0) return sr_fail(ctx, SR_E_BADARG, "sr_evaldisp: bad argument");
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    size_t n = (size_t)w * h;
+    float* dd = (float*)sr_scratch(ctx, 4, n * 4);
+    float* dg = (float*)sr_scratch(ctx, 5, n * 4);
+    uint8_t* dm = (uint8_t*)sr_scratch(ctx, 13, n + 64);
+    if (!dd || !dg || !dm) return SR_E_CUDA;
+    int* counts = (int*)(dm + ((n + 15) & ~(size_t)15));
+    double* serr = (double*)(counts + 4);
+    SR_CUDA(ctx, cudaMemcpyAsync(dd, disp, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    SR_CUDA(ctx, cudaMemcpyAsync(dg, gt, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    SR_CUDA(ctx, cudaMemcpyAsync(dm, mask, n, cudaMemcpyHostToDevice, ctx->stream));
+    SR_CUDA(ctx, cudaMemsetAsync(counts, 0, 32, ctx->stream));
+    evaldisp_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(dd, dg, dm, n, badthresh, maxdisp, rounddisp, counts, serr);
+    SR_LAUNCHED(ctx);
+    int c[4];
+    double s;
+    SR_CUDA(ctx, cudaMemcpyAsync(c, counts, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    SR_CUDA(ctx, cudaMemcpyAsync(&s, serr, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    out->n = c[0]; out->bad = c[1]; out->invalid = c[2]; out->serr = s;
+    out->bad_pct = (float)(100.0 * c[1] / c[0]); out->invalid_pct = (float)(100.0 * c[2] / c[0]);
+    out->total_bad_pct = (float)(100.0 * (c[1] + c[2]) / c[0]);
+    out->avg_err = (float)(s / (double)(c[0] - c[2]));
+    return SR_OK;
+}
+
+}  // extern "C"

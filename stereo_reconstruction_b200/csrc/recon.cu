@@ -1,0 +1,281 @@
+// recon.cu -- Reconstruction kernels (src/Reconstruction/reconstruction.cpp) on device buffers.
+// Every kernel is O(1) work per pixel and HBM-bound; arithmetic follows the reference's operation
+// order exactly (no FMA contraction: the library is compiled with --fmad=false; IEEE division
+// and square root are nvcc defaults), so results are bit-identical to the CPU code.
+#include "sr_internal.cuh"
+#include "recon.cuh"
+
+// cv::borderInterpolate(p, len, BORDER_REFLECT_101)
+__host__ __device__ static inline int reflect101(int p, int len) {
+    if ((unsigned)p < (unsigned)len) return p;
+    if (len == 1) return 0;
+    do {
+        if (p < 0) p = -p; else p = 2 * (len - 1) - p;
+    } while ((unsigned)p >= (unsigned)len);
+    return p;
+}
+
+// ---- cv::blur(32F, Size(k,k)) (reconstruction.cpp:8) ----------------------------------------------
+// OpenCV's box filter = RowSum<float,double> (first window summed left to right, then
+// s += new - old) followed by ColumnSum<double,float> (running column sums over k rows,
+// out = (float)(sum * 1/(k*k))).  Both are sequential double-precision recurrences; to stay
+// bit-exact for arbitrary float input the recurrences are kept and parallelised across the
+// other dimension: one thread per row for the horizontal pass, one per column for the vertical.
+__global__ void blur_rows_kernel(const float* __restrict__ src, int w, int h, int k, double* __restrict__ rows) {
+    int y = blockIdx.x * blockDim.x + threadIdx.x;
+    if (y >= h) return;
+    const float* s = src + (size_t)y * w;
+    double* o = rows + (size_t)y * w;
+    int a = k / 2;
+    double acc = 0;
+    for (int i = 0; i < k; i++) acc += (double)s[reflect101(i - a, w)];
+    o[0] = acc;
+    for (int x = 1; x < w; x++) {
+        acc += (double)s[reflect101(x + k - 1 - a, w)] - (double)s[reflect101(x - 1 - a, w)];
+        o[x] = acc;
+    }
+}
+
+__global__ void blur_cols_kernel(const double* __restrict__ rows, int w, int h, int k, float* __restrict__ dst) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= w) return;
+    int a = k / 2;
+    double scale = 1.0 / ((double)k * (double)k);
+    double sum = 0;
+    for (int i = 0; i < k - 1; i++) sum += rows[(size_t)reflect101(i - a, h) * w + x];
+    for (int y = 0; y < h; y++) {
+        double s0 = sum + rows[(size_t)reflect101(y - a + k - 1, h) * w + x];
+        dst[(size_t)y * w + x] = (float)(s0 * scale);
+        sum = s0 - rows[(size_t)reflect101(y - a, h) * w + x];
+    }
+}
+
+int recon_box_blur(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, int k) {
+    double* rows = (double*)sr_scratch(ctx, 1, (size_t)w * h * sizeof(double));
+    if (!rows) return SR_E_CUDA;
+    blur_rows_kernel<<<cdiv(h, 64), 64, 0, ctx->stream>>>(d_src, w, h, k, rows);
+    SR_LAUNCHED(ctx);
+    blur_cols_kernel<<<cdiv(w, 64), 64, 0, ctx->stream>>>(rows, w, h, k, d_dst);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
+// reconstruction.cpp:11-17
+__global__ void outlier_replace_kernel(float* __restrict__ disp, const float* __restrict__ blurred, size_t n,
+                                       float thr_front, float thr_back) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float d = disp[i], b = blurred[i];
+    if (d > thr_front * b || d < thr_back * b) disp[i] = b;
+}
+
+int recon_remove_outliers(sr_ctx* ctx, float* d_disp, int w, int h, int k, float thr_front, float thr_back) {
+    float* blurred = (float*)sr_scratch(ctx, 2, (size_t)w * h * sizeof(float));
+    if (!blurred) return SR_E_CUDA;
+    int rc = recon_box_blur(ctx, d_disp, blurred, w, h, k);
+    if (rc != SR_OK) return rc;
+    size_t n = (size_t)w * h;
+    outlier_replace_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_disp, blurred, n, thr_front, thr_back);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
+// reconstruction.cpp:21-27
+__global__ void scale_kernel(float* __restrict__ disp, size_t n, float f) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) disp[i] = f * disp[i];
+}
+int recon_scale(sr_ctx* ctx, float* d_disp, size_t n, float f) {
+    scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_disp, n, f);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
+// Fused disparity -> depth -> back-projected vertex (reconstruction.cpp:30-43 and :169-196).
+// depth = d == 0 ? -inf : (focal*baseline)/d;  x = (w*depth - cX*depth)/fX (two rounded products,
+// a rounded subtract, a rounded divide).  Either output may be NULL.  bgr: tight 3*w pitch.
+__global__ void depth_backproject_kernel(const float* __restrict__ disp, const float* __restrict__ depth_in,
+                                         const uint8_t* __restrict__ bgr, size_t bgr_pitch, int w, int h, float focal,
+                                         float baseline, float fx, float fy, float cx, float cy,
+                                         float* __restrict__ depth_out, sr_vertex* __restrict__ vert) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = blockIdx.y;
+    if (x >= w) return;
+    size_t i = (size_t)y * w + x;
+    float depth;
+    if (disp) {
+        float d = disp[i];
+        depth = d == 0.0f ? -INFINITY : focal * baseline / d;
+        if (depth_out) depth_out[i] = depth;
+    } else {
+        depth = depth_in[i];
+    }
+    if (!vert) return;
+    float4 pos;
+    uint32_t rgba;
+    if (depth == -INFINITY) {
+        pos = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        rgba = 0;
+    } else {
+        float xc = ((float)x * depth - cx * depth) / fx;
+        float yc = ((float)y * depth - cy * depth) / fy;
+        pos = make_float4(xc, yc, depth, 1.0f);
+        const uint8_t* p = bgr + (size_t)y * bgr_pitch + 3 * (size_t)x;
+        rgba = (uint32_t)p[2] | ((uint32_t)p[1] << 8) | ((uint32_t)p[0] << 16) | 0xFF000000u;
+    }
+    // 32-byte vertex: two 16-byte stores (position; colour + zeroed padding)
+    float4* o = reinterpret_cast<float4*>(vert + i);
+    o[0] = pos;
+    o[1] = make_float4(__uint_as_float(rgba), 0.f, 0.f, 0.f);
+}
+
+int recon_depth_backproject(sr_ctx* ctx, const float* d_disp, const float* d_depth_in, const uint8_t* d_bgr, size_t bgr_pitch,
+                            int w, int h, float focal, float baseline, float fx, float fy, float cx, float cy,
+                            float* d_depth_out, sr_vertex* d_vert) {
+    dim3 grid(cdiv(w, 128), h);
+    depth_backproject_kernel<<<grid, 128, 0, ctx->stream>>>(d_disp, d_depth_in, d_bgr, bgr_pitch, w, h, focal, baseline, fx, fy,
+                                                            cx, cy, d_depth_out, d_vert);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
+// ---- WriteMesh face list (reconstruction.cpp:46-69, :92-113) ----------------------------------------
+// Grid cells in row-major order, per cell the upper-left triangle (a,b,c) then the lower-right
+// (b,d,c).  Validity is embarrassingly parallel; the reference's face ORDER is kept with an
+// ordered stream compaction: per-block counts -> exclusive scan of block totals -> scatter.
+__device__ __forceinline__ float edge_len(const float4& a, const float4& b) {
+    float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z;
+    return sqrtf(dx * dx + dy * dy + dz * dz);  // powf(v,2) == v*v; sums left to right; no FMA
+}
+__device__ __forceinline__ bool tri_valid(const float4& a, const float4& b, const float4& c, float thr) {
+    if (a.x == -INFINITY || b.x == -INFINITY || c.x == -INFINITY) return false;
+    float l1 = edge_len(a, b), l2 = edge_len(a, c), l3 = edge_len(b, c);
+    return !(l1 > thr || l2 > thr || l3 > thr);
+}
+
+#define FACE_THREADS 256
+// flags of cell `cell`: bit0 = upper-left triangle valid, bit1 = lower-right valid
+__device__ __forceinline__ uint32_t cell_flags(const sr_vertex* __restrict__ v, int w, int h, unsigned cell, float thr) {
+    unsigned cw = (unsigned)(w - 1);
+    unsigned y = cell / cw, x = cell - y * cw;
+    const float4 pa = *reinterpret_cast<const float4*>(v + (size_t)y * w + x);
+    const float4 pb = *reinterpret_cast<const float4*>(v + (size_t)(y + 1) * w + x);
+    const float4 pc = *reinterpret_cast<const float4*>(v + (size_t)y * w + x + 1);
+    const float4 pd = *reinterpret_cast<const float4*>(v + (size_t)(y + 1) * w + x + 1);
+    return (tri_valid(pa, pb, pc, thr) ? 1u : 0u) | (tri_valid(pb, pd, pc, thr) ? 2u : 0u);
+}
+
+__global__ void __launch_bounds__(FACE_THREADS) face_count_kernel(const sr_vertex* __restrict__ v, int w, int h, float thr,
+                                                                  unsigned ncells, uint8_t* __restrict__ flags,
+                                                                  uint32_t* __restrict__ block_total) {
+    __shared__ uint32_t wsum[FACE_THREADS / 32];
+    unsigned cell = blockIdx.x * FACE_THREADS + threadIdx.x;
+    uint32_t f = cell < ncells ? cell_flags(v, w, h, cell, thr) : 0u;
+    if (cell < ncells) flags[cell] = (uint8_t)f;
+    uint32_t n = __popc(f);
+    for (int o = 16; o; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int i = 0; i < FACE_THREADS / 32; i++) t += wsum[i];
+        block_total[blockIdx.x] = t;
+    }
+}
+
+// single-CTA exclusive scan of the block totals (in place); total -> block_total[nblocks]
+__global__ void __launch_bounds__(1024) face_scan_kernel(uint32_t* __restrict__ block_total, unsigned nblocks) {
+    __shared__ uint32_t wsum[32];
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (unsigned base = 0; base < nblocks; base += 1024) {
+        unsigned i = base + threadIdx.x;
+        uint32_t v = i < nblocks ? block_total[i] : 0u;
+        uint32_t inc = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if ((threadIdx.x & 31) >= o) inc += t;
+        }
+        if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t s = wsum[threadIdx.x], si = s;
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t t = __shfl_up_sync(0xffffffffu, si, o);
+                if (threadIdx.x >= o) si += t;
+            }
+            wsum[threadIdx.x] = si - s;  // exclusive warp offsets
+        }
+        __syncthreads();
+        uint32_t excl = carry + wsum[threadIdx.x >> 5] + inc - v;
+        if (i < nblocks) block_total[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) block_total[nblocks] = carry;
+}
+
+__global__ void __launch_bounds__(FACE_THREADS) face_scatter_kernel(int w, unsigned ncells, const uint8_t* __restrict__ flags,
+                                                                    const uint32_t* __restrict__ block_off,
+                                                                    uint32_t* __restrict__ tri) {
+    __shared__ uint32_t wsum[FACE_THREADS / 32];
+    unsigned cell = blockIdx.x * FACE_THREADS + threadIdx.x;
+    uint32_t f = cell < ncells ? flags[cell] : 0u;
+    uint32_t n = __popc(f), inc = n;
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if ((threadIdx.x & 31) >= o) inc += t;
+    }
+    if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    uint32_t off = block_off[blockIdx.x] + inc - n;
+    for (int i = 0; i < (int)(threadIdx.x >> 5); i++) off += wsum[i];
+    if (!f) return;
+    unsigned cw = (unsigned)(w - 1);
+    unsigned y = cell / cw, x = cell - y * cw;
+    uint32_t a = y * w + x, b = (y + 1) * w + x, c = y * w + x + 1, d = (y + 1) * w + x + 1;
+    if (f & 1u) { tri[3 * (size_t)off] = a; tri[3 * (size_t)off + 1] = b; tri[3 * (size_t)off + 2] = c; off++; }
+    if (f & 2u) { tri[3 * (size_t)off] = b; tri[3 * (size_t)off + 1] = d; tri[3 * (size_t)off + 2] = c; }
+}
+
+int recon_mesh_faces(sr_ctx* ctx, const sr_vertex* d_vert, int w, int h, float thr, uint32_t* d_tri, uint32_t* n_faces) {
+    *n_faces = 0;
+    if (w < 2 || h < 2) return SR_OK;
+    unsigned ncells = (unsigned)(w - 1) * (unsigned)(h - 1);
+    unsigned nblocks = (ncells + FACE_THREADS - 1) / FACE_THREADS;
+    uint8_t* flags = (uint8_t*)sr_scratch(ctx, 3, (size_t)ncells + ((size_t)nblocks + 1) * 4 + 16);
+    if (!flags) return SR_E_CUDA;
+    uint32_t* block_total = (uint32_t*)(flags + (((size_t)ncells + 15) & ~(size_t)15));
+    face_count_kernel<<<nblocks, FACE_THREADS, 0, ctx->stream>>>(d_vert, w, h, thr, ncells, flags, block_total);
+    SR_LAUNCHED(ctx);
+    face_scan_kernel<<<1, 1024, 0, ctx->stream>>>(block_total, nblocks);
+    SR_LAUNCHED(ctx);
+    if (d_tri) {
+        face_scatter_kernel<<<nblocks, FACE_THREADS, 0, ctx->stream>>>(w, ncells, flags, block_total, d_tri);
+        SR_LAUNCHED(ctx);
+    }
+    SR_CUDA(ctx, cudaMemcpyAsync(n_faces, block_total + nblocks, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SR_OK;
+}
+
+// main.cpp:41-50: CV_64F -> 8-bit PNG (rint half-even, saturate) -> float32; or a plain cast.
+__global__ void quantize_kernel(const double* __restrict__ disp, float* __restrict__ out, size_t n, int quantize_u8) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double v = disp[i];
+    if (quantize_u8) {
+        long long q = (v != v) ? 0 : __double2ll_rn(fmax(-1e9, fmin(1e9, v)));
+        q = q < 0 ? 0 : (q > 255 ? 255 : q);
+        out[i] = (float)q;
+    } else {
+        out[i] = (float)v;
+    }
+}
+int recon_quantize(sr_ctx* ctx, const double* d_disp, float* d_out, size_t n, int quantize_u8) {
+    quantize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_disp, d_out, n, quantize_u8);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}

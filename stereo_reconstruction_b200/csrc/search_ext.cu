@@ -1,0 +1,219 @@
+// search_ext.cu -- extension searches (no reference counterpart; definitions of SURVEY.md 8c):
+// SAD / SSD (integer compare) / NCC (fp32) costs with the reference's window geometry, candidate
+// order, break rule and first-minimum rule; optional sub-pixel parabola fit; optional left-right
+// consistency check.  Output convention of the extensions: black / no-candidate pixels -> 0.
+//
+// SSD / SAD right-referenced searches reuse the fused tile kernel for the integer winner d*; the
+// two neighbouring costs of the parabola are then recomputed directly (O(window) per pixel).
+// NCC and the left-referenced (mirrored) search of the LR check run in the per-pixel direct kernel.
+#include <cmath>
+#include "sr_internal.cuh"
+
+struct WStats { long long sl, sr, sll, srr, slr, ssd, sad; };
+
+// stats over a ww x wh window; "l" = left-image sample, "q" = right-image sample
+__device__ __forceinline__ WStats window_stats(const uint32_t* __restrict__ Lp, int pitchL, int lx0,
+                                               const uint32_t* __restrict__ Rp, int pitchR, int rx0, int y0, int ww, int wh,
+                                               bool want_moments) {
+    WStats s = {0, 0, 0, 0, 0, 0, 0};
+    for (int r = 0; r < wh; r++) {
+        const uint32_t* lrow = Lp + (size_t)(y0 + r) * pitchL + lx0;
+        const uint32_t* rrow = Rp + (size_t)(y0 + r) * pitchR + rx0;
+        uint32_t sl = 0, sr = 0, sll = 0, srr = 0, slr = 0, ssd = 0, sad = 0;  // a row of < 2^14 pixels fits 32 bits
+        for (int i = 0; i < ww; i++) {
+            uint32_t l = __ldg(lrow + i), q = __ldg(rrow + i);
+            uint32_t ad = __vabsdiffu4(l, q);
+            ssd = __dp4a(ad, ad, ssd);
+            sad = __dp4a(ad, 0x01010101u, sad);
+            if (want_moments) {
+                sl = __dp4a(l, 0x01010101u, sl); sr = __dp4a(q, 0x01010101u, sr);
+                sll = __dp4a(l, l, sll); srr = __dp4a(q, q, srr); slr = __dp4a(l, q, slr);
+            }
+        }
+        s.sl += sl; s.sr += sr; s.sll += sll; s.srr += srr; s.slr += slr; s.ssd += ssd; s.sad += sad;
+    }
+    return s;
+}
+
+// NCC cost (fp32, fixed operation order): -num/sqrt(vl*vr), exact int64 moments scaled by n
+__device__ __forceinline__ float ncc_cost(const WStats& s, long long n) {
+    long long num = n * s.slr - s.sl * s.sr, vl = n * s.sll - s.sl * s.sl, vr = n * s.srr - s.sr * s.sr;
+    if (vl <= 0 || vr <= 0) return INFINITY;
+    float den = sqrtf(__fmul_rn(__ll2float_rn(vl), __ll2float_rn(vr)));
+    return -__fdiv_rn(__ll2float_rn(num), den);
+}
+
+__device__ __forceinline__ float parabola(float dsub, float cm, float c0, float cp) {
+    float den = __fadd_rn(__fsub_rn(cm, __fmul_rn(2.0f, c0)), cp);
+    if (den > 0.0f) dsub = __fadd_rn(dsub, __fdiv_rn(__fsub_rn(cm, cp), __fmul_rn(2.0f, den)));
+    return dsub;
+}
+
+struct ExtGeom {
+    int wr, hr, wo, ho;   // reference image (gets the disparities) and the other image
+    int height, half, dlo, dhi, left_ref, cost;
+    int row0;             // first output row of the launch (grid.y rows from here)
+};
+
+// Universal extension kernel: one thread per reference pixel.
+__global__ void __launch_bounds__(128) ext_direct_kernel(const uint32_t* __restrict__ Lp, int pitchL,
+                                                         const uint32_t* __restrict__ Rp, int pitchR, ExtGeom g,
+                                                         int* __restrict__ disp, float* __restrict__ subpix) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = g.row0 + blockIdx.y;
+    if (x >= g.wr) return;
+    size_t o = (size_t)y * g.wr + x;
+    int dbest = 0;
+    float dsub = 0.0f;
+    const uint32_t* refp = g.left_ref ? Lp : Rp;
+    int refpitch = g.left_ref ? pitchL : pitchR;
+    if (y < g.height && (__ldg(refp + (size_t)y * refpitch + x) & 0xFFFFFFu) != 0) {
+        int l = min(x, g.half), r = min(g.wr - x - 1, g.half), u = min(y, g.half), dn = min(g.hr - y - 1, g.half);
+        int ww = l + r, wh = u + dn;
+        long long n = (long long)ww * wh * 3;
+        int sgn = g.left_ref ? -1 : 1;
+        bool ncc = g.cost == SR_COST_NCC;
+        // running first minimum with its two neighbours (costs compared as double like the oracle)
+        double best = INFINITY, prev = INFINITY, cm = INFINITY, cp = INFINITY, c0 = INFINITY;
+        int bi = -1, k = 0;
+        bool want_next = false;
+        for (int d = g.dlo; d < g.dhi; d++, k++) {
+            int cx = x + sgn * d;
+            if (g.left_ref ? (cx - l < 0) : (cx + r >= g.wo)) break;
+            double c;
+            if (g.left_ref && cx + r > g.wo) c = INFINITY;       // partner window beyond the right image
+            else {
+                WStats s = g.left_ref ? window_stats(Lp, pitchL, x - l, Rp, pitchR, cx - l, y - u, ww, wh, ncc)
+                                      : window_stats(Lp, pitchL, cx - l, Rp, pitchR, x - l, y - u, ww, wh, ncc);
+                if (ncc) c = n ? (double)ncc_cost(s, n) : (double)INFINITY;
+                else c = (double)(g.cost == SR_COST_SAD ? s.sad : s.ssd);
+            }
+            if (want_next) { cp = c; want_next = false; }
+            if (c < best) { best = c; bi = k; cm = prev; c0 = c; cp = INFINITY; want_next = true; }
+            prev = c;
+        }
+        if (bi >= 0) {
+            dbest = g.dlo + bi;
+            dsub = (float)dbest;
+            // both neighbours evaluated and finite (bi >= 1 and bi+1 < nv in the oracle)
+            if (bi >= 1 && !want_next && isfinite(cm) && isfinite(cp)) dsub = parabola(dsub, (float)cm, (float)c0, (float)cp);
+        }
+    }
+    disp[o] = dbest;
+    if (subpix) subpix[o] = dsub;
+}
+
+// Winner from the tile kernel's key planes + direct recomputation of the parabola neighbours.
+__global__ void __launch_bounds__(128) ext_from_planes_kernel(const uint32_t* __restrict__ Lp, int pitchL,
+                                                              const uint32_t* __restrict__ Rp, int pitchR, ExtGeom g,
+                                                              const uint32_t* __restrict__ planes, size_t stride, int npass,
+                                                              int dbase, int want_subpix, int* __restrict__ disp,
+                                                              float* __restrict__ subpix) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = g.row0 + blockIdx.y;
+    if (x >= g.wr) return;
+    size_t o = (size_t)y * g.wr + x;
+    int dbest = 0;
+    float dsub = 0.0f;
+    if (y < g.height && (__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) != 0) {
+        uint32_t bc = 0xFFFFFFFFu; int bd = -1;
+        for (int p = 0; p < npass; p++) {
+            uint32_t k = __ldg(planes + (size_t)p * stride + o);
+            if (k != 0xFFFFFFFFu && (k >> 6) < bc) { bc = k >> 6; bd = dbase + 64 * p + (int)(k & 63u); }
+        }
+        if (bd >= 0) {
+            dbest = bd;
+            dsub = (float)bd;
+            if (want_subpix) {
+                int l = min(x, g.half), r = min(g.wr - x - 1, g.half), u = min(y, g.half), dn = min(g.hr - y - 1, g.half);
+                // candidates d*-1 and d*+1 must both exist: d*-1 >= dlo, d*+1 < dhi and before the break
+                if (bd - 1 >= g.dlo && bd + 1 < g.dhi && x + bd + 1 + r < g.wo) {
+                    WStats sm = window_stats(Lp, pitchL, x + bd - 1 - l, Rp, pitchR, x - l, y - u, l + r, u + dn, false);
+                    WStats sp = window_stats(Lp, pitchL, x + bd + 1 - l, Rp, pitchR, x - l, y - u, l + r, u + dn, false);
+                    long long cm = g.cost == SR_COST_SAD ? sm.sad : sm.ssd, cp = g.cost == SR_COST_SAD ? sp.sad : sp.ssd;
+                    dsub = parabola(dsub, __ll2float_rn(cm), __uint2float_rn(bc), __ll2float_rn(cp));
+                }
+            }
+        }
+    }
+    disp[o] = dbest;
+    if (subpix) subpix[o] = dsub;
+}
+
+// LR check + conversion to the CV_64F output map.
+__global__ void ext_finish_kernel(const int* __restrict__ disp_r, const float* __restrict__ subpix, int w2, int h2,
+                                  const int* __restrict__ disp_l, int w1, int h1, int row0, double* __restrict__ out) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = row0 + blockIdx.y;
+    if (x >= w2) return;
+    size_t o = (size_t)y * w2 + x;
+    int d = disp_r[o];
+    bool ok = true;
+    if (disp_l) {
+        int u = x + d;
+        int dl = (y < h1 && u >= 0 && u < w1) ? disp_l[(size_t)y * w1 + u] : 0x40000000;
+        ok = y < h1 && u >= 0 && u < w1 && abs(dl - d) <= 1;
+    }
+    out[o] = ok ? (subpix ? (double)subpix[o] : (double)d) : 0.0;
+}
+
+static int rows_fit_ext(int ho, int hr, int half) {
+    int height = ho < hr ? ho : hr;
+    for (int y = (height - half - 2 > 0 ? height - half - 2 : 0); y < height; y++) {
+        int down = hr - y - 1 < half ? hr - y - 1 : half;
+        if (y + down > ho) return 0;
+    }
+    return 1;
+}
+
+int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1) {
+    int w1 = pair->w1, h1 = pair->h1, w2 = pair->w2, h2 = pair->h2;
+    int half = (p->block - 1) / 2;
+    if (p->var_block) return sr_fail(ctx, SR_E_BADARG, "var_block is a reference-only option (SSD_L2 cost, no extensions)");
+    if (p->smooth != 1.0) return sr_fail(ctx, SR_E_BADARG, "the smoothing rule is defined for the reference cost only; extensions need smooth == 1");
+    if (!rows_fit_ext(h1, h2, half) || (p->lr_check && !rows_fit_ext(h2, h1, half)))
+        return sr_fail(ctx, SR_E_SHAPE, "image heights do not fit the window rows (h1=%d, h2=%d)", h1, h2);
+    row0 = row0 < 0 ? 0 : row0;
+    row1 = row1 > h2 ? h2 : row1;
+    if (p->lr_check && (row0 != 0 || row1 != h2)) return sr_fail(ctx, SR_E_BADARG, "lr_check needs the full image (no row bands)");
+    pair->ow = w2; pair->oh = h2; pair->last_row0 = row0; pair->last_row1 = row1;
+    int init[2] = {p->block, SR_OK};
+    SR_CUDA(ctx, cudaMemcpyAsync(pair->maxblock, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+    if (row1 <= row0) return SR_OK;
+    size_t npx = pair->npx_cap;
+    int* disp_r = (int*)sr_scratch(ctx, 14, npx * 4 * 2);
+    float* subpix = p->subpixel ? (float*)sr_scratch(ctx, 15, npx * 4) : nullptr;
+    if (!disp_r || (p->subpixel && !subpix)) return SR_E_CUDA;
+    int* disp_l = p->lr_check ? disp_r + npx : nullptr;
+    int dhi = p->max_disp, dlo = p->min_disp;
+    if (dhi < dlo) dhi = dlo;
+    ExtGeom g{w2, h2, w1, h1, h1 < h2 ? h1 : h2, half, dlo, dhi, 0, p->cost, row0};
+    bool tiled = false;
+    if (p->cost != SR_COST_NCC && half >= 1 && half <= 8 && w2 > 1 && h2 > 1) {
+        SearchGeom sg;
+        sg.w1 = w1; sg.h1 = h1; sg.w2 = w2; sg.h2 = h2; sg.height = g.height; sg.block = p->block; sg.half = half;
+        sg.dlo = dlo; sg.dhi = dhi > w1 ? w1 : dhi; if (sg.dhi < sg.dlo) sg.dhi = sg.dlo;
+        sg.row0 = row0; sg.row1 = row1;
+        int handled = sr_launch_search_tile(ctx, pair, sg, p->cost, 0);
+        if (handled < 0) return handled;
+        if (handled) {
+            tiled = true;
+            ext_from_planes_kernel<<<dim3(cdiv(w2, 128), row1 - row0), 128, 0, ctx->stream>>>(
+                pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, pair->planes, pair->npx_cap,
+                pair->npass, pair->plane_dbase, p->subpixel, disp_r, subpix);
+            SR_LAUNCHED(ctx);
+        }
+    }
+    if (!tiled) {
+        ext_direct_kernel<<<dim3(cdiv(w2, 128), row1 - row0), 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g,
+                                                                             disp_r, subpix);
+        SR_LAUNCHED(ctx);
+    }
+    ctx->last_kernel = tiled ? "tile+ext" : "ext-direct";
+    if (p->lr_check) {
+        ExtGeom gl{w1, h1, w2, h2, h1 < h2 ? h1 : h2, half, dlo, dhi, 1, p->cost, 0};
+        ext_direct_kernel<<<dim3(cdiv(w1, 128), h1), 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, gl,
+                                                                             disp_l, nullptr);
+        SR_LAUNCHED(ctx);
+    }
+    ext_finish_kernel<<<dim3(cdiv(w2, 128), row1 - row0), 128, 0, ctx->stream>>>(disp_r, subpix, w2, h2, disp_l, w1, h1, row0, pair->out);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}

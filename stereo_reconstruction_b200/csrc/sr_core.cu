@@ -213,7 +213,9 @@ static int upload_one(sr_ctx* ctx, const sr_image* im, uint8_t* raw, PackedImage
     if (pinned) {
         SR_CUDA(ctx, cudaMemcpy2DAsync(raw, row, im->bgr, im->pitch, row, im->h, cudaMemcpyHostToDevice, ctx->stream));
     } else {
-        // pageable source: stage through the context's pinned buffer (one memcpy, one DMA)
+        // pageable source: stage through the context's pinned buffer (one memcpy, one DMA);
+        // the buffer is reused, so the previous upload's DMA must have drained
+        SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         uint8_t* st = (uint8_t*)sr_pinned(ctx, slot, row * im->h);
         if (!st) return SR_E_CUDA;
         if (im->pitch == row) memcpy(st, im->bgr, row * im->h);
@@ -228,8 +230,6 @@ int sr_pair_upload(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_im
     if (left->w != pair->w1 || left->h != pair->h1 || right->w != pair->w2 || right->h != pair->h2)
         return sr_fail(ctx, SR_E_BADARG, "sr_pair_upload: image sizes differ from the pair's");
     SR_CUDA(ctx, cudaSetDevice(ctx->device));
-    // the staging buffers are reused: make sure the previous upload's DMA has drained
-    SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     int rc = upload_one(ctx, left, pair->rawL, &pair->L, 0);
     if (rc != SR_OK) return rc;
     return upload_one(ctx, right, pair->rawR, &pair->R, 1);

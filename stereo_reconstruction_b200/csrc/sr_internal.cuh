@@ -26,7 +26,7 @@ struct sr_ctx {
     std::string err;
     uint64_t launches = 0;
     const char* last_kernel = "";
-    DevBuf scratch[8];        // grow-only device scratch, reused across calls
+    DevBuf scratch[16];        // grow-only device scratch, reused across calls
     void* pinned[4] = {nullptr, nullptr, nullptr, nullptr};
     size_t pinned_cap[4] = {0, 0, 0, 0};
     std::vector<sr_pair*> batch_pairs;

@@ -1,0 +1,209 @@
+"""Parity of the remaining CUDA entry points (Left / Linear searches, extensions, Reconstruction,
+warp, evaldisp, batch API) with the CPU oracle and the cv2-executed golden vectors.  Integer,
+index and the reference's fp32/fp64 expressions: bit-exact.  NCC / sub-pixel: within 1e-3 px
+(north_star), and in fact compared bit-exact except where two NCC costs tie within 1e-6."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import golden_cases
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def sr():
+    import stereo_reconstruction_b200 as s
+    return s
+
+
+@pytest.fixture(scope="module")
+def ctx(sr):
+    return sr.capi.default_context()
+
+
+@pytest.mark.parametrize("name,z", golden_cases("left"), ids=lambda v: v if isinstance(v, str) else "")
+def test_left_golden(sr, ctx, name, z):
+    out = sr.BlockSearch(z["left"], z["right"], int(z["block"]), 0, int(z["max_d"]), ctx=ctx).computeDisparityMapLeft(float(z["smooth"]))
+    np.testing.assert_array_equal(out, z["out"])
+
+
+@pytest.mark.parametrize("smooth", [1.0, 0.9, 1.3])
+def test_left_vs_oracle(sr, ctx, orc, smooth):
+    L, R = orc.synth_pair(11, 0, 260, 70, 0, 30, True)   # quantised: many ties, the largest d must win
+    L[20:30, 100:120] = 0
+    want = orc.block_search_left(L, R, 7, 30, smooth)
+    got = sr.BlockSearch(L, R, 7, 0, 30, ctx=ctx).computeDisparityMapLeft(smooth)
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("name,z", golden_cases("linear"), ids=lambda v: v if isinstance(v, str) else "")
+def test_linear_golden(sr, ctx, name, z):
+    out = sr.LinearSearch(z["left"], z["right"], ctx=ctx).computeDisparityMap(float(z["smooth"]))
+    np.testing.assert_array_equal(out, z["out"])
+
+
+def test_linear_vs_oracle(sr, ctx, orc):
+    L, R = orc.synth_pair(5, 0, 500, 40, 0, 150)
+    for smooth in (1.0, 0.7):
+        np.testing.assert_array_equal(sr.LinearSearch(L, R, ctx=ctx).computeDisparityMap(smooth), orc.linear_search(L, R, smooth))
+
+
+# ---- extensions -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("cost", [0, 1])
+@pytest.mark.parametrize("block", [7, 9, 19])
+def test_ext_subpixel_int_costs(sr, ctx, orc, cost, block):
+    L, R = orc.synth_pair(21, 0, 520, 64, 0, 48)
+    R[5:9, 40:60] = 0
+    d, _, sp = orc.search_ext(L, R, block, 0, 48, cost, want_subpix=True)
+    got = sr.BlockSearch(L, R, block, 0, 48, cost=cost, ctx=ctx).computeDisparityMapRight(1.0, subpixel=True)
+    np.testing.assert_array_equal(got, sp.astype(np.float64))       # same fp32 expression: bit-exact
+    assert np.abs(got - sp).max() <= 1e-3
+
+
+def test_ext_ncc(sr, ctx, orc):
+    L, R = orc.synth_pair(22, 0, 300, 48, 0, 32)
+    d, _, sp = orc.search_ext(L, R, 7, 0, 32, orc.COST_NCC, want_subpix=True)
+    got = sr.BlockSearch(L, R, 7, 0, 32, cost=sr.capi.COST_NCC, ctx=ctx).computeDisparityMapRight(1.0)
+    assert (got != d).sum() == 0
+    gots = sr.BlockSearch(L, R, 7, 0, 32, cost=sr.capi.COST_NCC, ctx=ctx).computeDisparityMapRight(1.0, subpixel=True)
+    assert np.abs(gots - sp).max() <= 1e-3                          # north_star tolerance
+
+
+@pytest.mark.parametrize("cost", [0, 1, 2])
+def test_ext_lr_check(sr, ctx, orc, cost):
+    L, R = orc.synth_pair(23, 0, 280, 50, 0, 40)
+    dr, _, _ = orc.search_ext(L, R, 9, 0, 40, cost)
+    dl, _, _ = orc.search_ext(L, R, 9, 0, 40, cost, left_ref=True)
+    want = orc.lr_check(dr, dl)
+    got = sr.BlockSearch(L, R, 9, 0, 40, cost=cost, ctx=ctx).computeDisparityMapRight(1.0, lr_check=True)
+    np.testing.assert_array_equal(got, want.astype(np.float64))
+
+
+# ---- Reconstruction -----------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,z", golden_cases("outliers"), ids=lambda v: v if isinstance(v, str) else "")
+def test_outliers_golden(sr, ctx, name, z):
+    R = sr.reconstruction
+    np.testing.assert_array_equal(R.boxBlur(z["disp"], int(z["k"]), ctx=ctx), z["blur"])
+    d = np.array(z["disp"], dtype=np.float32)
+    R.removeDisparityOutliers(d, int(z["k"]), float(z["front"]), float(z["back"]), ctx=ctx)
+    np.testing.assert_array_equal(d, z["out"])
+
+
+def test_outliers_full_golden(sr, ctx):
+    (name, z), = golden_cases("outliers_full")
+    disp = z["disp_u8"].astype(np.float32)
+    d = disp.copy()
+    sr.reconstruction.removeDisparityOutliers(d, int(z["k"]), float(z["front"]), float(z["back"]), ctx=ctx)
+    np.testing.assert_array_equal(d[::25, ::25], z["out_sample"])
+    assert float(d.astype(np.float64).sum()) == float(z["out_sum"])
+    assert int((d != disp).sum()) == int(z["changed"])
+
+
+def _recon_inputs(orc, w=310, h=200):
+    rng = np.random.default_rng(9)
+    bgr = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    disp = rng.integers(0, 60, (h, w)).astype(np.float32)
+    disp[rng.random((h, w)) < 0.1] = 0            # invalid -> -inf depth
+    disp += (rng.random((h, w)) < 0.3) * rng.random((h, w)).astype(np.float32)
+    K = np.array([[1733.74, 0, 792.27], [0, 1733.74, 541.89], [0, 0, 1]], np.float32)
+    return bgr, disp.astype(np.float32), K
+
+
+def test_depth_backproject_faces(sr, ctx, orc):
+    R = sr.reconstruction
+    bgr, disp, K = _recon_inputs(orc)
+    h, w = disp.shape
+    s = disp.copy(); R.scaleDisparityMap(s, 1.7, ctx=ctx)
+    np.testing.assert_array_equal(s, orc.scale(disp, 1.7))
+    depth = R.convertDisparityToDepth(disp, K[0, 0], 1.0, ctx=ctx)
+    np.testing.assert_array_equal(depth, orc.disparity_to_depth(disp, K[0, 0], 1.0))
+    v = R.backproject(bgr, depth, K, ctx=ctx)
+    want_v = orc.backproject(bgr, depth, K[0, 0], K[1, 1], K[0, 2], K[1, 2])
+    assert v.tobytes() == want_v.tobytes()                          # 32-byte Vertex layout, bit for bit
+    for thr in (0.5, 5.0, 1e9):
+        np.testing.assert_array_equal(R.meshFaces(v, w, h, thr, ctx=ctx), orc.mesh_faces(want_v, w, h, thr))
+    assert R.CheckTriangularValidity(v, 0, w, 1, 1e9, ctx=ctx) == bool(orc.lib().orc_triangle_valid(
+        want_v.ctypes.data, 0, w, 1, __import__("ctypes").c_float(1e9)))
+
+
+def test_fused_pipeline_and_mesh_file(sr, ctx, orc, tmp_path):
+    R = sr.reconstruction
+    bgr, disp, K = _recon_inputs(orc, 180, 120)
+    h, w = disp.shape
+    got = R.reconstructFused(bgr, disp, K, K[0, 0], 1.0, kernelSize=31, thrFront=1.5, thrBack=0.8, thrMesh=3.0, ctx=ctx)
+    d = orc.remove_outliers(disp, 31, 1.5, 0.8)
+    depth = orc.disparity_to_depth(d, K[0, 0], 1.0)
+    v = orc.backproject(bgr, depth, K[0, 0], K[1, 1], K[0, 2], K[1, 2])
+    np.testing.assert_array_equal(got["disp"], d)
+    np.testing.assert_array_equal(got["depth"], depth)
+    assert got["vertices"].tobytes() == v.tobytes()
+    np.testing.assert_array_equal(got["faces"], orc.mesh_faces(v, w, h, 3.0))
+    a, b = tmp_path / "gpu.off", tmp_path / "cpu.off"
+    assert R.WriteMesh(got["vertices"], w, h, a, 3.0, ctx=ctx)
+    orc.write_off(str(b), v, w, h, 3.0)
+    assert a.read_bytes() == b.read_bytes()                         # byte-identical COFF text
+    assert R.WriteMesh(got["vertices"], w, h, tmp_path / "no_such_dir" / "x.off", 3.0, ctx=ctx) is False
+    R.writePFM(tmp_path / "g.pfm", got["disp"]); orc.write_pfm(str(tmp_path / "c.pfm"), d)
+    assert (tmp_path / "g.pfm").read_bytes() == (tmp_path / "c.pfm").read_bytes()
+    R.writePLY(tmp_path / "g.ply", got["vertices"], w, h); orc.write_ply(str(tmp_path / "c.ply"), v, w, h)
+    assert (tmp_path / "g.ply").read_bytes() == (tmp_path / "c.ply").read_bytes()
+
+
+def test_pair_reconstruct_device_resident(sr, ctx, orc):
+    """main.cpp:40-65 without a host round trip of the disparity map."""
+    L, Rr = orc.synth_pair(31, 0, 400, 90, 0, 60)
+    K = np.array([[500.0, 0, 200.0], [0, 500.0, 45.0], [0, 0, 1]], np.float32)
+    pair = sr.capi.Pair(ctx, 400, 90, 400, 90)
+    pair.upload(L, Rr)
+    p = sr.capi.search_params(block=17, min_disp=0, max_disp=60, smooth=0.9)
+    pair.run(p)
+    got = sr.reconstruction.pairReconstruct(pair, K, K[0, 0], 1.0, True, 25, 1.5, 0.8, 2.0)
+    disp64 = orc.block_search_right_fast(L, Rr, 17, 0, 60, 0.9)
+    d = orc.remove_outliers(orc.quantize_u8(disp64), 25, 1.5, 0.8)
+    depth = orc.disparity_to_depth(d, K[0, 0], 1.0)
+    v = orc.backproject(Rr, depth, K[0, 0], K[1, 1], K[0, 2], K[1, 2])
+    np.testing.assert_array_equal(got["disp"], d)
+    assert got["vertices"].tobytes() == v.tobytes()
+    np.testing.assert_array_equal(got["faces"], orc.mesh_faces(v, 400, 90, 2.0))
+
+
+def test_warp_and_quantize_golden(sr, ctx, orc):
+    (name, z), = golden_cases("warp")
+    out = sr.reconstruction.warpPerspectiveNearest(z["src"], z["M"], (int(z["dw"]), int(z["dh"])), ctx=ctx)
+    np.testing.assert_array_equal(out, z["out"])
+
+
+def test_evaldisp(sr, ctx, orc):
+    rng = np.random.default_rng(4)
+    h, w = 120, 200
+    gt = (rng.random((h, w)) * 60).astype(np.float32); gt[rng.random((h, w)) < 0.05] = np.inf
+    disp = (gt + rng.normal(0, 2, (h, w))).astype(np.float32); disp[~np.isfinite(disp)] = 3
+    disp[rng.random((h, w)) < 0.1] = 0
+    mask = np.where(rng.random((h, w)) < 0.8, 255, 128).astype(np.uint8)
+    for rd in (0, 1):
+        want = orc.evaldisp(disp, gt, mask, 2.0, 64.0, rd)
+        got = sr.reconstruction.evaldisp(disp, gt, mask, 2.0, 64.0, rd, ctx=ctx)
+        assert (got["n"], got["bad"], got["invalid"]) == (want.n, want.bad, want.invalid)   # counts exact
+        assert got["bad_pct"] == want.bad_pct and got["invalid_pct"] == want.invalid_pct
+        assert abs(got["avg_err"] - want.avg_err) <= 1e-4 * max(1.0, want.avg_err)           # float sum order differs
+
+
+def test_batch_api(sr, ctx, orc):
+    import ctypes as C
+    capi = sr.capi
+    n, w, h, D = 7, 384, 72, 48
+    pairs = [orc.synth_pair(0xB200, i, w, h, 0, D) for i in range(n)]
+    Ls = (capi.SrImage * n)(); Rs = (capi.SrImage * n)()
+    keep = []
+    outs = [np.zeros((h, w), np.float64) for _ in range(n)]
+    for i, (L, R) in enumerate(pairs):
+        la, li = capi.image(L); ra, ri = capi.image(R); keep += [la, ra]
+        Ls[i] = li; Rs[i] = ri
+    optrs = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
+    p = capi.search_params(block=7, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD, subpixel=True)
+    ctx.check(ctx._l.sr_block_search_batch(ctx.h, n, Ls, Rs, C.byref(p), optrs, C.c_size_t(w * 8)))
+    for i, (L, R) in enumerate(pairs):
+        _, _, sp = orc.search_ext(L, R, 7, 0, D, orc.COST_SAD, want_subpix=True)
+        np.testing.assert_array_equal(outs[i], sp.astype(np.float64))
