@@ -30,6 +30,10 @@ int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row
     if (rc != SR_OK) return rc;
     SR_CUDA(ctx, cudaSetDevice(ctx->device));
     pair->evals_valid = false;
+    {
+        int init0[2] = {p->block, SR_OK};   // "max block size" (BlockSearch.cpp:98) and the device status word
+        SR_CUDA(ctx, cudaMemcpyAsync(pair->maxblock, init0, sizeof init0, cudaMemcpyHostToDevice, ctx->stream));
+    }
     if (p->variant == SR_VARIANT_LEFT) {
         if (p->cost != SR_COST_SSD_L2 || p->subpixel || p->lr_check)
             return sr_fail(ctx, SR_E_BADARG, "the Left variant is reference-exact only (SSD, no extensions)");
