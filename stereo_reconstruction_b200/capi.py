@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsr_b200.so")
+LIB_PATH = os.environ.get("SR_B200_LIB") or os.path.join(_HERE, "libsr_b200.so")
 
 OK, E_BADARG, E_SHAPE, E_CUDA, E_NCCL, E_IO = 0, -1, -2, -3, -4, -5
 VARIANT_RIGHT, VARIANT_LEFT, VARIANT_LINEAR = 0, 1, 2

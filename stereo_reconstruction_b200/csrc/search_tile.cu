@@ -35,6 +35,10 @@ constexpr int LPOS = LCH + LCH / 4;
 constexpr int SLOT_U4 = RPOS + LPOS;  // uint4 per ring slot
 constexpr int KEY_U4 = 160;           // uint4 per warp key row (128 chunks padded)
 constexpr int PF = 2;                 // rows prefetched ahead
+#ifndef SR_TILE_FMA_FROM
+#define SR_TILE_FMA_FROM 2             // disparity pairs >= this index slide on the FMA pipe (4 = none)
+#endif
+constexpr int FMA_FROM = SR_TILE_FMA_FROM;
 
 __device__ __forceinline__ int padpos(int c) { return c + (c >> 2); }
 
@@ -57,18 +61,25 @@ __device__ __forceinline__ uint32_t pcost_add(uint32_t l, uint32_t r, uint32_t a
     return __dp4a(ad, ad, acc);
 }
 
+// 16-byte shared-memory load at a 32-bit byte offset from the dynamic shared base
+__device__ __forceinline__ uint4 lds128(uint32_t saddr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr));
+    return v;
+}
+
 // vertical update of the 64 column sums with one staged image row (ADD: row enters the window).
-// rs / ls: this lane's base inside the slot (right segment / left segment), lo[i]: warp-uniform
-// padded offsets of the 5 left chunks.
+// slot: shared address of the ring slot (warp-uniform); rb: this lane's byte offset inside the right
+// segment; lb[i]: byte offsets (lane base + warp-uniform chunk) of the 5 left chunks.
 template <int COST, bool ADD>
-__device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], const uint4* rs, const uint4* ls,
-                                                const int (&lo)[5], uint32_t colmask) {
-    uint4 la = ls[lo[0]];
+__device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], uint32_t slot, uint32_t rb,
+                                                const uint32_t (&lb)[5], uint32_t colmask) {
+    uint4 la = lds128(slot + lb[0]);
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        uint4 lb = ls[lo[k + 1]];
-        uint4 rr = rs[k];
-        uint32_t l7[7] = {la.x, la.y, la.z, la.w, lb.x, lb.y, lb.z};
+        uint4 lbv = lds128(slot + lb[k + 1]);
+        uint4 rr = lds128(slot + rb + 16 * k);
+        uint32_t l7[7] = {la.x, la.y, la.z, la.w, lbv.x, lbv.y, lbv.z};
         uint32_t r4[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
         for (int jj = 0; jj < 4; jj++)
@@ -77,7 +88,7 @@ __device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], const u
                 if (ADD) col[4 * k + jj][t] = pcost_add<COST>(l7[jj + t], r4[jj], col[4 * k + jj][t]);
                 else col[4 * k + jj][t] -= pcost_add<COST>(l7[jj + t], r4[jj], 0u);
             }
-        la = lb;
+        la = lbv;
     }
     if (colmask != 0xFFFFu) {
 #pragma unroll
@@ -102,42 +113,58 @@ struct TileArgs {
     int row0, row1;      // output rows (already clipped to min(h1,h2))
     int band;            // rows per CTA band
     uint32_t k64;        // == 64, passed as data so that key = S*64+d stays one IMAD (FMA pipe)
+    uint32_t kp1, km1;   // == 1, == 0xFFFFFFFF (-1): IMAD-based sliding sums
 };
 
-// horizontal window sums + in-thread WTA for one output row.  MASKED: candidates outside
+// horizontal window sums + in-thread WTA for one output row.  Disparities are processed in pairs so
+// that the two keys fold into one 3-input min (VIMNMX3).  The sliding update S += in - out of the
+// second pair runs as two IMADs (FMA pipe: multipliers kp1 = 1, km1 = -1 are kernel arguments so that
+// they are not strength-reduced) to balance the two integer pipes.  MASKED: candidates outside
 // [dlo, dlim(x)) are discarded (tiles that touch the break rule or the range ends).
 template <int H2, bool MASKED>
 __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32_t (&keys)[XT], uint32_t k64,
-                                           uint32_t dl0, int d0, int x0, const TileArgs& a) {
+                                           uint32_t kp1, uint32_t km1, uint32_t dl0, int d0, int x0, const TileArgs& a) {
     constexpr int HALO = H2 - 1;
 #pragma unroll
-    for (int t = 0; t < DT; t++) {
-        uint32_t win[XT + HALO];
+    for (int tp = 0; tp < DT; tp += 2) {
+        uint32_t w0[XT + HALO], w1[XT + HALO];
 #pragma unroll
-        for (int i = 0; i < XT; i++) win[i] = col[i][t];
+        for (int i = 0; i < XT; i++) { w0[i] = col[i][tp]; w1[i] = col[i][tp + 1]; }
 #pragma unroll
-        for (int i = 0; i < HALO; i++) win[XT + i] = __shfl_down_sync(0xffffffffu, col[i][t], 1);
-        uint32_t S = 0;
+        for (int i = 0; i < HALO; i++) {
+            w0[XT + i] = __shfl_down_sync(0xffffffffu, col[i][tp], 1);
+            w1[XT + i] = __shfl_down_sync(0xffffffffu, col[i][tp + 1], 1);
+        }
+        uint32_t S0 = 0, S1 = 0;
 #pragma unroll
-        for (int i = 0; i < H2; i++) S += win[i];
-        const uint32_t dl = dl0 + t;
+        for (int i = 0; i < H2; i++) { S0 += w0[i]; S1 += w1[i]; }
+        const uint32_t dla = dl0 + tp, dlb = dl0 + tp + 1;
 #pragma unroll
         for (int j = 0; j < XT; j++) {
-            uint32_t key = S * k64 + dl;
+            uint32_t ka = S0 * k64 + dla, kb = S1 * k64 + dlb;
             if (MASKED) {
-                int x = x0 + j, d = d0 + t;
+                int x = x0 + j;
                 int lim = min(a.dhi, a.w1 - x - min(a.w2 - x - 1, a.half));
-                if (d < a.dlo || d >= lim) key = 0xFFFFFFFFu;
+                if (d0 + tp < a.dlo || d0 + tp >= lim) ka = 0xFFFFFFFFu;
+                if (d0 + tp + 1 < a.dlo || d0 + tp + 1 >= lim) kb = 0xFFFFFFFFu;
             }
-            keys[j] = min(keys[j], key);
-            if (j + 1 < XT) S += win[j + H2] - win[j];
+            keys[j] = min(min(keys[j], ka), kb);
+            if (j + 1 < XT) {
+                if (tp >= FMA_FROM) {
+                    S0 = w0[j + H2] * kp1 + S0; S0 = w0[j] * km1 + S0;
+                    S1 = w1[j + H2] * kp1 + S1; S1 = w1[j] * km1 + S1;
+                } else {
+                    S0 += w0[j + H2] - w0[j];
+                    S1 += w1[j + H2] - w1[j];
+                }
+            }
         }
     }
 }
 
 template <int H2, int COST, int NW>
 __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
-    constexpr int NSLOT = H2 + PF;
+    constexpr int NSLOT = H2 + PF + 1;   // +1: half of the warps subtract the leaving row one iteration late
     static_assert(RCH + LCH <= NW * 32, "one staged chunk per thread");
     extern __shared__ __align__(128) uint4 smem4[];
     uint4* ring = smem4;                          // NSLOT x SLOT_U4
@@ -164,11 +191,14 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
         int x = cb + h + j;
         if (x >= 0 && x < a.w2) dlim_min = min(dlim_min, min(a.dhi, a.w1 - x - min(a.w2 - x - 1, h)));
     }
-    // lane bases inside a slot / key row (5 chunk positions per lane: 4 data + 1 pad)
+    // lane bases inside a slot / key row (5 chunk positions per lane: 4 data + 1 pad), as 32-bit
+    // shared-memory byte offsets: every hot-loop load is "uniform slot base + per-thread constant"
     const int lane_u4 = 5 * lane;
-    int lo[5];
+    const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem4);
+    const uint32_t rb = 16u * lane_u4;
+    uint32_t lb[5];
 #pragma unroll
-    for (int i = 0; i < 5; i++) lo[i] = padpos(warp + i);      // warp-uniform left-chunk offsets
+    for (int i = 0; i < 5; i++) lb[i] = 16u * (RPOS + lane_u4 + padpos(warp + i));
     const int y_start = yb0 - (H2 - 1);
     // this thread's chunk of every staged row (RCH + LCH <= NW*32 chunks per row)
     const int ld_dst = tid < RCH ? padpos(tid) : RPOS + padpos(tid - RCH);
@@ -182,6 +212,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
         const int d0 = dcta + DT * warp;                        // this warp's 4 disparities
         const int nactive = min(NW, (a.dhi - dcta + DT - 1) / DT);  // warps with at least one d < dhi
         const bool active = warp < nactive;
+        const bool late_sub = (warp >> 2) & 1;
         const bool needmask = __any_sync(0xffffffffu, d0 < a.dlo || d0 + DT - 1 >= dlim_min);
 
         uint32_t col[XT][DT];
@@ -227,25 +258,30 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
             issue_row(y + PF + h - 1);
             if (y - 1 >= yb0) reduce_row(y - 1);
             if (active) {
+                // Phase staggering: the warps of one scheduler alternate between "subtract now" and
+                // "subtract at the start of the next iteration", so that ALU-only phases (pointwise
+                // costs) of some warps overlap the FMA-heavy window/WTA phase of the others.
+                if (late_sub && y - 1 >= yb0 && row_ok(y - 1 - h) && colmask != 0) {
+                    const int sp = s_out == 0 ? NSLOT - 1 : s_out - 1;
+                    vertical_update<COST, false>(col, smem_base + (uint32_t)sp * (SLOT_U4 * 16), rb, lb, colmask);
+                }
                 const int rin = y + h - 1;
                 if (row_ok(rin) && colmask != 0) {
-                    const uint4* sl = ring + s_in * SLOT_U4 + lane_u4;
-                    vertical_update<COST, true>(col, sl, sl + RPOS, lo, colmask);
+                    vertical_update<COST, true>(col, smem_base + (uint32_t)s_in * (SLOT_U4 * 16), rb, lb, colmask);
                 }
                 if (y >= yb0) {
                     uint32_t keys[XT];
 #pragma unroll
                     for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
-                    if (needmask) window_wta<H2, true>(col, keys, k64, (uint32_t)(DT * warp), d0, cb + h, a);
-                    else window_wta<H2, false>(col, keys, k64, (uint32_t)(DT * warp), d0, cb + h, a);
+                    if (needmask) window_wta<H2, true>(col, keys, k64, a.kp1, a.km1, (uint32_t)(DT * warp), d0, cb + h, a);
+                    else window_wta<H2, false>(col, keys, k64, a.kp1, a.km1, (uint32_t)(DT * warp), d0, cb + h, a);
                     uint4* kw = keysm + ((y & 1) * NW + warp) * KEY_U4 + lane_u4;
 #pragma unroll
                     for (int k = 0; k < 4; k++)
                         kw[k] = make_uint4(keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
                     const int rout = y - h;
-                    if (y + 1 < yb1 && row_ok(rout) && colmask != 0) {
-                        const uint4* sl = ring + s_out * SLOT_U4 + lane_u4;
-                        vertical_update<COST, false>(col, sl, sl + RPOS, lo, colmask);
+                    if (!late_sub && y + 1 < yb1 && row_ok(rout) && colmask != 0) {
+                        vertical_update<COST, false>(col, smem_base + (uint32_t)s_out * (SLOT_U4 * 16), rb, lb, colmask);
                     }
                 }
             }
@@ -266,7 +302,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
 template <int H2, int COST>
 int launch(sr_ctx* ctx, const TileArgs& a, int ntx, int nbands) {
     constexpr int NW = 16;
-    size_t smem = ((size_t)(H2 + PF) * SLOT_U4 + 2 * NW * KEY_U4) * sizeof(uint4);
+    size_t smem = ((size_t)(H2 + PF + 1) * SLOT_U4 + 2 * NW * KEY_U4) * sizeof(uint4);
     static bool configured = false;
     if (!configured) {
         SR_CUDA(ctx, cudaFuncSetAttribute(search_tile_kernel<H2, COST, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -308,7 +344,7 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     a.w1 = g.w1; a.h1 = g.h1; a.w2 = g.w2; a.h2 = g.h2; a.half = g.half;
     a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
     a.npass = (g.dhi - a.dbase + 63) / 64;
-    a.row0 = g.row0; a.row1 = r1; a.k64 = 64;
+    a.row0 = g.row0; a.row1 = r1; a.k64 = 64; a.kp1 = 1u; a.km1 = 0xFFFFFFFFu;
     int ntx = (g.w2 + XT - g.half + TILE_OUT - 1) / TILE_OUT;
     int rows = r1 - g.row0;
     if (a.npass <= 0) {
