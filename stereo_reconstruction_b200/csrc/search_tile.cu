@@ -21,6 +21,7 @@
 // Window geometry of the reference: rows [y-u, y+dn), cols [x-l, x+r) with l=min(x,h),
 // r=min(w2-x-1,h), u=min(y,h), dn=min(h2-y-1,h)  ==  the fixed window [x-h,x+h) x [y-h,y+h) with
 // the pointwise cost forced to 0 outside columns [0,w2-1) and rows [0,h2-1).
+#include <cstdlib>
 #include "sr_internal.cuh"
 
 namespace {
@@ -36,7 +37,7 @@ constexpr int SLOT_U4 = RPOS + LPOS;  // uint4 per ring slot
 constexpr int KEY_U4 = 160;           // uint4 per warp key row (128 chunks padded)
 constexpr int PF = 2;                 // rows prefetched ahead
 #ifndef SR_TILE_FMA_FROM
-#define SR_TILE_FMA_FROM 2             // disparity pairs >= this index slide on the FMA pipe (4 = none)
+#define SR_TILE_FMA_FROM 4             // disparity pairs >= this index slide on the FMA pipe (4 = none)
 #endif
 constexpr int FMA_FROM = SR_TILE_FMA_FROM;
 
@@ -45,6 +46,9 @@ __device__ __forceinline__ int padpos(int c) { return c + (c >> 2); }
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     unsigned s = (unsigned)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async16_s(uint32_t saddr, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(saddr), "l"(gmem));
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 template <int N>
@@ -72,13 +76,13 @@ __device__ __forceinline__ uint4 lds128(uint32_t saddr) {
 // slot: shared address of the ring slot (warp-uniform); rb: this lane's byte offset inside the right
 // segment; lb[i]: byte offsets (lane base + warp-uniform chunk) of the 5 left chunks.
 template <int COST, bool ADD>
-__device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], uint32_t slot, uint32_t rb,
-                                                const uint32_t (&lb)[5], uint32_t colmask) {
-    uint4 la = lds128(slot + lb[0]);
+__device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], uint32_t slot, uint32_t lane_b,
+                                                const uint32_t (&uo)[5], uint32_t colmask) {
+    uint4 la = lds128((slot + uo[0]) + lane_b);
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        uint4 lbv = lds128(slot + lb[k + 1]);
-        uint4 rr = lds128(slot + rb + 16 * k);
+        uint4 lbv = lds128((slot + uo[k + 1]) + lane_b);
+        uint4 rr = lds128(slot + lane_b + 16 * k);
         uint32_t l7[7] = {la.x, la.y, la.z, la.w, lbv.x, lbv.y, lbv.z};
         uint32_t r4[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
@@ -162,13 +166,22 @@ __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32
     }
 }
 
+__device__ __forceinline__ void sts128(uint32_t saddr, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(saddr), "r"(x), "r"(y), "r"(z), "r"(w));
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t saddr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
+    return v;
+}
+
 template <int H2, int COST, int NW>
 __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     constexpr int NSLOT = H2 + PF + 1;   // +1: half of the warps subtract the leaving row one iteration late
+    constexpr uint32_t SLOT_B = SLOT_U4 * 16, RING_B = NSLOT * SLOT_B, KEYROW_B = KEY_U4 * 16, KEYBUF_B = NW * KEYROW_B;
     static_assert(RCH + LCH <= NW * 32, "one staged chunk per thread");
-    extern __shared__ __align__(128) uint4 smem4[];
-    uint4* ring = smem4;                          // NSLOT x SLOT_U4
-    uint4* keysm = smem4 + NSLOT * SLOT_U4;       // 2 x NW x KEY_U4
+    static_assert(TILE_OUT <= NW * 32, "one output column per thread in the key reduction");
+    extern __shared__ __align__(128) uint4 smem4[];   // ring: NSLOT x SLOT_U4, then keys: 2 x NW x KEY_U4
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler
@@ -179,6 +192,11 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     if (yb0 >= yb1) return;
     const int cb = CB + XT * lane;                             // this thread's own columns [cb, cb+16)
     const uint32_t k64 = a.k64;
+    const int pass = (int)(gridDim.z - 1 - blockIdx.z);        // heaviest (masked / ragged) passes are scheduled first
+    const int dcta = a.dbase + pass * (DT * NW);               // first disparity of the pass (multiple of 4)
+    const int d0 = dcta + DT * warp;                            // this warp's 4 disparities
+    const bool active = d0 < a.dhi;                             // warps with at least one d < dhi
+    const bool late_sub = (warp >> 2) & 1;
 
     // own columns that contribute (inside [0, w2-1)); others are forced to 0
     uint32_t colmask = 0;
@@ -191,112 +209,98 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
         int x = cb + h + j;
         if (x >= 0 && x < a.w2) dlim_min = min(dlim_min, min(a.dhi, a.w1 - x - min(a.w2 - x - 1, h)));
     }
-    // lane bases inside a slot / key row (5 chunk positions per lane: 4 data + 1 pad), as 32-bit
-    // shared-memory byte offsets: every hot-loop load is "uniform slot base + per-thread constant"
-    const int lane_u4 = 5 * lane;
+    const bool needmask = __any_sync(0xffffffffu, d0 < a.dlo || d0 + DT - 1 >= dlim_min);
+
+    // Shared-memory addressing, all 32-bit byte addresses: a hot-loop load is
+    // "uniform (slot base + chunk offset of this warp) + per-thread lane offset".
     const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem4);
-    const uint32_t rb = 16u * lane_u4;
-    uint32_t lb[5];
+    const uint32_t keys_base = smem_base + RING_B;
+    const uint32_t lane_b = 80u * lane;                        // 5 chunk positions per lane: 4 data + 1 pad
+    uint32_t uo[5];                                            // warp-uniform offsets of the 5 left chunks
 #pragma unroll
-    for (int i = 0; i < 5; i++) lb[i] = 16u * (RPOS + lane_u4 + padpos(warp + i));
-    const int y_start = yb0 - (H2 - 1);
-    // this thread's chunk of every staged row (RCH + LCH <= NW*32 chunks per row)
-    const int ld_dst = tid < RCH ? padpos(tid) : RPOS + padpos(tid - RCH);
-    const int ld_src = CB + 4 * (tid < RCH ? tid : tid - RCH);
+    for (int i = 0; i < 5; i++) uo[i] = 16u * (RPOS + padpos(warp + i));
+    auto slot_of = [&](int r) { return (uint32_t)(((r % NSLOT) + NSLOT) % NSLOT) * SLOT_B; };
+    auto next_slot = [&](uint32_t sb) { return sb + SLOT_B == RING_B ? 0u : sb + SLOT_B; };
     auto row_ok = [&](int r) { return r >= 0 && r < a.h2 - 1; };
-    auto slot_of = [&](int r) { return ((r % NSLOT) + NSLOT) % NSLOT; };
 
-    {
-        const int pass = (int)blockIdx.z;
-        const int dcta = a.dbase + pass * (DT * NW);           // first disparity of the pass (multiple of 4)
-        const int d0 = dcta + DT * warp;                        // this warp's 4 disparities
-        const int nactive = min(NW, (a.dhi - dcta + DT - 1) / DT);  // warps with at least one d < dhi
-        const bool active = warp < nactive;
-        const bool late_sub = (warp >> 2) & 1;
-        const bool needmask = __any_sync(0xffffffffu, d0 < a.dlo || d0 + DT - 1 >= dlim_min);
+    // staging: thread t copies chunk t of every row (right chunks first, then left chunks)
+    const int y_start = yb0 - (H2 - 1);
+    const bool ld_on = tid < RCH + LCH;
+    const bool ld_right = tid < RCH;
+    const uint32_t ld_dst = smem_base + 16u * (ld_right ? padpos(tid) : RPOS + padpos(tid - RCH));
+    const int ld_pitch = ld_right ? a.pitchR : a.pitchL;
+    int r_pf = y_start + h - 1;                                // next row to stage
+    const uint32_t* ld_ptr = (ld_right ? a.R : a.L + dcta) + (ptrdiff_t)r_pf * ld_pitch + CB + 4 * (ld_right ? tid : tid - RCH);
+    uint32_t slot_pf = slot_of(r_pf);
+    auto issue_row = [&]() {
+        if (row_ok(r_pf) && ld_on) cp_async16_s(slot_pf + ld_dst, ld_ptr);
+        cp_async_commit();
+        r_pf++; ld_ptr += ld_pitch; slot_pf = next_slot(slot_pf);
+    };
 
-        uint32_t col[XT][DT];
+    // key reduction: thread q owns output column CB + h + q
+    const int xq = CB + h + tid;
+    const bool red_on = tid < TILE_OUT && xq >= 0 && xq < a.w2;
+    const uint32_t red_b = keys_base + 4u * (tid + 4 * (tid >> 4));
+    uint32_t* pl = a.planes + (size_t)pass * a.plane_stride + (size_t)yb0 * a.w2 + xq;
+    auto reduce_row = [&](uint32_t buf) {
+        if (red_on) {
+            uint32_t kk[NW];
 #pragma unroll
-        for (int j = 0; j < XT; j++)
+            for (int w = 0; w < NW; w++) kk[w] = lds32(red_b + buf + w * KEYROW_B);
+            uint32_t k = 0xFFFFFFFFu;
 #pragma unroll
-            for (int t = 0; t < DT; t++) col[j][t] = 0;
-
-        auto issue_row = [&](int r) {
-            if (row_ok(r) && tid < RCH + LCH) {
-                uint4* dst = ring + slot_of(r) * SLOT_U4 + ld_dst;
-                const uint32_t* src = (tid < RCH ? a.R + (size_t)r * a.pitchR : a.L + (size_t)r * a.pitchL + dcta) + ld_src;
-                cp_async16(dst, src);
-            }
-            cp_async_commit();
-        };
-        // CTA-wide reduction of the keys of output row y -> this pass's key plane
-        uint32_t* plane = a.planes + (size_t)pass * a.plane_stride;
-        auto reduce_row = [&](int y) {
-            const uint32_t* kb = reinterpret_cast<const uint32_t*>(keysm + (y & 1) * NW * KEY_U4);
-            for (int q = tid; q < TILE_OUT; q += NW * 32) {
-                int x = CB + h + q;
-                if (x < 0 || x >= a.w2) continue;
-                int word = q + 4 * (q >> 4);
-                uint32_t kk[NW];
-#pragma unroll
-                for (int w = 0; w < NW; w++) kk[w] = kb[w * (KEY_U4 * 4) + word];
-                uint32_t k = 0xFFFFFFFFu;
-#pragma unroll
-                for (int w = 0; w < NW; w++) k = min(k, kk[w]);
-                plane[(size_t)y * a.w2 + x] = k;
-            }
-        };
-
-        // prologue: rows of the first PF iterations
-#pragma unroll
-        for (int i = 0; i < PF; i++) issue_row(y_start + i + h - 1);
-
-        int s_in = slot_of(y_start + h - 1), s_out = slot_of(y_start - h);
-        for (int y = y_start; y < yb1; y++) {
-            cp_async_wait<PF - 1>();
-            __syncthreads();
-            issue_row(y + PF + h - 1);
-            if (y - 1 >= yb0) reduce_row(y - 1);
-            if (active) {
-                // Phase staggering: the warps of one scheduler alternate between "subtract now" and
-                // "subtract at the start of the next iteration", so that ALU-only phases (pointwise
-                // costs) of some warps overlap the FMA-heavy window/WTA phase of the others.
-                if (late_sub && y - 1 >= yb0 && row_ok(y - 1 - h) && colmask != 0) {
-                    const int sp = s_out == 0 ? NSLOT - 1 : s_out - 1;
-                    vertical_update<COST, false>(col, smem_base + (uint32_t)sp * (SLOT_U4 * 16), rb, lb, colmask);
-                }
-                const int rin = y + h - 1;
-                if (row_ok(rin) && colmask != 0) {
-                    vertical_update<COST, true>(col, smem_base + (uint32_t)s_in * (SLOT_U4 * 16), rb, lb, colmask);
-                }
-                if (y >= yb0) {
-                    uint32_t keys[XT];
-#pragma unroll
-                    for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
-                    if (needmask) window_wta<H2, true>(col, keys, k64, a.kp1, a.km1, (uint32_t)(DT * warp), d0, cb + h, a);
-                    else window_wta<H2, false>(col, keys, k64, a.kp1, a.km1, (uint32_t)(DT * warp), d0, cb + h, a);
-                    uint4* kw = keysm + ((y & 1) * NW + warp) * KEY_U4 + lane_u4;
-#pragma unroll
-                    for (int k = 0; k < 4; k++)
-                        kw[k] = make_uint4(keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
-                    const int rout = y - h;
-                    if (!late_sub && y + 1 < yb1 && row_ok(rout) && colmask != 0) {
-                        vertical_update<COST, false>(col, smem_base + (uint32_t)s_out * (SLOT_U4 * 16), rb, lb, colmask);
-                    }
-                }
-            }
-            else if (y >= yb0) {
-                uint4* kw = keysm + ((y & 1) * NW + warp) * KEY_U4 + lane_u4;
-#pragma unroll
-                for (int k = 0; k < 4; k++) kw[k] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
-            }
-            s_in = s_in + 1 == NSLOT ? 0 : s_in + 1;
-            s_out = s_out + 1 == NSLOT ? 0 : s_out + 1;
+            for (int w = 0; w < NW; w++) k = min(k, kk[w]);
+            *pl = k;
         }
-        cp_async_wait<0>();
+        pl += a.w2;
+    };
+
+    uint32_t col[XT][DT];
+#pragma unroll
+    for (int j = 0; j < XT; j++)
+#pragma unroll
+        for (int t = 0; t < DT; t++) col[j][t] = 0;
+
+#pragma unroll
+    for (int i = 0; i < PF; i++) issue_row();                  // rows of the first PF iterations
+
+    uint32_t s_in = slot_of(y_start + h - 1), s_out = slot_of(y_start - h), s_prev = slot_of(y_start - h - 1);
+    const uint32_t key_st = keys_base + warp * KEYROW_B + lane_b;
+    for (int y = y_start; y < yb1; y++) {
+        const uint32_t buf = (y & 1) ? KEYBUF_B : 0u;
+        cp_async_wait<PF - 1>();
         __syncthreads();
-        reduce_row(yb1 - 1);
+        issue_row();
+        if (y - 1 >= yb0) reduce_row(buf ^ KEYBUF_B);
+        if (active) {
+            // Phase staggering: the warps of one scheduler alternate between "subtract now" and
+            // "subtract at the start of the next iteration", so that ALU-only phases (pointwise
+            // costs) of some warps overlap the FMA-heavy window/WTA phase of the others.
+            if (late_sub && y - 1 >= yb0 && row_ok(y - 1 - h) && colmask != 0)
+                vertical_update<COST, false>(col, smem_base + s_prev, lane_b, uo, colmask);
+            if (row_ok(y + h - 1) && colmask != 0) vertical_update<COST, true>(col, smem_base + s_in, lane_b, uo, colmask);
+            if (y >= yb0) {
+                uint32_t keys[XT];
+#pragma unroll
+                for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
+                if (needmask) window_wta<H2, true>(col, keys, k64, a.kp1, a.km1, (uint32_t)(DT * warp), d0, cb + h, a);
+                else window_wta<H2, false>(col, keys, k64, a.kp1, a.km1, (uint32_t)(DT * warp), d0, cb + h, a);
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    sts128(key_st + buf + 16 * k, keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
+                if (!late_sub && y + 1 < yb1 && row_ok(y - h) && colmask != 0)
+                    vertical_update<COST, false>(col, smem_base + s_out, lane_b, uo, colmask);
+            }
+        } else if (y >= yb0) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) sts128(key_st + buf + 16 * k, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+        }
+        s_prev = s_out; s_out = next_slot(s_out); s_in = next_slot(s_in);
     }
+    cp_async_wait<0>();
+    __syncthreads();
+    reduce_row(((yb1 - 1) & 1) ? KEYBUF_B : 0u);
 }
 
 template <int H2, int COST>
@@ -364,12 +368,16 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     if (maxnb > 256) maxnb = 256;
     long bestcost = -1;
     int nbands = 1;
-    for (int nb = 1; nb <= maxnb; nb++) {
+    static const char* nb_env = getenv("SR_TILE_NBANDS");   // tuning override
+    int nb_lo = 1;
+    if (nb_env && atoi(nb_env) > 0) { nb_lo = atoi(nb_env); if (nb_lo > maxnb) nb_lo = maxnb; maxnb = nb_lo; }
+    for (int nb = nb_lo; nb <= maxnb; nb++) {
         int band = (rows + nb - 1) / nb;
         int nbe = (rows + band - 1) / band;
         long ctas = (long)ntx * a.npass * nbe;
-        long waves = (ctas + sms - 1) / sms;
-        long c = waves * (band + 2 * g.half - 1 + 2);
+        // makespan model: CTAs are list-scheduled one per SM; durations vary (masked passes, image edges),
+        // so the tail costs about one CTA duration on top of the average load
+        long c = (long)((double)(ctas + sms) / sms * (band + 2 * g.half - 1 + 2) * 16.0);
         if (bestcost < 0 || c < bestcost) { bestcost = c; nbands = nbe; a.band = band; }
     }
     if (cost == SR_COST_SAD) return dispatch_h2<SR_COST_SAD>(ctx, a, ntx, nbands);
