@@ -1,4 +1,5 @@
 // capi_search.cu -- WindowSearch entry points of the C-ABI (dispatch, download, one-shot calls).
+#include <cstdlib>
 #include <cstring>
 #include "sr_internal.cuh"
 
@@ -20,6 +21,120 @@ static int validate(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p) {
         return sr_fail(ctx, SR_E_BADARG, "unknown cost %d", p->cost);
     if (p->variant != SR_VARIANT_RIGHT && p->variant != SR_VARIANT_LEFT && p->variant != SR_VARIANT_LINEAR)
         return sr_fail(ctx, SR_E_BADARG, "unknown variant %d", p->variant);
+    return SR_OK;
+}
+
+// ---- row-chunk pipeline of the one-shot call ------------------------------------------------------
+// H2D + pack of chunk c+1 (copy stream 0), search + resolve of chunk c (compute stream) and D2H of
+// chunk c-1 (copy stream 1) overlap; only the first upload and the last download are exposed.
+// Applies where output rows are independent (Right variant, tile kernel, no raster smoothing rule)
+// and both host sides are pinned (a pageable buffer needs a staging memcpy that serialises anyway).
+static bool host_pinned(const void* p) {
+    cudaPointerAttributes attr;
+    bool pinned = cudaPointerGetAttributes(&attr, p) == cudaSuccess &&
+                  (attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged);
+    cudaGetLastError();
+    return pinned;
+}
+
+static int pipeline_chunks(const sr_pair* pair, const sr_search_params* p) {
+    const char* env = getenv("SR_PIPE_CHUNKS");   // tuning / test override
+    int c = env ? atoi(env) : 0;
+    if (c <= 0) {
+        // small pairs: one chunk (launch overheads dominate); large pairs: ~2.8 M right pixels per chunk
+        double px = (double)pair->w2 * pair->h2;
+        c = (int)(px / 1.3e6);
+        if (c > 8) c = 8;
+    }
+    int maxc = pair->h2 / (4 * p->block + 16);
+    if (c > maxc) c = maxc;
+    return c < 1 ? 1 : c;
+}
+
+static bool can_pipeline(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_image* right,
+                         const sr_search_params* p, const double* disp_out) {
+    if (p->variant != SR_VARIANT_RIGHT || p->var_block || p->cost == SR_COST_NCC || p->subpixel || p->lr_check) return false;
+    if (p->min_disp < 0 || p->block < 3 || (p->block - 1) / 2 > 8) return false;
+    if (p->smooth != 1.0 && p->min_disp == 0) return false;   // raster dependency between rows
+    if (pair->w2 == 1 || pair->h2 == 1) return false;
+    if (!rows_fit(pair->h1, pair->h2, (p->block - 1) / 2)) return false;
+    if (pipeline_chunks(pair, p) < 2) return false;
+    return host_pinned(left->bgr) && host_pinned(right->bgr) && host_pinned(disp_out);
+}
+
+static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_image* right,
+                                  const sr_search_params* p, double* disp_out, size_t out_pitch) {
+    const int nch = pipeline_chunks(pair, p);
+    const int half = (p->block - 1) / 2;
+    const int oh = pair->h2, ow = pair->w2;
+    const size_t rowb = (size_t)ow * sizeof(double);
+    if (out_pitch < rowb) return sr_fail(ctx, SR_E_BADARG, "output pitch %zu smaller than a row (%zu)", out_pitch, rowb);
+    if (left->pitch < (size_t)left->w * 3 || right->pitch < (size_t)right->w * 3)
+        return sr_fail(ctx, SR_E_BADARG, "image pitch smaller than a row");
+    while ((int)ctx->pipe_ev.size() < 2 * nch + 1) {
+        cudaEvent_t e;
+        SR_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->pipe_ev.push_back(e);
+    }
+    cudaStream_t compute = ctx->stream, s_up = ctx->aux[0], s_down = ctx->aux[1];
+    // the copy streams start after whatever the compute stream still has queued (previous call)
+    cudaEvent_t ev_start = ctx->pipe_ev[2 * nch];
+    SR_CUDA(ctx, cudaEventRecord(ev_start, compute));
+    SR_CUDA(ctx, cudaStreamWaitEvent(s_up, ev_start, 0));
+    SR_CUDA(ctx, cudaStreamWaitEvent(s_down, ev_start, 0));
+    SR_CUDA(ctx, cudaStreamWaitEvent(ctx->aux[2], ev_start, 0));
+    int upL = 0, upR = 0, rc = SR_OK;
+    const size_t rowL = (size_t)left->w * 3, rowR = (size_t)right->w * 3;
+    for (int c = 0; c < nch && rc == SR_OK; c++) {
+        int r0 = (int)((long)oh * c / nch), r1 = (int)((long)oh * (c + 1) / nch);
+        // input rows this chunk needs: window rows [r0 - half, r1 + half) of both images
+        int needR = r1 + half + 1 < pair->h2 ? r1 + half + 1 : pair->h2;
+        int needL = r1 + half + 1 < pair->h1 ? r1 + half + 1 : pair->h1;
+        if (c == nch - 1) { needR = pair->h2; needL = pair->h1; }
+        {
+            cudaStream_t saved = ctx->stream;
+            ctx->stream = s_up;
+            if (needR > upR) {
+                cudaError_t e = cudaMemcpy2DAsync(pair->rawR + (size_t)upR * rowR, rowR, right->bgr + (size_t)upR * right->pitch,
+                                                  right->pitch, rowR, needR - upR, cudaMemcpyHostToDevice, s_up);
+                if (e != cudaSuccess) rc = sr_cuda_check(ctx, e, "cudaMemcpy2DAsync(H2D right rows)");
+                if (rc == SR_OK) rc = sr_launch_pack_rows(ctx, pair->rawR, rowR, right->w, upR, needR, &pair->R);
+                upR = needR;
+            }
+            if (rc == SR_OK && needL > upL) {
+                cudaError_t e = cudaMemcpy2DAsync(pair->rawL + (size_t)upL * rowL, rowL, left->bgr + (size_t)upL * left->pitch,
+                                                  left->pitch, rowL, needL - upL, cudaMemcpyHostToDevice, s_up);
+                if (e != cudaSuccess) rc = sr_cuda_check(ctx, e, "cudaMemcpy2DAsync(H2D left rows)");
+                if (rc == SR_OK) rc = sr_launch_pack_rows(ctx, pair->rawL, rowL, left->w, upL, needL, &pair->L);
+                upL = needL;
+            }
+            ctx->stream = saved;
+        }
+        if (rc != SR_OK) break;
+        // chunks alternate between two compute streams: the first CTAs of chunk c+1 fill the SMs that
+        // the last wave of chunk c leaves idle (one 512-thread CTA per SM, so no other overlap exists)
+        cudaStream_t cs = (c & 1) ? ctx->aux[2] : compute;
+        SR_CUDA(ctx, cudaEventRecord(ctx->pipe_ev[2 * c], s_up));
+        SR_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->pipe_ev[2 * c], 0));
+        ctx->stream = cs;
+        rc = sr_search_run(ctx, pair, p, r0, r1);
+        ctx->stream = compute;
+        if (rc != SR_OK) break;
+        SR_CUDA(ctx, cudaEventRecord(ctx->pipe_ev[2 * c + 1], cs));
+        SR_CUDA(ctx, cudaStreamWaitEvent(s_down, ctx->pipe_ev[2 * c + 1], 0));
+        cudaError_t e = cudaMemcpy2DAsync((char*)disp_out + (size_t)r0 * out_pitch, out_pitch, pair->out + (size_t)r0 * ow, rowb, rowb,
+                                          r1 - r0, cudaMemcpyDeviceToHost, s_down);
+        if (e != cudaSuccess) rc = sr_cuda_check(ctx, e, "cudaMemcpy2DAsync(D2H rows)");
+    }
+    cudaStreamSynchronize(s_up);
+    cudaStreamSynchronize(compute);
+    cudaStreamSynchronize(ctx->aux[2]);
+    cudaStreamSynchronize(s_down);
+    if (rc != SR_OK) return rc;
+    pair->last_row0 = 0; pair->last_row1 = oh;
+    pair->last_geom.row0 = 0; pair->last_geom.row1 = oh;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return sr_cuda_check(ctx, e, "row-chunk pipeline");
     return SR_OK;
 }
 
@@ -165,6 +280,11 @@ int sr_block_search(sr_ctx* ctx, const sr_image* left, const sr_image* right, co
     if (!pair) {
         if ((rc = sr_pair_create(ctx, left->w, left->h, right->w, right->h, &pair)) != SR_OK) return rc;
         ctx->batch_pairs.push_back(pair);
+    }
+    if (validate(ctx, pair, p) == SR_OK && can_pipeline(ctx, pair, left, right, p, disp_out)) {
+        if ((rc = block_search_pipelined(ctx, pair, left, right, p, disp_out, out_pitch)) != SR_OK) return rc;
+        if (max_block) *max_block = p->block;   // fixed window: BlockSearch.cpp:98
+        return SR_OK;
     }
     if ((rc = sr_pair_upload(ctx, pair, left, right)) != SR_OK) return rc;
     int oh = p->variant == SR_VARIANT_LEFT ? left->h : right->h;

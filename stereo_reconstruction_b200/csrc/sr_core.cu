@@ -62,9 +62,14 @@ int sr_ctx_create(int device, sr_ctx** out) {
     if ((e = cudaSetDevice(device)) != cudaSuccess) return sr_cuda_check(nullptr, e, "cudaSetDevice");
     sr_ctx* c = new sr_ctx();
     c->device = device;
-    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaStreamCreateWithFlags(&c->aux[0], cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaStreamCreateWithFlags(&c->aux[1], cudaStreamNonBlocking)) != cudaSuccess ||
+    // the copy streams outrank the compute stream: their small pack kernels must not queue behind the
+    // search kernel's CTAs (one per SM) when the pipelines overlap upload, search and download
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    if ((e = cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
+        (e = cudaStreamCreateWithPriority(&c->aux[0], cudaStreamNonBlocking, prio_hi)) != cudaSuccess ||
+        (e = cudaStreamCreateWithPriority(&c->aux[1], cudaStreamNonBlocking, prio_hi)) != cudaSuccess ||
+        (e = cudaStreamCreateWithPriority(&c->aux[2], cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
         (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
         (e = cudaEventCreate(&c->kev0)) != cudaSuccess || (e = cudaEventCreate(&c->kev1)) != cudaSuccess) {
         int rc = sr_cuda_check(nullptr, e, "stream/event creation");
@@ -81,6 +86,7 @@ void sr_ctx_destroy(sr_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (sr_pair* p : ctx->batch_pairs) sr_pair_destroy(ctx, p);
     ctx->batch_pairs.clear();
+    for (cudaEvent_t e : ctx->pipe_ev) cudaEventDestroy(e);
     for (auto& b : ctx->scratch) if (b.p) cudaFree(b.p);
     for (auto& p : ctx->pinned) if (p) cudaFreeHost(p);
     cudaEventDestroy(ctx->ev0);
@@ -89,6 +95,7 @@ void sr_ctx_destroy(sr_ctx* ctx) {
     cudaEventDestroy(ctx->kev1);
     cudaStreamDestroy(ctx->aux[0]);
     cudaStreamDestroy(ctx->aux[1]);
+    cudaStreamDestroy(ctx->aux[2]);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -125,11 +132,11 @@ const char* sr_last_kernel(const sr_ctx* ctx) { return ctx ? ctx->last_kernel : 
 }  // extern "C"
 
 // ---- packing: BGR u8 (pitch) -> one uint32 per pixel, padded rows ---------------------------
-__global__ void pack_bgr_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, int w, int h,
+__global__ void pack_bgr_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, int w, int y0,
                                 uint32_t* __restrict__ dst, int pitch_px, int padl) {
     // one thread per destination pixel of the padded row (padding written as 0)
     int xp = blockIdx.x * blockDim.x + threadIdx.x;
-    int y = blockIdx.y;
+    int y = y0 + blockIdx.y;
     if (xp >= pitch_px) return;
     int x = xp - padl;
     uint32_t v = 0;
@@ -140,11 +147,15 @@ __global__ void pack_bgr_kernel(const uint8_t* __restrict__ raw, size_t raw_pitc
     dst[(size_t)y * pitch_px + xp] = v;
 }
 
-int sr_launch_pack(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int h, PackedImage* img) {
-    dim3 grid(cdiv(img->pitch, 256), h);
-    pack_bgr_kernel<<<grid, 256, 0, ctx->stream>>>(raw, raw_pitch, w, h, img->base, img->pitch, SR_PADL);
+int sr_launch_pack_rows(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int y0, int y1, PackedImage* img) {
+    if (y1 <= y0) return SR_OK;
+    dim3 grid(cdiv(img->pitch, 256), y1 - y0);
+    pack_bgr_kernel<<<grid, 256, 0, ctx->stream>>>(raw, raw_pitch, w, y0, img->base, img->pitch, SR_PADL);
     SR_LAUNCHED(ctx);
     return SR_OK;
+}
+int sr_launch_pack(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int h, PackedImage* img) {
+    return sr_launch_pack_rows(ctx, raw, raw_pitch, w, 0, h, img);
 }
 
 static int alloc_packed(sr_ctx* ctx, PackedImage* img, int w, int h, int padr) {

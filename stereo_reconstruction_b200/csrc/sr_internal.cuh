@@ -19,7 +19,7 @@ struct DevBuf {
 struct sr_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaStream_t aux[2] = {nullptr, nullptr};  // copy streams of the batch pipeline
+    cudaStream_t aux[3] = {nullptr, nullptr, nullptr};  // copy streams of the pipelines + second compute stream
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t kev0 = nullptr, kev1 = nullptr;  // around the dominant search kernel of the last run
     bool kev_valid = false;
@@ -30,6 +30,7 @@ struct sr_ctx {
     void* pinned[4] = {nullptr, nullptr, nullptr, nullptr};
     size_t pinned_cap[4] = {0, 0, 0, 0};
     std::vector<sr_pair*> batch_pairs;
+    std::vector<cudaEvent_t> pipe_ev;  // events of the row-chunk pipeline of sr_block_search
     void* nccl_comm = nullptr;
     int rank = 0, nranks = 1;
 };
@@ -97,6 +98,8 @@ static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
 // ---- launchers implemented in the .cu files (all asynchronous on ctx->stream) ----
 int sr_launch_pack(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int h, PackedImage* img);
+// rows [y0, y1) only (raw points at row 0 of the device copy)
+int sr_launch_pack_rows(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int y0, int y1, PackedImage* img);
 
 // Fast path: fixed window, SSD/SAD, first minimum over [dlo,dhi) -> pair->best.
 // Returns 1 when it handled the request, 0 when the shape is not supported (caller falls back).

@@ -95,3 +95,34 @@ def test_errors(sr, ctx):
         sr.BlockSearch(L, L, 0, 0, 16, ctx=ctx).computeDisparityMapRight(1.0)
     with pytest.raises(sr.capi.SrError):
         sr.BlockSearch(L[:, :, :2], L, 9, 0, 16, ctx=ctx).computeDisparityMapRight(1.0)
+
+
+@pytest.mark.parametrize("cost,block,min_d", [(0, 9, 0), (1, 9, 0), (0, 17, 2), (1, 5, 0)])
+@pytest.mark.parametrize("chunks", ["3", "7"])
+def test_one_shot_row_chunk_pipeline(sr, ctx, orc, monkeypatch, cost, block, min_d, chunks):
+    """sr_block_search with pinned host buffers runs the row-chunk pipeline (H2D / search / D2H
+    overlapped): the result must equal the oracle and the plain (pageable, single-launch) call."""
+    capi = sr.capi
+    w, h, D = 640, 333, 48
+    L, R = synth(orc, w, h, min_d, D, seed=11)
+    R[100:120, 200:260] = 0
+    # a pitch wider than the row, as cv::Mat ROI views have
+    Lp, lh = capi.pinned_empty((h, w + 5, 3), np.uint8)
+    Rp, rh = capi.pinned_empty((h, w + 5, 3), np.uint8)
+    outp, oh_ = capi.pinned_empty((h, w + 3), np.float64)
+    try:
+        Lp[:, :w] = L
+        Rp[:, :w] = R
+        outp[...] = -7.0
+        monkeypatch.setenv("SR_PIPE_CHUNKS", chunks)
+        p = capi.search_params(block=block, min_disp=min_d, max_disp=D, smooth=1.0, cost=cost)
+        n0 = ctx.launches
+        got = capi.block_search(ctx, Lp[:, :w], Rp[:, :w], p, out=outp[:, :w])
+        assert ctx.launches - n0 >= 3 * 2, "row-chunk pipeline did not run (expected several chunk launches)"
+        want = orc.block_search_right_fast(L, R, block, min_d, D, 1.0, cost=cost)
+        np.testing.assert_array_equal(np.asarray(got), want)
+        assert (outp[:, w:] == -7.0).all(), "pipeline wrote outside the output rows' extent"
+        plain = capi.block_search(ctx, L, R, p)
+        np.testing.assert_array_equal(plain, want)
+    finally:
+        capi.free_pinned(lh); capi.free_pinned(rh); capi.free_pinned(oh_)
