@@ -118,6 +118,7 @@ struct TileArgs {
     int band;            // rows per CTA band
     uint32_t k64;        // == 64, passed as data so that key = S*64+d stays one IMAD (FMA pipe)
     uint32_t kp1, km1;   // == 1, == 0xFFFFFFFF (-1): IMAD-based sliding sums
+    int red_mode;        // 1: half of the warps merge the previous row's keys at the end of the iteration
 };
 
 // horizontal window sums + in-thread WTA for one output row.  Disparities are processed in pairs so
@@ -197,6 +198,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int d0 = dcta + DT * warp;                            // this warp's 4 disparities
     const bool active = d0 < a.dhi;                             // warps with at least one d < dhi
     const bool late_sub = (warp >> 2) & 1;
+    const bool red_late = a.red_mode && ((warp >> 3) & 1);   // spreads the LDS burst of the key merge over the iteration
 
     // own columns that contribute (inside [0, w2-1)); others are forced to 0
     uint32_t colmask = 0;
@@ -238,10 +240,14 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
         r_pf++; ld_ptr += ld_pitch; slot_pf = next_slot(slot_pf);
     };
 
-    // key reduction: thread q owns output column CB + h + q
-    const int xq = CB + h + tid;
-    const bool red_on = tid < TILE_OUT && xq >= 0 && xq < a.w2;
-    const uint32_t red_b = keys_base + 4u * (tid + 4 * (tid >> 4));
+    // key reduction: each half-warp owns one 16-column group (= one thread's columns in the key row,
+    // 20 words apart because of the padding).  The two groups of a warp are 4 apart: their bank
+    // ranges [20g, 20g+16) and [20g+80, 20g+96) mod 32 are disjoint, so the LDS is conflict-free.
+    const int rgrp = (warp >> 2) * 8 + (warp & 3) + ((lane >> 4) << 2);
+    const int rq = XT * rgrp + (lane & 15);
+    const int xq = CB + h + rq;
+    const bool red_on = rgrp < 31 && xq >= 0 && xq < a.w2;
+    const uint32_t red_b = keys_base + 4u * (20 * rgrp + (lane & 15));
     uint32_t* pl = a.planes + (size_t)pass * a.plane_stride + (size_t)yb0 * a.w2 + xq;
     auto reduce_row = [&](uint32_t buf) {
         if (red_on) {
@@ -272,7 +278,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
         cp_async_wait<PF - 1>();
         __syncthreads();
         issue_row();
-        if (y - 1 >= yb0) reduce_row(buf ^ KEYBUF_B);
+        if (!red_late && y - 1 >= yb0) reduce_row(buf ^ KEYBUF_B);
         if (active) {
             // Phase staggering: the warps of one scheduler alternate between "subtract now" and
             // "subtract at the start of the next iteration", so that ALU-only phases (pointwise
@@ -296,6 +302,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
 #pragma unroll
             for (int k = 0; k < 4; k++) sts128(key_st + buf + 16 * k, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
         }
+        if (red_late && y - 1 >= yb0) reduce_row(buf ^ KEYBUF_B);
         s_prev = s_out; s_out = next_slot(s_out); s_in = next_slot(s_in);
     }
     cp_async_wait<0>();
@@ -349,6 +356,8 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
     a.npass = (g.dhi - a.dbase + 63) / 64;
     a.row0 = g.row0; a.row1 = r1; a.k64 = 64; a.kp1 = 1u; a.km1 = 0xFFFFFFFFu;
+    static const char* rm_env = getenv("SR_TILE_REDMODE");
+    a.red_mode = rm_env ? atoi(rm_env) : 1;
     int ntx = (g.w2 + XT - g.half + TILE_OUT - 1) / TILE_OUT;
     int rows = r1 - g.row0;
     if (a.npass <= 0) {
