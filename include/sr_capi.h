@@ -126,6 +126,9 @@ int sr_search_download(sr_ctx* ctx, sr_pair* pair, double* disp_out, size_t out_
 /* Device pointer (double*, tightly packed rows of the output width) of the last result. */
 void* sr_search_result_dev(sr_ctx* ctx, sr_pair* pair);
 int sr_search_max_block(sr_ctx* ctx, sr_pair* pair, int* max_block);
+/* The left-referenced integer disparity map (w1 x h1, int32) that the last run with lr_check = 1
+ * computed for the consistency test (extension); SR_E_BADARG when there is none. */
+int sr_search_left_disparity(sr_ctx* ctx, sr_pair* pair, int32_t* disp_left, size_t out_pitch);
 /* Effective (reference-semantics) number of (pixel, candidate) evaluations of the last run
  * restricted to its rows: sum over non-black pixels of the candidates before the break
  * (BlockSearch.cpp:147-149). */

@@ -48,7 +48,7 @@ SYMBOLS = [
     "sr_ctx_create", "sr_ctx_destroy", "sr_last_error", "sr_version", "sr_host_alloc", "sr_host_free",
     "sr_ctx_stream", "sr_ctx_sync", "sr_timer_start", "sr_timer_stop", "sr_kernel_launches", "sr_last_kernel",
     "sr_block_search", "sr_block_search_batch", "sr_pair_create", "sr_pair_destroy", "sr_pair_upload",
-    "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block",
+    "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block", "sr_search_left_disparity",
     "sr_search_effective_evals", "sr_remove_outliers", "sr_box_blur", "sr_scale", "sr_disparity_to_depth",
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
     "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
@@ -232,6 +232,12 @@ class Pair:
                                                       C.c_size_t(out.strides[0]), int(row0), int(row1)))
         return out
 
+    def left_disparity(self):
+        """int32 left-referenced map of the last lr_check run (sr_search_left_disparity)."""
+        out = np.zeros((self.h1, self.w1), np.int32)
+        self.ctx.check(self.ctx._l.sr_search_left_disparity(self.ctx.h, self.h, C.c_void_p(out.ctypes.data), C.c_size_t(out.strides[0])))
+        return out
+
     def max_block(self):
         v = C.c_int()
         self.ctx.check(self.ctx._l.sr_search_max_block(self.ctx.h, self.h, C.byref(v)))
@@ -268,3 +274,29 @@ def block_search(ctx, left, right, params, out=None, return_max_block=False):
     ctx.check(ctx._l.sr_block_search(ctx.h, C.byref(li), C.byref(ri), C.byref(params), C.c_void_p(out.ctypes.data),
                                      C.c_size_t(out.strides[0]), C.byref(mb)))
     return (out, mb.value) if return_max_block else out
+
+
+def block_search_batch(ctx, lefts, rights, params, outs):
+    """sr_block_search_batch: n pairs of one shape, pipelined H2D / kernels / D2H (config 5).
+    lefts/rights: sequences of HxWx3 uint8 arrays; outs: sequence of HxW float64 arrays (written)."""
+    n = len(lefts)
+    if len(rights) != n or len(outs) != n:
+        raise SrError(E_BADARG, "block_search_batch: lefts, rights and outs differ in length")
+    if n == 0:
+        return outs
+    Ls = (SrImage * n)()
+    Rs = (SrImage * n)()
+    keep = []
+    for i in range(n):
+        la, li = image(lefts[i])
+        ra, ri = image(rights[i])
+        keep += [la, ra]
+        Ls[i] = li
+        Rs[i] = ri
+    pitch = outs[0].strides[0]
+    for o in outs:
+        if o.dtype != np.float64 or o.strides[0] != pitch or o.strides[1] != 8:
+            raise SrError(E_BADARG, "block_search_batch: outputs must be float64 with one common row pitch")
+    optrs = (C.c_void_p * n)(*[o.ctypes.data for o in outs])
+    ctx.check(ctx._l.sr_block_search_batch(ctx.h, n, Ls, Rs, C.byref(params), optrs, C.c_size_t(pitch)))
+    return outs

@@ -145,6 +145,7 @@ int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row
     if (rc != SR_OK) return rc;
     SR_CUDA(ctx, cudaSetDevice(ctx->device));
     pair->evals_valid = false;
+    pair->disp_left = nullptr;
     {
         int init0[2] = {p->block, SR_OK};   // "max block size" (BlockSearch.cpp:98) and the device status word
         SR_CUDA(ctx, cudaMemcpyAsync(pair->maxblock, init0, sizeof init0, cudaMemcpyHostToDevice, ctx->stream));
@@ -249,6 +250,16 @@ int sr_search_max_block(sr_ctx* ctx, sr_pair* pair, int* max_block) {
     if (!ctx || !pair || !max_block) return SR_E_BADARG;
     SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     SR_CUDA(ctx, cudaMemcpy(max_block, pair->maxblock, sizeof(int), cudaMemcpyDeviceToHost));
+    return SR_OK;
+}
+
+int sr_search_left_disparity(sr_ctx* ctx, sr_pair* pair, int32_t* disp_left, size_t out_pitch) {
+    if (!ctx || !pair || !disp_left) return sr_fail(ctx, SR_E_BADARG, "sr_search_left_disparity: NULL argument");
+    if (!pair->disp_left) return sr_fail(ctx, SR_E_BADARG, "the last run had no left-right check");
+    size_t rowb = (size_t)pair->w1 * sizeof(int32_t);
+    if (out_pitch < rowb) return sr_fail(ctx, SR_E_BADARG, "output pitch %zu smaller than a row (%zu)", out_pitch, rowb);
+    SR_CUDA(ctx, cudaMemcpy2DAsync(disp_left, out_pitch, pair->disp_left, rowb, rowb, pair->h1, cudaMemcpyDeviceToHost, ctx->stream));
+    SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return SR_OK;
 }
 

@@ -138,6 +138,25 @@ __global__ void __launch_bounds__(128) ext_from_planes_kernel(const uint32_t* __
     if (subpix) subpix[o] = dsub;
 }
 
+// Left-referenced winners from the key planes of the tile search on the mirror-packed pair:
+// output column xc of that search is left-image column w1-1-xc (see sr_search_run_ext).
+__global__ void __launch_bounds__(128) left_from_mirror_planes_kernel(const uint32_t* __restrict__ Lp, int pitchL, int w1, int h1,
+                                                                      int height, const uint32_t* __restrict__ planes, size_t stride,
+                                                                      int npass, int dbase, int* __restrict__ disp) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= w1) return;
+    int dbest = 0;
+    if (y < height && (__ldg(Lp + (size_t)y * pitchL + x) & 0xFFFFFFu) != 0) {
+        size_t o = (size_t)y * w1 + (w1 - 1 - x);
+        uint32_t bc = 0xFFFFFFFFu;
+        for (int p = 0; p < npass; p++) {
+            uint32_t k = __ldg(planes + (size_t)p * stride + o);
+            if (k != 0xFFFFFFFFu && (k >> 6) < bc) { bc = k >> 6; dbest = dbase + 64 * p + (int)(k & 63u); }
+        }
+    }
+    disp[(size_t)y * w1 + x] = dbest;
+}
+
 // LR check + conversion to the CV_64F output map.
 __global__ void ext_finish_kernel(const int* __restrict__ disp_r, const float* __restrict__ subpix, int w2, int h2,
                                   const int* __restrict__ disp_l, int w1, int h1, int row0, double* __restrict__ out) {
@@ -208,11 +227,46 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
     }
     ctx->last_kernel = tiled ? "tile+ext" : "ext-direct";
     if (p->lr_check) {
-        ExtGeom gl{w1, h1, w2, h2, h1 < h2 ? h1 : h2, half, dlo, dhi, 1, p->cost, 0};
-        ext_direct_kernel<<<dim3(cdiv(w1, 128), h1), 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, gl,
-                                                                             disp_l, nullptr);
-        SR_LAUNCHED(ctx);
+        // Left-referenced search (window [x-l, x+r) on the left image, partner at x - d, break when the
+        // partner window leaves the right image on the left).  With both images mirror-packed about the
+        // left width (stored[s] = image[w1-2-s]) and the roles swapped, the right-referenced tile kernel
+        // computes exactly this search: its window [xc-h, xc+h) covers left columns (x-h-1, x+h-1] ->
+        // [x-h, x+h) for x = w1-1-xc, its column range [0, w1-1) is the left image's, and its break rule
+        // d < w1 - xc - min(w1-1-xc, h) is d <= x - min(x, h).  Needs w1 <= w2 (no partner beyond R).
+        bool mirrored = false;
+        if (p->cost != SR_COST_NCC && half >= 1 && half <= 8 && w1 > 1 && h1 > 1 && w1 <= w2) {
+            int rc;
+            if (!pair->Lm.base) {
+                if ((rc = sr_alloc_packed(ctx, &pair->Lm, w1, h1, w1 + 704)) != SR_OK) return rc;
+                if ((rc = sr_alloc_packed(ctx, &pair->Rm, w1, h2, w1 + 704)) != SR_OK) return rc;
+            }
+            if ((rc = sr_launch_pack_mirror(ctx, pair->rawL, (size_t)w1 * 3, w1, h1, w1, &pair->Lm)) != SR_OK) return rc;
+            if ((rc = sr_launch_pack_mirror(ctx, pair->rawR, (size_t)w2 * 3, w2, h2, w1, &pair->Rm)) != SR_OK) return rc;
+            SearchGeom sg;
+            sg.w1 = w1; sg.h1 = h2; sg.w2 = w1; sg.h2 = h1; sg.height = g.height; sg.block = p->block; sg.half = half;
+            sg.dlo = dlo; sg.dhi = dhi > w1 ? w1 : dhi; if (sg.dhi < sg.dlo) sg.dhi = sg.dlo;
+            sg.row0 = 0; sg.row1 = h1;
+            PackedImage keepL = pair->L, keepR = pair->R;
+            pair->L = pair->Rm; pair->R = pair->Lm;   // tile roles: "left" = searched image, "right" = reference image
+            int handled = sr_launch_search_tile(ctx, pair, sg, p->cost, 0);
+            pair->L = keepL; pair->R = keepR;
+            if (handled < 0) return handled;
+            if (handled) {
+                mirrored = true;
+                left_from_mirror_planes_kernel<<<dim3(cdiv(w1, 128), h1), 128, 0, ctx->stream>>>(
+                    pair->L.px, pair->L.pitch, w1, h1, g.height, pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase, disp_l);
+                SR_LAUNCHED(ctx);
+                ctx->last_kernel = tiled ? "tile+ext+mirror" : "ext-direct+mirror";
+            }
+        }
+        if (!mirrored) {
+            ExtGeom gl{w1, h1, w2, h2, h1 < h2 ? h1 : h2, half, dlo, dhi, 1, p->cost, 0};
+            ext_direct_kernel<<<dim3(cdiv(w1, 128), h1), 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, gl,
+                                                                                 disp_l, nullptr);
+            SR_LAUNCHED(ctx);
+        }
     }
+    pair->disp_left = disp_l;
     ext_finish_kernel<<<dim3(cdiv(w2, 128), row1 - row0), 128, 0, ctx->stream>>>(disp_r, subpix, w2, h2, disp_l, w1, h1, row0, pair->out);
     SR_LAUNCHED(ctx);
     return SR_OK;

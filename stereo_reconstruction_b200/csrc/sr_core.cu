@@ -158,7 +158,30 @@ int sr_launch_pack(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int
     return sr_launch_pack_rows(ctx, raw, raw_pitch, w, 0, h, img);
 }
 
-static int alloc_packed(sr_ctx* ctx, PackedImage* img, int w, int h, int padr) {
+__global__ void pack_mirror_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, int w, int wref,
+                                   uint32_t* __restrict__ dst, int pitch_px, int padl) {
+    int xp = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = blockIdx.y;
+    if (xp >= pitch_px) return;
+    int x = wref - 2 - (xp - padl);   // source column of stored column s = xp - padl
+    uint32_t v = 0;
+    if (x >= 0 && x < w) {
+        const uint8_t* p = raw + (size_t)y * raw_pitch + 3 * (size_t)x;
+        v = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
+    }
+    dst[(size_t)y * pitch_px + xp] = v;
+}
+
+int sr_launch_pack_mirror(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int h, int wref, PackedImage* img) {
+    dim3 grid(cdiv(img->pitch, 256), h);
+    pack_mirror_kernel<<<grid, 256, 0, ctx->stream>>>(raw, raw_pitch, w, wref, img->base, img->pitch, SR_PADL);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
+int sr_alloc_packed(sr_ctx* ctx, PackedImage* img, int w, int h, int padr);
+static int alloc_packed(sr_ctx* ctx, PackedImage* img, int w, int h, int padr) { return sr_alloc_packed(ctx, img, w, h, padr); }
+int sr_alloc_packed(sr_ctx* ctx, PackedImage* img, int w, int h, int padr) {
     img->w = w; img->h = h;
     img->pitch = ((SR_PADL + w + padr + 31) / 32) * 32;
     SR_CUDA(ctx, cudaMalloc((void**)&img->base, (size_t)img->pitch * h * sizeof(uint32_t)));
@@ -208,7 +231,7 @@ int sr_pair_create(sr_ctx* ctx, int w1, int h1, int w2, int h2, sr_pair** out) {
 void sr_pair_destroy(sr_ctx* ctx, sr_pair* p) {
     if (!p) return;
     if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
-    cudaFree(p->L.base); cudaFree(p->R.base); cudaFree(p->rawL); cudaFree(p->rawR);
+    cudaFree(p->L.base); cudaFree(p->R.base); cudaFree(p->Lm.base); cudaFree(p->Rm.base); cudaFree(p->rawL); cudaFree(p->rawR);
     cudaFree(p->best); cudaFree(p->c0); cudaFree(p->cr); cudaFree(p->dr); cudaFree(p->nwin);
     cudaFree(p->bits); cudaFree(p->alt); cudaFree(p->out); cudaFree(p->outf); cudaFree(p->maxblock);
     delete p;

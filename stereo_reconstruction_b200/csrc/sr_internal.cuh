@@ -55,6 +55,7 @@ struct sr_pair {
     int w1 = 0, h1 = 0, w2 = 0, h2 = 0;
     uint8_t *rawL = nullptr, *rawR = nullptr;  // BGR as uploaded, tight pitch 3*w
     PackedImage L, R;
+    PackedImage Lm, Rm;        // mirror-packed copies (stored[s] = image[w1-2-s]) for the left-referenced tile search
     int pad_disp = 0;          // right padding of L covers this many disparities
     // per-pixel records of the reference-side (output) image
     int ow = 0, oh = 0;        // output size (RIGHT/LINEAR: w2 x h2; LEFT: w1 x h1)
@@ -74,6 +75,7 @@ struct sr_pair {
     size_t npx_cap = 0;
     int last_row0 = 0, last_row1 = 0;
     bool evals_valid = false;
+    const int* disp_left = nullptr;       // left-referenced map of the last lr_check run (ctx scratch)
     SearchGeom last_geom;
 };
 
@@ -99,6 +101,9 @@ static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 // ---- launchers implemented in the .cu files (all asynchronous on ctx->stream) ----
 int sr_launch_pack(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int h, PackedImage* img);
 // rows [y0, y1) only (raw points at row 0 of the device copy)
+// mirror packing about the left image's width: dst[s] = src[wref-2-s] (0 outside the source image)
+int sr_launch_pack_mirror(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int h, int wref, PackedImage* img);
+int sr_alloc_packed(sr_ctx* ctx, PackedImage* img, int w, int h, int padr);
 int sr_launch_pack_rows(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int y0, int y1, PackedImage* img);
 
 // Fast path: fixed window, SSD/SAD, first minimum over [dlo,dhi) -> pair->best.

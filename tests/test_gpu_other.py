@@ -207,3 +207,37 @@ def test_batch_api(sr, ctx, orc):
     for i, (L, R) in enumerate(pairs):
         _, _, sp = orc.search_ext(L, R, 7, 0, D, orc.COST_SAD, want_subpix=True)
         np.testing.assert_array_equal(outs[i], sp.astype(np.float64))
+
+
+@pytest.mark.parametrize("cost", [0, 1])
+@pytest.mark.parametrize("shape", [
+    # (w1, h1, w2, h2, block, min_d, max_d, quant)
+    (280, 50, 280, 50, 9, 0, 40, False),
+    (280, 50, 280, 50, 8, 0, 40, True),      # even block, frequent ties
+    (523, 61, 523, 61, 17, 2, 70, False),    # min_disp > 0, widest tile window
+    (300, 48, 340, 48, 5, 0, 33, True),      # w1 < w2: still the mirrored tile search
+    (340, 48, 300, 48, 7, 0, 33, False),     # w1 > w2: per-pixel fallback (partner windows beyond the right image)
+])
+def test_ext_left_referenced_map(sr, ctx, orc, cost, shape):
+    """The left-referenced search behind the LR check (mirror-packed tile search) equals the oracle's
+    left_ref search pixel for pixel -- not only where the consistency test looks."""
+    w1, h1, w2, h2, block, dlo, dhi, quant = shape
+    w, h = max(w1, w2), max(h1, h2)
+    L, R = orc.synth_pair(29, 0, w, h, dlo, dhi, quant)
+    L = np.ascontiguousarray(L[:h1, :w1]); R = np.ascontiguousarray(R[:h2, :w2])
+    L[7:12, 100:130] = 0                        # black reference pixels on the left image are skipped
+    R[20:25, 50:90] = 0
+    capi = sr.capi
+    pair = capi.Pair(ctx, w1, h1, w2, h2)
+    pair.upload(L, R)
+    p = capi.search_params(block=block, min_disp=dlo, max_disp=dhi, smooth=1.0, cost=cost, lr_check=True)
+    pair.run(p)
+    got = pair.download(p)
+    got_l = pair.left_disparity()
+    dr, _, _ = orc.search_ext(L, R, block, dlo, dhi, cost)
+    dl, _, _ = orc.search_ext(L, R, block, dlo, dhi, cost, left_ref=True)
+    np.testing.assert_array_equal(got_l, dl)
+    np.testing.assert_array_equal(got, orc.lr_check(dr, dl).astype(np.float64))
+    if w1 <= w2:
+        assert "mirror" in ctx.last_kernel
+    pair.close()
