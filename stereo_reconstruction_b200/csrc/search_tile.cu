@@ -196,7 +196,6 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int pass = (int)(gridDim.z - 1 - blockIdx.z);        // heaviest (masked / ragged) passes are scheduled first
     const int dcta = a.dbase + pass * (DT * NW);               // first disparity of the pass (multiple of 4)
     const int d0 = dcta + DT * warp;                            // this warp's 4 disparities
-    const bool active = d0 < a.dhi;                             // warps with at least one d < dhi
     const bool late_sub = (warp >> 2) & 1;
     const bool red_late = a.red_mode && ((warp >> 3) & 1);   // spreads the LDS burst of the key merge over the iteration
 
@@ -212,6 +211,20 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
         if (x >= 0 && x < a.w2) dlim_min = min(dlim_min, min(a.dhi, a.w1 - x - min(a.w2 - x - 1, h)));
     }
     const bool needmask = __any_sync(0xffffffffu, d0 < a.dlo || d0 + DT - 1 >= dlim_min);
+    // The break rule cuts a triangle off the (x, d) plane at the right image edge: the largest limit of
+    // the tile (its first output column) decides which warps / whole CTAs have no candidate at all.
+    const int x_first = max(CB + h, 0);                         // first output column of the tile inside the image (the limit never grows with x)
+    const int dlim_tile = min(a.dhi, a.w1 - x_first - min(a.w2 - x_first - 1, h));
+    const bool active = d0 < dlim_tile;                         // warps with at least one candidate
+    if (dcta >= dlim_tile) {
+        // nothing to search in this (tile, pass): the planes still get their "no candidate" keys
+        for (int y = yb0 + warp; y < yb1; y += NW)
+            for (int q = lane; q < TILE_OUT; q += 32) {
+                int x = CB + h + q;
+                if (x >= 0 && x < a.w2) a.planes[(size_t)pass * a.plane_stride + (size_t)y * a.w2 + x] = 0xFFFFFFFFu;
+            }
+        return;
+    }
 
     // Shared-memory addressing, all 32-bit byte addresses: a hot-loop load is
     // "uniform (slot base + chunk offset of this warp) + per-thread lane offset".
