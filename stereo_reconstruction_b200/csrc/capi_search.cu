@@ -199,7 +199,7 @@ int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row
         if (handled) {
             ctx->last_kernel = "tile";
             if (smoothing && (rc = sr_launch_cost0(ctx, pair, g, p->cost)) != SR_OK) return rc;
-            rc = sr_launch_resolve_right(ctx, pair, g, p->smooth, 0, smoothing ? 1 : 0);
+            rc = sr_launch_resolve_right(ctx, pair, g, p->smooth, 0, smoothing ? 2 : 0);   // 2: c0 is the u32 plane of sr_launch_cost0
         }
     }
     if (!handled) {

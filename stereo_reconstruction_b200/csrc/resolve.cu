@@ -42,7 +42,13 @@ __device__ __forceinline__ PixRec load_rec(int from_direct, int have_c0, size_t 
         }
         r.cr = bc == 0xFFFFFFFFu ? SR_NONE64 : (unsigned long long)bc;
         r.dr = bd;
-        r.c0 = have_c0 ? c0[i] : SR_NONE64;
+        if (have_c0 == 2) {
+            // u32 plane written by the tile kernel: raw window cost at d == 0; it is a candidate when the
+            // break rule lets d == 0 through (x + r < w1)
+            r.c0 = (!r.skip && x + rr < g.w1) ? (unsigned long long)((const uint32_t*)c0)[i] : SR_NONE64;
+        } else {
+            r.c0 = have_c0 ? c0[i] : SR_NONE64;
+        }
     }
     return r;
 }
@@ -67,7 +73,7 @@ __global__ void resolve_plain_kernel(SearchGeom g, int from_direct, int have_c0,
 }
 
 // Phase A of the smoothing pass: bit planes a0,a1,a2 (ballot words) and the alternative value.
-__global__ void smooth_prepare_kernel(SearchGeom g, int from_direct, double s, Planes best,
+__global__ void smooth_prepare_kernel(SearchGeom g, int from_direct, int have_c0, double s, Planes best,
                                       const unsigned long long* __restrict__ c0, const unsigned long long* __restrict__ cr,
                                       const int* __restrict__ dr, const int* __restrict__ nwin,
                                       const uint32_t* __restrict__ Rp, int pitchR, uint32_t* __restrict__ bits,
@@ -77,7 +83,7 @@ __global__ void smooth_prepare_kernel(SearchGeom g, int from_direct, double s, P
     bool a0 = false, a1 = false, a2 = false;
     if (x < g.w2) {
         size_t i = (size_t)y * g.w2 + x;
-        PixRec r = load_rec(from_direct, 1, i, x, y, best, c0, cr, dr, nwin, Rp, pitchR, g);
+        PixRec r = load_rec(from_direct, have_c0, i, x, y, best, c0, cr, dr, nwin, Rp, pitchR, g);
         double v;  // value when d = 0 does not win
         if (r.skip) { v = 0.0; }
         else if (r.n == 0 || r.cr == SR_NONE64) v = (r.n != 0 && r.c0 != SR_NONE64) ? 0.0 : (double)(0 - x);
@@ -175,6 +181,75 @@ __global__ void __launch_bounds__(SMOOTH_THREADS) smooth_raster_kernel(int rows,
     }
 }
 
+// Phase B, fast form: ONE warp walks the rows (rows are strictly sequential, and within a row the only
+// cross-word dependency is a one-bit carry).  Lane l owns the KW consecutive words l*KW .. l*KW+KW-1 of
+// every row, so the "row above" bits are its own registers; the carry crosses lanes through two ballots
+// (per-lane transfer function: carry-out for carry-in 0 / 1) and one adder-style chain on the ballot
+// words.  The a0/a1/a2 bit planes of the coming rows are prefetched into a shared-memory ring with
+// 4-byte cp.async (they do not depend on earlier rows), which hides the L2/HBM latency that dominated
+// the one-CTA version (~1.1 us/row -> ~0.1 us/row).
+#define RASTER_PF 8
+template <int KW>
+__global__ void __launch_bounds__(32) smooth_raster_warp_kernel(int rows, int words, const uint32_t* __restrict__ bits,
+                                                                uint32_t* __restrict__ zbits, int monotone) {
+    extern __shared__ uint32_t ring[];   // RASTER_PF x (32*KW*3) words
+    const int lane = threadIdx.x;
+    const int w0 = lane * KW;
+    const int row_words = 32 * KW * 3;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(ring);
+    auto prefetch = [&](int y) {
+        if (y < rows) {
+            uint32_t dst = sbase + 4u * ((y % RASTER_PF) * row_words + w0 * 3);
+            const uint32_t* src = bits + ((size_t)y * words + w0) * 3;
+#pragma unroll
+            for (int i = 0; i < 3 * KW; i++)
+                if (w0 + i / 3 < words) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst + 4u * i), "l"(src + i) : "memory");
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+#pragma unroll 1
+    for (int y = 0; y < RASTER_PF - 1; y++) prefetch(y);
+    uint32_t up[KW];
+#pragma unroll
+    for (int k = 0; k < KW; k++) up[k] = 0;   // y == 0 has no row above: the rule needs y >= 1
+#pragma unroll 1
+    for (int y = 0; y < rows; y++) {
+        prefetch(y + RASTER_PF - 1);
+        asm volatile("cp.async.wait_group %0;\n" ::"n"(RASTER_PF - 1) : "memory");
+        const uint32_t* r = ring + (y % RASTER_PF) * row_words + w0 * 3;
+        uint32_t F0[KW], F1[KW];
+#pragma unroll
+        for (int k = 0; k < KW; k++) {
+            uint32_t a0 = 0, a1 = 0, a2 = 0;
+            if (w0 + k < words) { a0 = r[3 * k]; a1 = r[3 * k + 1]; a2 = r[3 * k + 2]; }
+            F0[k] = (up[k] & a1) | (~up[k] & a0);
+            F1[k] = (up[k] & a2) | (~up[k] & a1);
+        }
+        // transfer function of this lane's KW words
+        uint32_t c0 = 0, c1 = 1;
+#pragma unroll
+        for (int k = 0; k < KW; k++) {
+            c0 = chain_word(F0[k], F1[k], c0, monotone) >> 31;
+            c1 = chain_word(F0[k], F1[k], c1, monotone) >> 31;
+        }
+        uint32_t G = __ballot_sync(0xffffffffu, c0), P = __ballot_sync(0xffffffffu, c1);
+        uint32_t zz = chain_word(G, P, 0u, monotone);         // carry out of every lane (x == 0 has carry-in 0)
+        uint32_t c = ((zz << 1) >> lane) & 1u;                // carry into this lane
+#pragma unroll
+        for (int k = 0; k < KW; k++) {
+            uint32_t z = chain_word(F0[k], F1[k], c, monotone);
+            c = z >> 31;
+            up[k] = z;
+            if (w0 + k < words) zbits[(size_t)y * words + w0 + k] = z;
+        }
+    }
+}
+
+template <int KW>
+static void launch_raster_warp(cudaStream_t st, int rows, int words, const uint32_t* bits, uint32_t* zb, int monotone) {
+    smooth_raster_warp_kernel<KW><<<1, 32, RASTER_PF * 32 * KW * 3 * sizeof(uint32_t), st>>>(rows, words, bits, zb, monotone);
+}
+
 __global__ void smooth_expand_kernel(SearchGeom g, int words, const uint32_t* __restrict__ zbits,
                                      const double* __restrict__ alt, double* __restrict__ out) {
     int x = blockIdx.x * blockDim.x + threadIdx.x;
@@ -206,12 +281,16 @@ int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, dou
     uint32_t* zb = pair->bits + (size_t)rows * words * 3;
     dim3 gridw(words, rows);
     smooth_prepare_kernel<<<dim3(cdiv(words * 32, 128), rows), 128, 0, ctx->stream>>>(
-        g, from_direct, smooth, pl, pair->c0, pair->cr, pair->dr, pair->nwin, pair->R.px, pair->R.pitch, pair->bits,
+        g, from_direct, have_c0, smooth, pl, pair->c0, pair->cr, pair->dr, pair->nwin, pair->R.px, pair->R.pitch, pair->bits,
         words, pair->alt);
     SR_LAUNCHED(ctx);
     // s <= 1 makes a0 <= a1 <= a2 (more multiplications -> smaller cost): adder-style carries
     int monotone = (smooth >= 0.0 && smooth <= 1.0) ? 1 : 0;
-    smooth_raster_kernel<<<1, SMOOTH_THREADS, 0, ctx->stream>>>(rows, words, 0, pair->bits, zb, monotone);
+    if (words <= 32) launch_raster_warp<1>(ctx->stream, rows, words, pair->bits, zb, monotone);
+    else if (words <= 64) launch_raster_warp<2>(ctx->stream, rows, words, pair->bits, zb, monotone);
+    else if (words <= 128) launch_raster_warp<4>(ctx->stream, rows, words, pair->bits, zb, monotone);
+    else if (words <= 256) launch_raster_warp<8>(ctx->stream, rows, words, pair->bits, zb, monotone);
+    else smooth_raster_kernel<<<1, SMOOTH_THREADS, 0, ctx->stream>>>(rows, words, 0, pair->bits, zb, monotone);
     SR_LAUNCHED(ctx);
     smooth_expand_kernel<<<grid, 128, 0, ctx->stream>>>(g, words, zb, pair->alt, pair->out);
     SR_LAUNCHED(ctx);

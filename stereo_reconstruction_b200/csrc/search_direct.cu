@@ -120,31 +120,65 @@ int sr_launch_search_direct(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int
     return SR_OK;
 }
 
-// cost at d == 0 for the fixed (border-clamped) window -> c0 (SR_NONE64 where d == 0 is not a
-// candidate: black pixel, row beyond min(h1,h2), or x + r >= w1).
+// Cost at d == 0 for the fixed (border-clamped) window -> u32 plane in pair->c0 (the smoothing rule's
+// "stay at 0" candidate; whether d == 0 is a candidate at all -- black pixel, break rule -- is decided
+// by the resolve kernels).  Separable box sum, O(1) per pixel: the window [x-l, x+r) x [y-u, y+dn) is the
+// fixed window [x-h, x+h) x [y-h, y+h) with the pointwise cost forced to 0 outside columns [0, w2-1)
+// and rows [0, h2-1) (same identity as the tile kernel).
 template <int COST>
-__global__ void __launch_bounds__(128) cost0_kernel(const uint32_t* __restrict__ Lp, int pitchL,
-                                                    const uint32_t* __restrict__ Rp, int pitchR, SearchGeom g,
-                                                    unsigned long long* __restrict__ c0) {
+__device__ __forceinline__ uint32_t pcost0(const uint32_t* __restrict__ Lp, int pitchL, const uint32_t* __restrict__ Rp,
+                                           int pitchR, int y, int x) {
+    uint32_t l = __ldg(Lp + (size_t)y * pitchL + x), r = __ldg(Rp + (size_t)y * pitchR + x);
+    uint32_t ad = __vabsdiffu4(l, r);
+    return COST == SR_COST_SAD ? __dp4a(ad, 0x01010101u, 0u) : __dp4a(ad, ad, 0u);
+}
+
+#define C0_BAND 32
+template <int COST>
+__global__ void __launch_bounds__(128) cost0_vertical_kernel(const uint32_t* __restrict__ Lp, int pitchL,
+                                                             const uint32_t* __restrict__ Rp, int pitchR, SearchGeom g,
+                                                             uint32_t* __restrict__ vsum) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y0 = g.row0 + C0_BAND * blockIdx.y, y1 = min(y0 + C0_BAND, g.row1);
+    if (x >= g.w2) return;
+    const int h = g.half;
+    const bool col_ok = x < g.w2 - 1;
+    auto row_ok = [&](int r) { return r >= 0 && r < g.h2 - 1; };
+    uint32_t s = 0;
+    if (col_ok)
+        for (int r = y0 - h; r < y0 + h - 1; r++)
+            if (row_ok(r)) s += pcost0<COST>(Lp, pitchL, Rp, pitchR, r, x);
+    for (int y = y0; y < y1; y++) {
+        if (col_ok && row_ok(y + h - 1)) s += pcost0<COST>(Lp, pitchL, Rp, pitchR, y + h - 1, x);
+        vsum[(size_t)y * g.w2 + x] = s;
+        if (col_ok && row_ok(y - h)) s -= pcost0<COST>(Lp, pitchL, Rp, pitchR, y - h, x);
+    }
+}
+
+__global__ void __launch_bounds__(128) cost0_horizontal_kernel(const uint32_t* __restrict__ vsum, SearchGeom g,
+                                                               uint32_t* __restrict__ c0) {
     int x = blockIdx.x * blockDim.x + threadIdx.x;
     int y = g.row0 + blockIdx.y;
     if (x >= g.w2 || y >= g.row1) return;
-    size_t i = (size_t)y * g.w2 + x;
-    unsigned long long c = SR_NONE64;
-    if (y < g.height && (__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) != 0) {
-        int l = min(x, g.half), r = min(g.w2 - x - 1, g.half), u = min(y, g.half), dn = min(g.h2 - y - 1, g.half);
-        if (x + r < g.w1) c = window_cost<COST>(Lp, pitchL, Rp, pitchR, y - u, x - l, x - l, l + r, u + dn);
-    }
-    c0[i] = c;
+    const uint32_t* row = vsum + (size_t)y * g.w2;
+    uint32_t s = 0;
+    int xa = max(x - g.half, 0), xb = min(x + g.half, g.w2);
+    for (int i = xa; i < xb; i++) s += __ldg(row + i);
+    c0[(size_t)y * g.w2 + x] = s;
 }
 
 int sr_launch_cost0(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost) {
-    dim3 grid(cdiv(g.w2, 128), g.row1 - g.row0);
-    if (grid.y == 0) return SR_OK;
+    int rows = g.row1 - g.row0;
+    if (rows <= 0) return SR_OK;
+    uint32_t* vsum = (uint32_t*)sr_scratch(ctx, 1, pair->npx_cap * sizeof(uint32_t));
+    if (!vsum) return SR_E_CUDA;
+    dim3 gridv(cdiv(g.w2, 128), cdiv(rows, C0_BAND));
     if (cost == SR_COST_SAD)
-        cost0_kernel<SR_COST_SAD><<<grid, 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, pair->c0);
+        cost0_vertical_kernel<SR_COST_SAD><<<gridv, 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, vsum);
     else
-        cost0_kernel<SR_COST_SSD_L2><<<grid, 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, pair->c0);
+        cost0_vertical_kernel<SR_COST_SSD_L2><<<gridv, 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, vsum);
+    SR_LAUNCHED(ctx);
+    cost0_horizontal_kernel<<<dim3(cdiv(g.w2, 128), rows), 128, 0, ctx->stream>>>(vsum, g, (uint32_t*)pair->c0);
     SR_LAUNCHED(ctx);
     return SR_OK;
 }

@@ -112,7 +112,7 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
 // Universal path: per-pixel windows (var_block), any size; wide costs -> c0/cr/dr/nwin.
 int sr_launch_search_direct(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int var_block,
                             double thres, int want_c0);
-// cost at d == 0 for the fixed window -> pair->c0
+// cost at d == 0 for the fixed window -> pair->c0 as a u32 plane (resolve: have_c0 == 2)
 int sr_launch_cost0(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost);
 // best/c0 (tile path) or c0/cr/dr/nwin (direct path) -> pair->out, reference rules.
 int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, double smooth, int from_direct,
