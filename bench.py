@@ -40,7 +40,7 @@ WORKLOADS = {
 OPS_PER_EVAL = {"ssd": 8, "sad": 7}
 # dram__bytes_read.sum + dram__bytes_write.sum of the search kernel from the committed ncu capture
 # (profiles/), per launch, keyed by workload; None = not captured for this workload
-NCU_TRAFFIC = {}
+NCU_TRAFFIC = {"4k512": 279182336 + 235187968}   # profiles/r01_tile_sad_4k512_ncu_full.csv (read + write bytes)
 
 
 def parse():
@@ -67,7 +67,7 @@ class ClockSampler:
         self.proc = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
         except Exception:
@@ -191,6 +191,9 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        # stdout carries exactly one JSON line: NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION) goes to stderr
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     w, h, D, block, cost = WORKLOADS[args.workload]
     cost = args.cost or cost
@@ -211,6 +214,10 @@ def main():
     full = sharding.result_tensor(pair, dev)
     total_evals = synth.effective_evals(w, w, h, block, 0, D)
 
+    half = (block - 1) // 2
+    h2d_rows = h if world == 1 else sum(min(b1 + half + 1, h) - max(b0 - half, 0)
+                                        for b0, b1 in (sharding.band_rows(h, r, world) for r in range(world)))
+
     def barrier():
         ctx.sync()
         torch.cuda.synchronize(dev)
@@ -227,12 +234,14 @@ def main():
         if world == 1:
             capi.block_search(ctx, Lp, Rp, params, out=outp)          # sr_block_search: H2D + kernels + D2H
         else:
-            pair.upload(Lp, Rp)
-            pair.run(params, r0, r1)
+            # every rank: H2D of its band's image rows (+ halo), band search, by row chunks (sr_pair_search_band);
+            # rank 0 streams its own band back to the host inside that pipeline, the others keep theirs in HBM
+            pair.search_band(Lp, Rp, params, r0, r1, out=outp if rank == 0 else None)
             with torch.cuda.stream(ext):
                 sharding.gather_bands(full, h, rank, world)
             if rank == 0:
-                pair.download(params, out=outp)
+                ext.synchronize()
+                pair.download(params, out=outp, row0=r1, row1=h)   # the gathered bands (rank 0 owns rows [0, r1))
             ctx.sync()
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -306,8 +315,8 @@ def main():
             "pairs_per_s": 1e3 / ms_per_step,
             "nominal_value": w * h * D / (ms_per_step * 1e-3) / 1e6,
             "e2e": {"value": total_evals / e2e_s / 1e6, "unit": "MDE/s", "ms_per_step": e2e_s * 1e3,
-                    "h2d_bytes_per_step": int(2 * w * h * 3 * world), "d2h_bytes_per_step": int(w * h * 8),
-                    "api": "sr_block_search (pinned host buffers)" if world == 1 else "sr_pair_upload + sr_search_run(band) + NCCL gather + sr_search_download"},
+                    "h2d_bytes_per_step": int(h2d_rows * w * 3 * 2), "d2h_bytes_per_step": int(w * h * 8),
+                    "api": "sr_block_search (pinned host buffers)" if world == 1 else "sr_pair_search_band (band rows + halo H2D, chunked) + NCCL gather + sr_search_download of the gathered bands"},
             "gpu_launches": int(launches),
             "kernel_family": ctx.last_kernel,
             "clocks": clocks,

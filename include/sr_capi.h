@@ -123,6 +123,14 @@ int sr_pair_upload(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_im
  * row-band sharding -- a band needs smooth == 1). */
 int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1);
 int sr_search_download(sr_ctx* ctx, sr_pair* pair, double* disp_out, size_t out_pitch, int row0, int row1);
+/* One rank's share of a row-band sharded pair, from host images (north_star: "by row bands with halo
+ * rows for single very large pairs"): uploads only the image rows that output rows [row0,row1) and their
+ * window halo read, searches the band and -- when disp_out is not NULL -- downloads it to rows
+ * [row0,row1) of disp_out; with pinned host buffers upload / search / download overlap by row chunks.
+ * disp_out == NULL leaves the band in HBM (sr_search_result_dev) for the device-side gather to rank 0.
+ * Blocking.  The band's result equals rows [row0,row1) of sr_block_search on the whole pair. */
+int sr_pair_search_band(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_image* right,
+                        const sr_search_params* p, int row0, int row1, double* disp_out, size_t out_pitch);
 /* Device pointer (double*, tightly packed rows of the output width) of the last result. */
 void* sr_search_result_dev(sr_ctx* ctx, sr_pair* pair);
 int sr_search_max_block(sr_ctx* ctx, sr_pair* pair, int* max_block);

@@ -48,7 +48,7 @@ SYMBOLS = [
     "sr_ctx_create", "sr_ctx_destroy", "sr_last_error", "sr_version", "sr_host_alloc", "sr_host_free",
     "sr_ctx_stream", "sr_ctx_sync", "sr_timer_start", "sr_timer_stop", "sr_kernel_launches", "sr_last_kernel",
     "sr_block_search", "sr_block_search_batch", "sr_pair_create", "sr_pair_destroy", "sr_pair_upload",
-    "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block", "sr_search_left_disparity",
+    "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block", "sr_search_left_disparity", "sr_pair_search_band",
     "sr_search_effective_evals", "sr_remove_outliers", "sr_box_blur", "sr_scale", "sr_disparity_to_depth",
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
     "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
@@ -230,6 +230,15 @@ class Pair:
             out = np.zeros((oh, ow), np.float64)
         self.ctx.check(self.ctx._l.sr_search_download(self.ctx.h, self.h, C.c_void_p(out.ctypes.data),
                                                       C.c_size_t(out.strides[0]), int(row0), int(row1)))
+        return out
+
+    def search_band(self, left, right, params, row0, row1, out=None):
+        """sr_pair_search_band: rows [row0,row1) from host images; out=None keeps the band in HBM."""
+        la, li = image(left)
+        ra, ri = image(right)
+        optr, pitch = (C.c_void_p(out.ctypes.data), out.strides[0]) if out is not None else (C.c_void_p(None), 0)
+        self.ctx.check(self.ctx._l.sr_pair_search_band(self.ctx.h, self.h, C.byref(li), C.byref(ri), C.byref(params),
+                                                       int(row0), int(row1), optr, C.c_size_t(pitch)))
         return out
 
     def left_disparity(self):

@@ -37,16 +37,17 @@ static bool host_pinned(const void* p) {
     return pinned;
 }
 
-static int pipeline_chunks(const sr_pair* pair, const sr_search_params* p) {
+static int pipeline_chunks(const sr_pair* pair, const sr_search_params* p, int rows = -1) {
+    if (rows < 0) rows = pair->h2;
     const char* env = getenv("SR_PIPE_CHUNKS");   // tuning / test override
     int c = env ? atoi(env) : 0;
     if (c <= 0) {
-        // small pairs: one chunk (launch overheads dominate); large pairs: ~2.8 M right pixels per chunk
-        double px = (double)pair->w2 * pair->h2;
+        // small pairs: one chunk (launch overheads dominate); large pairs: ~1.3 M right pixels per chunk
+        double px = (double)pair->w2 * rows;
         c = (int)(px / 1.3e6);
         if (c > 8) c = 8;
     }
-    int maxc = pair->h2 / (4 * p->block + 16);
+    int maxc = rows / (4 * p->block + 16);
     if (c > maxc) c = maxc;
     return c < 1 ? 1 : c;
 }
@@ -62,13 +63,17 @@ static bool can_pipeline(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const
     return host_pinned(left->bgr) && host_pinned(right->bgr) && host_pinned(disp_out);
 }
 
+// rows [band0, band1) of the output only (row-band sharding: a rank uploads just the image rows its band
+// and the window halo need); disp_out == nullptr leaves the band in HBM (sr_search_result_dev) for a
+// device-side gather.
+
 static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_image* right,
-                                  const sr_search_params* p, double* disp_out, size_t out_pitch) {
-    const int nch = pipeline_chunks(pair, p);
+                                  const sr_search_params* p, double* disp_out, size_t out_pitch, int band0, int band1) {
+    const int nch = pipeline_chunks(pair, p, band1 - band0);
     const int half = (p->block - 1) / 2;
-    const int oh = pair->h2, ow = pair->w2;
+    const int oh = band1 - band0, ow = pair->w2;
     const size_t rowb = (size_t)ow * sizeof(double);
-    if (out_pitch < rowb) return sr_fail(ctx, SR_E_BADARG, "output pitch %zu smaller than a row (%zu)", out_pitch, rowb);
+    if (disp_out && out_pitch < rowb) return sr_fail(ctx, SR_E_BADARG, "output pitch %zu smaller than a row (%zu)", out_pitch, rowb);
     if (left->pitch < (size_t)left->w * 3 || right->pitch < (size_t)right->w * 3)
         return sr_fail(ctx, SR_E_BADARG, "image pitch smaller than a row");
     while ((int)ctx->pipe_ev.size() < 2 * nch + 1) {
@@ -83,14 +88,15 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     SR_CUDA(ctx, cudaStreamWaitEvent(s_up, ev_start, 0));
     SR_CUDA(ctx, cudaStreamWaitEvent(s_down, ev_start, 0));
     SR_CUDA(ctx, cudaStreamWaitEvent(ctx->aux[2], ev_start, 0));
-    int upL = 0, upR = 0, rc = SR_OK;
+    int up0 = band0 - half > 0 ? band0 - half : 0;   // first image row the band's windows read
+    int upL = up0 < pair->h1 ? up0 : pair->h1, upR = up0 < pair->h2 ? up0 : pair->h2, rc = SR_OK;
     const size_t rowL = (size_t)left->w * 3, rowR = (size_t)right->w * 3;
     for (int c = 0; c < nch && rc == SR_OK; c++) {
-        int r0 = (int)((long)oh * c / nch), r1 = (int)((long)oh * (c + 1) / nch);
+        int r0 = band0 + (int)((long)oh * c / nch), r1 = band0 + (int)((long)oh * (c + 1) / nch);
         // input rows this chunk needs: window rows [r0 - half, r1 + half) of both images
         int needR = r1 + half + 1 < pair->h2 ? r1 + half + 1 : pair->h2;
         int needL = r1 + half + 1 < pair->h1 ? r1 + half + 1 : pair->h1;
-        if (c == nch - 1) { needR = pair->h2; needL = pair->h1; }
+        if (c == nch - 1 && band1 >= pair->h2) { needR = pair->h2; needL = pair->h1; }
         {
             cudaStream_t saved = ctx->stream;
             ctx->stream = s_up;
@@ -120,6 +126,7 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
         rc = sr_search_run(ctx, pair, p, r0, r1);
         ctx->stream = compute;
         if (rc != SR_OK) break;
+        if (!disp_out) continue;
         SR_CUDA(ctx, cudaEventRecord(ctx->pipe_ev[2 * c + 1], cs));
         SR_CUDA(ctx, cudaStreamWaitEvent(s_down, ctx->pipe_ev[2 * c + 1], 0));
         cudaError_t e = cudaMemcpy2DAsync((char*)disp_out + (size_t)r0 * out_pitch, out_pitch, pair->out + (size_t)r0 * ow, rowb, rowb,
@@ -131,8 +138,8 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     cudaStreamSynchronize(ctx->aux[2]);
     cudaStreamSynchronize(s_down);
     if (rc != SR_OK) return rc;
-    pair->last_row0 = 0; pair->last_row1 = oh;
-    pair->last_geom.row0 = 0; pair->last_geom.row1 = oh;
+    pair->last_row0 = band0; pair->last_row1 = band1;
+    pair->last_geom.row0 = band0; pair->last_geom.row1 = band1;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return sr_cuda_check(ctx, e, "row-chunk pipeline");
     return SR_OK;
@@ -275,6 +282,29 @@ int sr_search_effective_evals(sr_ctx* ctx, sr_pair* pair, uint64_t* evals) {
     return SR_OK;
 }
 
+int sr_pair_search_band(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_image* right, const sr_search_params* p,
+                        int row0, int row1, double* disp_out, size_t out_pitch) {
+    if (!ctx || !pair || !left || !right || !p || !left->bgr || !right->bgr) return sr_fail(ctx, SR_E_BADARG, "sr_pair_search_band: NULL argument");
+    if (left->w != pair->w1 || left->h != pair->h1 || right->w != pair->w2 || right->h != pair->h2)
+        return sr_fail(ctx, SR_E_BADARG, "sr_pair_search_band: image sizes differ from the pair's");
+    int rc = validate(ctx, pair, p);
+    if (rc != SR_OK) return rc;
+    if (p->variant != SR_VARIANT_RIGHT) return sr_fail(ctx, SR_E_BADARG, "row bands are defined for the Right variant");
+    if (row0 < 0) row0 = 0;
+    if (row1 > pair->h2) row1 = pair->h2;
+    if (row1 <= row0) return SR_OK;
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    const double* pin_probe = disp_out ? disp_out : (const double*)left->bgr;
+    bool piped = can_pipeline(ctx, pair, left, right, p, pin_probe) && pipeline_chunks(pair, p, row1 - row0) >= 1;
+    if (piped) return block_search_pipelined(ctx, pair, left, right, p, disp_out, out_pitch, row0, row1);
+    // general form: whole upload, band search, band download
+    if ((rc = sr_pair_upload(ctx, pair, left, right)) != SR_OK) return rc;
+    if ((rc = sr_search_run(ctx, pair, p, row0, row1)) != SR_OK) return rc;
+    if (disp_out) return sr_search_download(ctx, pair, disp_out, out_pitch, row0, row1);
+    SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SR_OK;
+}
+
 int sr_block_search(sr_ctx* ctx, const sr_image* left, const sr_image* right, const sr_search_params* p,
                     double* disp_out, size_t out_pitch, int* max_block) {
     if (!ctx || !left || !right || !p || !disp_out) return sr_fail(ctx, SR_E_BADARG, "sr_block_search: NULL argument");
@@ -293,7 +323,7 @@ int sr_block_search(sr_ctx* ctx, const sr_image* left, const sr_image* right, co
         ctx->batch_pairs.push_back(pair);
     }
     if (validate(ctx, pair, p) == SR_OK && can_pipeline(ctx, pair, left, right, p, disp_out)) {
-        if ((rc = block_search_pipelined(ctx, pair, left, right, p, disp_out, out_pitch)) != SR_OK) return rc;
+        if ((rc = block_search_pipelined(ctx, pair, left, right, p, disp_out, out_pitch, 0, pair->h2)) != SR_OK) return rc;
         if (max_block) *max_block = p->block;   // fixed window: BlockSearch.cpp:98
         return SR_OK;
     }

@@ -126,3 +126,37 @@ def test_one_shot_row_chunk_pipeline(sr, ctx, orc, monkeypatch, cost, block, min
         np.testing.assert_array_equal(plain, want)
     finally:
         capi.free_pinned(lh); capi.free_pinned(rh); capi.free_pinned(oh_)
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_pair_search_band_from_host(sr, ctx, orc, monkeypatch, pinned):
+    """sr_pair_search_band (one rank's share of a row-band sharded pair): partial upload with halo rows,
+    band search, optional download -- the bands of a 3-way split reassemble to the oracle's full map."""
+    capi = sr.capi
+    w, h, D, block = 600, 301, 40, 9
+    L, R = synth(orc, w, h, 0, D, seed=13)
+    want = orc.block_search_right_fast(L, R, block, 0, D, 1.0, cost=1)
+    p = capi.search_params(block=block, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD)
+    monkeypatch.setenv("SR_PIPE_CHUNKS", "2")
+    hs = []
+    try:
+        if pinned:
+            Lh, a = capi.pinned_empty(L.shape, np.uint8); Rh, b = capi.pinned_empty(R.shape, np.uint8)
+            out, c = capi.pinned_empty((h, w), np.float64); hs = [a, b, c]
+            Lh[...] = L; Rh[...] = R
+        else:
+            Lh, Rh, out = L, R, np.zeros((h, w), np.float64)
+        out[...] = -3.0
+        for rank in range(3):
+            r0, r1 = capi.band_rows(h, rank, 3)
+            pair = capi.Pair(ctx, w, h, w, h)        # a fresh pair per "rank": nothing uploaded before
+            if rank == 1:                            # device-resident band + separate download
+                pair.search_band(Lh, Rh, p, r0, r1, out=None)
+                pair.download(p, out=out, row0=r0, row1=r1)
+            else:
+                pair.search_band(Lh, Rh, p, r0, r1, out=out)
+            pair.close()
+        np.testing.assert_array_equal(np.asarray(out), want)
+    finally:
+        for x in hs:
+            capi.free_pinned(x)
