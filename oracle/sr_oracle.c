@@ -528,12 +528,21 @@ static void window_stats(const uint8_t* a, size_t pa, int ay, int ax, const uint
         }
     }
 }
-/* NCC cost (fp32, fixed operation order): -num/sqrt(vl*vr) with exact int64 moments scaled by n. */
+/* NCC cost (extension; fp32 with a fixed operation order):
+ *   num = n*slr - sl*sr,  vl = n*sll - sl^2,  vr = n*srr - sr^2      (exact integers)
+ *   rl = 1/sqrt((float)vl), rr = 1/sqrt((float)vr)                   (per-window factors, d-independent per image)
+ *   cost = -(((float)num * rl) * rr)                                 (+inf when a variance is not positive)
+ * i.e. -ZNCC of the two windows.  The factored form costs two multiplications per candidate once the
+ * per-window factors are tabulated, which is what the sliding-sum CUDA kernel does; every operation is a
+ * correctly rounded fp32 operation, so the GPU reproduces it bit for bit. */
 static float ncc_cost(const wstats* s, int64_t n) {
     int64_t num = n * s->slr - s->sl * s->sr, vl = n * s->sll - s->sl * s->sl, vr = n * s->srr - s->sr * s->sr;
     if (vl <= 0 || vr <= 0) return INFINITY;
-    float den = sqrtf((float)vl * (float)vr);
-    return -((float)num / den);
+    volatile float sl_ = sqrtf((float)vl), sr_ = sqrtf((float)vr);
+    volatile float rl = 1.0f / sl_, rr = 1.0f / sr_;
+    volatile float a = (float)num * rl;
+    volatile float c = a * rr;
+    return -c;
 }
 
 int orc_search_ext(const uint8_t* left, int w1, int h1, size_t pitch1,

@@ -35,12 +35,15 @@ __device__ __forceinline__ WStats window_stats(const uint32_t* __restrict__ Lp, 
     return s;
 }
 
-// NCC cost (fp32, fixed operation order): -num/sqrt(vl*vr), exact int64 moments scaled by n
+// NCC cost (extension definition of SURVEY.md 8c; fp32, fixed operation order): exact int64 moments,
+// per-window factors rl = 1/sqrt((float)vl), rr = 1/sqrt((float)vr), cost = -(((float)num * rl) * rr).
+__device__ __forceinline__ float ncc_inv_std(long long v) {
+    return __fdiv_rn(1.0f, __fsqrt_rn(__ll2float_rn(v)));
+}
 __device__ __forceinline__ float ncc_cost(const WStats& s, long long n) {
     long long num = n * s.slr - s.sl * s.sr, vl = n * s.sll - s.sl * s.sl, vr = n * s.srr - s.sr * s.sr;
     if (vl <= 0 || vr <= 0) return INFINITY;
-    float den = sqrtf(__fmul_rn(__ll2float_rn(vl), __ll2float_rn(vr)));
-    return -__fdiv_rn(__ll2float_rn(num), den);
+    return -__fmul_rn(__fmul_rn(__ll2float_rn(num), ncc_inv_std(vl)), ncc_inv_std(vr));
 }
 
 __device__ __forceinline__ float parabola(float dsub, float cm, float c0, float cp) {
@@ -53,14 +56,35 @@ struct ExtGeom {
     int wr, hr, wo, ho;   // reference image (gets the disparities) and the other image
     int height, half, dlo, dhi, left_ref, cost;
     int row0;             // first output row of the launch (grid.y rows from here)
+    int ix0, ix1, iy0, iy1;   // pixels inside [ix0,ix1) x [iy0,iy1) are someone else's (NCC interior): skipped
+    int row1;                 // end row of the launch when the border frame is enumerated compactly
 };
 
 // Universal extension kernel: one thread per reference pixel.
 __global__ void __launch_bounds__(128) ext_direct_kernel(const uint32_t* __restrict__ Lp, int pitchL,
                                                          const uint32_t* __restrict__ Rp, int pitchR, ExtGeom g,
                                                          int* __restrict__ disp, float* __restrict__ subpix) {
-    int x = blockIdx.x * blockDim.x + threadIdx.x, y = g.row0 + blockIdx.y;
-    if (x >= g.wr) return;
+    int x, y;
+    if (g.ix1 > g.ix0) {
+        // border frame around the interior rectangle, enumerated compactly (1-D grid) so that every lane works:
+        // full rows [row0, iy0), the two side strips of rows [iy0, iy1), full rows [iy1, row1)
+        long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
+        const int W = g.wr, side = g.ix0 + (W - g.ix1);
+        const long top = (long)(g.iy0 - g.row0) * W, mid = (long)(g.iy1 - g.iy0) * side;
+        if (idx < top) { y = g.row0 + (int)(idx / W); x = (int)(idx % W); }
+        else if (idx < top + mid) {
+            long k = idx - top;
+            int c = (int)(k % side);
+            y = g.iy0 + (int)(k / side); x = c < g.ix0 ? c : g.ix1 + (c - g.ix0);
+        } else {
+            long k = idx - top - mid;
+            y = g.iy1 + (int)(k / W); x = (int)(k % W);
+            if (y >= g.row1) return;
+        }
+    } else {
+        x = blockIdx.x * blockDim.x + threadIdx.x; y = g.row0 + blockIdx.y;
+        if (x >= g.wr) return;
+    }
     size_t o = (size_t)y * g.wr + x;
     int dbest = 0;
     float dsub = 0.0f;
@@ -131,6 +155,40 @@ __global__ void __launch_bounds__(128) ext_from_planes_kernel(const uint32_t* __
                     long long cm = g.cost == SR_COST_SAD ? sm.sad : sm.ssd, cp = g.cost == SR_COST_SAD ? sp.sad : sp.ssd;
                     dsub = parabola(dsub, __ll2float_rn(cm), __uint2float_rn(bc), __ll2float_rn(cp));
                 }
+            }
+        }
+    }
+    disp[o] = dbest;
+    if (subpix) subpix[o] = dsub;
+}
+
+// NCC interior pixels: first maximum of the per-pass (score, d) planes of search_ncc.cu (passes ascend in d,
+// strict > keeps the smaller d), plus the parabola through the directly recomputed neighbour costs.
+__global__ void __launch_bounds__(128) ncc_merge_kernel(const uint32_t* __restrict__ Lp, int pitchL,
+                                                        const uint32_t* __restrict__ Rp, int pitchR, ExtGeom g,
+                                                        const float* __restrict__ pscore, const int* __restrict__ pdisp,
+                                                        size_t stride, int npass, int want_subpix, int* __restrict__ disp,
+                                                        float* __restrict__ subpix) {
+    int x = g.ix0 + blockIdx.x * blockDim.x + threadIdx.x, y = g.iy0 + blockIdx.y;
+    if (x >= g.ix1) return;
+    size_t o = (size_t)y * g.wr + x;
+    int dbest = 0;
+    float dsub = 0.0f;
+    if ((__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) != 0) {
+        float best = -INFINITY; int bd = -1;
+        for (int p = 0; p < npass; p++) {
+            float s = __ldg(pscore + (size_t)p * stride + o);
+            if (s > best) { best = s; bd = __ldg(pdisp + (size_t)p * stride + o); }
+        }
+        if (bd >= 0) {
+            dbest = bd;
+            dsub = (float)bd;
+            const int h = g.half;
+            if (want_subpix && bd - 1 >= g.dlo && bd + 1 < g.dhi && x + bd + 1 + h < g.wo) {
+                long long n = (long long)(2 * h) * (2 * h) * 3;
+                float cm = ncc_cost(window_stats(Lp, pitchL, x + bd - 1 - h, Rp, pitchR, x - h, y - h, 2 * h, 2 * h, true), n);
+                float cp = ncc_cost(window_stats(Lp, pitchL, x + bd + 1 - h, Rp, pitchR, x - h, y - h, 2 * h, 2 * h, true), n);
+                if (isfinite(cm) && isfinite(cp)) dsub = parabola(dsub, cm, -best, cp);
             }
         }
     }
@@ -220,12 +278,45 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
             SR_LAUNCHED(ctx);
         }
     }
-    if (!tiled) {
-        ext_direct_kernel<<<dim3(cdiv(w2, 128), row1 - row0), 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g,
-                                                                             disp_r, subpix);
-        SR_LAUNCHED(ctx);
+    bool ncc_tiled = false;
+    if (p->cost == SR_COST_NCC && half >= 1 && half <= 8) {
+        // interior pixels (full window) through the sliding-sum NCC kernel, the frame of clamped windows directly
+        SearchGeom sg;
+        sg.w1 = w1; sg.h1 = h1; sg.w2 = w2; sg.h2 = h2; sg.height = g.height; sg.block = p->block; sg.half = half;
+        sg.dlo = dlo; sg.dhi = dhi > w1 ? w1 : dhi; if (sg.dhi < sg.dlo) sg.dhi = sg.dlo;
+        sg.row0 = row0; sg.row1 = row1;
+        float* ps = nullptr; int* pd = nullptr;
+        int handled = sg.dhi > sg.dlo ? sr_launch_search_ncc(ctx, pair, sg, &ps, &pd) : 0;
+        if (handled < 0) return handled;
+        if (handled) {
+            ncc_tiled = true;
+            g.ix0 = half; g.ix1 = w2 - half;
+            g.iy0 = row0 > half ? row0 : half;
+            g.iy1 = row1 < g.height ? row1 : g.height;
+            if (g.iy1 > h2 - half) g.iy1 = h2 - half;
+            if (g.iy1 > h1 - half) g.iy1 = h1 - half;
+            if (g.iy1 < g.iy0) g.iy1 = g.iy0;
+            if (g.iy1 > g.iy0 && g.ix1 > g.ix0) {
+                ncc_merge_kernel<<<dim3(cdiv(g.ix1 - g.ix0, 128), g.iy1 - g.iy0), 128, 0, ctx->stream>>>(
+                    pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, ps, pd, pair->npx_cap, pair->npass, p->subpixel,
+                    disp_r, subpix);
+                SR_LAUNCHED(ctx);
+            } else { g.ix1 = g.ix0; }
+        }
     }
-    ctx->last_kernel = tiled ? "tile+ext" : "ext-direct";
+    if (!tiled) {   // all pixels, or -- after the NCC kernel -- the border frame outside [ix0,ix1) x [iy0,iy1)
+        dim3 grid(cdiv(w2, 128), row1 - row0);
+        if (g.ix1 > g.ix0) {
+            g.row1 = row1;
+            long nborder = (long)(row1 - row0) * w2 - (long)(g.iy1 - g.iy0) * (g.ix1 - g.ix0);
+            grid = dim3((unsigned)((nborder + 127) / 128), 1);
+        }
+        if (grid.x > 0) {
+            ext_direct_kernel<<<grid, 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, disp_r, subpix);
+            SR_LAUNCHED(ctx);
+        }
+    }
+    ctx->last_kernel = tiled ? "tile+ext" : ncc_tiled ? "ncc-tile+ext" : "ext-direct";
     if (p->lr_check) {
         // Left-referenced search (window [x-l, x+r) on the left image, partner at x - d, break when the
         // partner window leaves the right image on the left).  With both images mirror-packed about the

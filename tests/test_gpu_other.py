@@ -241,3 +241,31 @@ def test_ext_left_referenced_map(sr, ctx, orc, cost, shape):
     if w1 <= w2:
         assert "mirror" in ctx.last_kernel
     pair.close()
+
+
+@pytest.mark.parametrize("shape", [
+    # (w1, h1, w2, h2, block, min_d, max_d, quant)
+    (420, 70, 420, 70, 9, 0, 100, False),     # two passes of 64 disparities
+    (420, 70, 420, 70, 5, 3, 40, True),       # min_disp > 0, quantised images (flat windows: zero variance -> +inf costs)
+    (333, 64, 333, 64, 15, 0, 70, False),     # halo from two neighbour lanes
+    (333, 64, 333, 64, 17, 0, 30, False),
+    (300, 48, 340, 48, 8, 0, 50, False),      # even block, w1 < w2
+    (340, 48, 300, 48, 3, 0, 20, True),       # w1 > w2, smallest window
+])
+def test_ext_ncc_sliding_kernel(sr, ctx, orc, shape):
+    """NCC through the sliding-sum kernel (interior) + per-pixel kernel (border frame) against the oracle:
+    integer winners and sub-pixel values, compared bit-exact (same fp32 operation order)."""
+    w1, h1, w2, h2, block, dlo, dhi, quant = shape
+    w, h = max(w1, w2), max(h1, h2)
+    L, R = orc.synth_pair(31, 0, w, h, dlo, dhi, quant)
+    L = np.ascontiguousarray(L[:h1, :w1]); R = np.ascontiguousarray(R[:h2, :w2])
+    R[20:25, 50:90] = 0
+    L[30:40, 200:230] = 77                      # a flat patch: zero left variance
+    d, _, sp = orc.search_ext(L, R, block, dlo, dhi, orc.COST_NCC, want_subpix=True)
+    bs = sr.BlockSearch(L, R, block, dlo, dhi, cost=sr.capi.COST_NCC, ctx=ctx)
+    got = bs.computeDisparityMapRight(1.0)
+    assert "ncc-tile" in ctx.last_kernel
+    np.testing.assert_array_equal(got, d.astype(np.float64))
+    gots = bs.computeDisparityMapRight(1.0, subpixel=True)
+    np.testing.assert_array_equal(gots, sp.astype(np.float64))
+    assert np.abs(gots - sp).max() <= 1e-3       # north_star tolerance (met exactly)
