@@ -126,6 +126,72 @@ __global__ void __launch_bounds__(128) ext_direct_kernel(const uint32_t* __restr
     if (subpix) subpix[o] = dsub;
 }
 
+// NCC on the border frame around the interior rectangle (clamped windows): one WARP per pixel, lanes
+// stride over the candidates, (cost, d) first-minimum reduction by shuffles.  Same arithmetic and
+// candidate rules as ext_direct_kernel (right-referenced), which spends one thread per pixel and is
+// latency-bound on a thin frame.
+__global__ void __launch_bounds__(128) ncc_border_warp_kernel(const uint32_t* __restrict__ Lp, int pitchL,
+                                                              const uint32_t* __restrict__ Rp, int pitchR, ExtGeom g,
+                                                              long npix, int* __restrict__ disp, float* __restrict__ subpix) {
+    const int lane = threadIdx.x & 31;
+    long idx = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (idx >= npix) return;
+    int x, y;
+    {
+        const int W = g.wr, side = g.ix0 + (W - g.ix1);
+        const long top = (long)(g.iy0 - g.row0) * W, mid = (long)(g.iy1 - g.iy0) * side;
+        if (idx < top) { y = g.row0 + (int)(idx / W); x = (int)(idx % W); }
+        else if (idx < top + mid) {
+            long k = idx - top;
+            int c = (int)(k % side);
+            y = g.iy0 + (int)(k / side); x = c < g.ix0 ? c : g.ix1 + (c - g.ix0);
+        } else {
+            long k = idx - top - mid;
+            y = g.iy1 + (int)(k / W); x = (int)(k % W);
+        }
+    }
+    size_t o = (size_t)y * g.wr + x;
+    int dbest = 0;
+    float dsub = 0.0f;
+    if (y < g.height && (__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) != 0) {
+        int l = min(x, g.half), r = min(g.wr - x - 1, g.half), u = min(y, g.half), dn = min(g.hr - y - 1, g.half);
+        int ww = l + r, wh = u + dn;
+        long long n = (long long)ww * wh * 3;
+        int dmax = min(g.dhi, g.wo - x - r);                 // candidates d in [dlo, dmax): before the break
+        float best = INFINITY; int bd = -1;
+        for (int d = g.dlo + lane; d < dmax; d += 32) {
+            float c = n ? ncc_cost(window_stats(Lp, pitchL, x + d - l, Rp, pitchR, x - l, y - u, ww, wh, true), n) : INFINITY;
+            if (c < best) { best = c; bd = d; }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            float oc = __shfl_down_sync(0xffffffffu, best, off);
+            int od = __shfl_down_sync(0xffffffffu, bd, off);
+            if (oc < best || (oc == best && od >= 0 && od < bd)) { best = oc; bd = od; }
+        }
+        bd = __shfl_sync(0xffffffffu, bd, 0);
+        best = __shfl_sync(0xffffffffu, best, 0);
+        if (bd >= 0) {
+            dbest = bd;
+            dsub = (float)bd;
+            if (subpix && bd - 1 >= g.dlo && bd + 1 < dmax) {
+                // lanes 0 / 1 recompute the two neighbours of the winner
+                float cn = INFINITY;
+                if (lane < 2) {
+                    int d = bd - 1 + 2 * lane;
+                    cn = n ? ncc_cost(window_stats(Lp, pitchL, x + d - l, Rp, pitchR, x - l, y - u, ww, wh, true), n) : INFINITY;
+                }
+                float cm = __shfl_sync(0xffffffffu, cn, 0), cp = __shfl_sync(0xffffffffu, cn, 1);
+                if (isfinite(cm) && isfinite(cp)) dsub = parabola(dsub, cm, best, cp);
+            }
+        }
+    }
+    if (lane == 0) {
+        disp[o] = dbest;
+        if (subpix) subpix[o] = dsub;
+    }
+}
+
 // Winner from the tile kernel's key planes + direct recomputation of the parabola neighbours.
 __global__ void __launch_bounds__(128) ext_from_planes_kernel(const uint32_t* __restrict__ Lp, int pitchL,
                                                               const uint32_t* __restrict__ Rp, int pitchR, ExtGeom g,
@@ -311,7 +377,14 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
             long nborder = (long)(row1 - row0) * w2 - (long)(g.iy1 - g.iy0) * (g.ix1 - g.ix0);
             grid = dim3((unsigned)((nborder + 127) / 128), 1);
         }
-        if (grid.x > 0) {
+        if (g.ix1 > g.ix0 && p->cost == SR_COST_NCC) {
+            long nborder = (long)(row1 - row0) * w2 - (long)(g.iy1 - g.iy0) * (g.ix1 - g.ix0);
+            if (nborder > 0) {
+                ncc_border_warp_kernel<<<(unsigned)((nborder * 32 + 127) / 128), 128, 0, ctx->stream>>>(
+                    pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, nborder, disp_r, subpix);
+                SR_LAUNCHED(ctx);
+            }
+        } else if (grid.x > 0) {
             ext_direct_kernel<<<grid, 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, disp_r, subpix);
             SR_LAUNCHED(ctx);
         }
