@@ -42,14 +42,31 @@ static int pipeline_chunks(const sr_pair* pair, const sr_search_params* p, int r
     const char* env = getenv("SR_PIPE_CHUNKS");   // tuning / test override
     int c = env ? atoi(env) : 0;
     if (c <= 0) {
-        // small pairs: one chunk (launch overheads dominate); large pairs: ~1.3 M right pixels per chunk
+        // small pairs: one chunk (launch overheads dominate); large pairs: ~1 M right pixels per chunk
         double px = (double)pair->w2 * rows;
-        c = (int)(px / 1.3e6);
+        c = (int)(px / 1.0e6);
         if (c > 8) c = 8;
     }
     int maxc = rows / (4 * p->block + 16);
     if (c > maxc) c = maxc;
     return c < 1 ? 1 : c;
+}
+
+// first row of chunk c of n (c == n: the end) when `rows` rows are cut into n chunks whose first and
+// last chunk have edge_w (< 1) times the weight of the inner ones
+static int chunk_start(int rows, int n, int c, int half) {
+    if (c <= 0) return 0;
+    if (c >= n) return rows;
+    const char* env = getenv("SR_PIPE_EDGE");
+    double edge_w = env ? atof(env) : 0.45;
+    if (n < 3 || edge_w <= 0.0 || edge_w > 1.0) edge_w = 1.0;
+    double total = (n - 2) + 2 * edge_w;
+    double upto = edge_w + (c - 1);            // weight of chunks 0..c-1
+    int r = (int)(rows * upto / total + 0.5);
+    int minrows = 2 * half + 2;
+    if (r < c * minrows) r = c * minrows;       // every chunk keeps at least a window's worth of rows
+    if (r > rows - (n - c) * minrows) r = rows - (n - c) * minrows;
+    return r;
 }
 
 static bool can_pipeline(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_image* right,
@@ -92,7 +109,9 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     int upL = up0 < pair->h1 ? up0 : pair->h1, upR = up0 < pair->h2 ? up0 : pair->h2, rc = SR_OK;
     const size_t rowL = (size_t)left->w * 3, rowR = (size_t)right->w * 3;
     for (int c = 0; c < nch && rc == SR_OK; c++) {
-        int r0 = band0 + (int)((long)oh * c / nch), r1 = band0 + (int)((long)oh * (c + 1) / nch);
+        // uneven chunks: a short first chunk starts the search early, a short last chunk leaves a short
+        // exposed download; the chunks in between are larger (fewer partial waves in the search kernel)
+        int r0 = band0 + chunk_start(oh, nch, c, half), r1 = band0 + chunk_start(oh, nch, c + 1, half);
         // input rows this chunk needs: window rows [r0 - half, r1 + half) of both images
         int needR = r1 + half + 1 < pair->h2 ? r1 + half + 1 : pair->h2;
         int needL = r1 + half + 1 < pair->h1 ? r1 + half + 1 : pair->h1;
