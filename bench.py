@@ -251,6 +251,7 @@ def main():
     sampler = ClockSampler(local_rank) if rank == 0 else None
     peak_dual, peak_single = ctx.int_peak()
     for _ in range(max(args.warmup, 3)):
+        ctx.l2_flush()                       # warm-up steps look exactly like timed steps (first flush allocates)
         step_resident()
     launches0 = ctx.launches
     barrier()
@@ -264,6 +265,8 @@ def main():
             kern_ms.append(ctx.search_kernel_ms())
     barrier()
     launches = ctx.launches - launches0 - args.steps * 0   # memset of the flush is not a kernel of ours
+    if os.environ.get("SR_BENCH_DEBUG"):
+        print(f"[rank {rank}] step ms {[round(x, 3) for x in step_ms]} kernel ms {[round(x, 3) for x in kern_ms]}", file=sys.stderr, flush=True)
     t_total = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t_total, op=dist.ReduceOp.MAX)
