@@ -216,6 +216,7 @@ def main():
     pair.upload(Lp, Rp)
     r0, r1 = sharding.band_rows(h, rank, world)
     full = sharding.result_tensor(pair, dev)
+    full16 = sharding.result16_tensor(pair, dev) if world > 1 else None   # int16 wire format of the band gather
     total_evals = synth.effective_evals(w, w, h, block, 0, D)
 
     half = (block - 1) // 2
@@ -232,7 +233,7 @@ def main():
         pair.run(params, r0, r1)
         if world > 1:
             with torch.cuda.stream(ext):
-                sharding.gather_bands(full, h, rank, world)
+                sharding.gather_bands16(pair, full16, h, rank, world)
 
     def step_e2e():
         if world == 1:
@@ -242,7 +243,7 @@ def main():
             # rank 0 streams its own band back to the host inside that pipeline, the others keep theirs in HBM
             pair.search_band(Lp, Rp, params, r0, r1, out=outp if rank == 0 else None)
             with torch.cuda.stream(ext):
-                sharding.gather_bands(full, h, rank, world)
+                sharding.gather_bands16(pair, full16, h, rank, world)
             if rank == 0:
                 ext.synchronize()
                 pair.download(params, out=outp, row0=r1, row1=h)   # the gathered bands (rank 0 owns rows [0, r1))
@@ -316,7 +317,7 @@ def main():
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: synthetic {w}x{h} rectified pair, {D} disparities, {block}x{block} "
                                    f"{cost.upper()}, smooth 1.0 (BASELINE.json configs)",
-                       "sharding": "row bands + NCCL gather to rank 0" if world > 1 else "single GPU",
+                       "sharding": "row bands + NCCL gather to rank 0 (int16 wire format, widened on rank 0)" if world > 1 else "single GPU",
                        "l2": "384 MB written between timed iterations", "evals": "effective (reference break rule)",
                        "nominal_MDE": w * h * D / 1e6, "effective_MDE": total_evals / 1e6},
             "pairs_per_s": 1e3 / ms_per_step,

@@ -133,6 +133,15 @@ int sr_pair_search_band(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const 
                         const sr_search_params* p, int row0, int row1, double* disp_out, size_t out_pitch);
 /* Device pointer (double*, tightly packed rows of the output width) of the last result. */
 void* sr_search_result_dev(sr_ctx* ctx, sr_pair* pair);
+/* int16 wire format of integer disparity maps for the device-side band gather ("16.6 MB as u16
+ * if the integer-disparity wire format is used and widened on rank 0"; signed because the reference stores
+ * -x where no candidate survives, BlockSearch.cpp:111,174).  sr_search_pack16 narrows rows [row0,row1) of the
+ * CV_64F result into the pair's int16 buffer (SR_E_BADARG if a value is not an integer in int16 range, e.g. a
+ * sub-pixel map), sr_search_unpack16 widens rows back into the CV_64F result; both asynchronous on the context
+ * stream.  sr_search_result16_dev returns the int16 buffer (w2 x h2, tight). */
+int sr_search_pack16(sr_ctx* ctx, sr_pair* pair, int row0, int row1);
+int sr_search_unpack16(sr_ctx* ctx, sr_pair* pair, int row0, int row1);
+void* sr_search_result16_dev(sr_ctx* ctx, sr_pair* pair);
 int sr_search_max_block(sr_ctx* ctx, sr_pair* pair, int* max_block);
 /* The left-referenced integer disparity map (w1 x h1, int32) that the last run with lr_check = 1
  * computed for the consistency test (extension); SR_E_BADARG when there is none. */

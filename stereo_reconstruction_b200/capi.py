@@ -48,7 +48,7 @@ SYMBOLS = [
     "sr_ctx_create", "sr_ctx_destroy", "sr_last_error", "sr_version", "sr_host_alloc", "sr_host_free",
     "sr_ctx_stream", "sr_ctx_sync", "sr_timer_start", "sr_timer_stop", "sr_kernel_launches", "sr_last_kernel",
     "sr_block_search", "sr_block_search_batch", "sr_pair_create", "sr_pair_destroy", "sr_pair_upload",
-    "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block", "sr_search_left_disparity", "sr_pair_search_band",
+    "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block", "sr_search_left_disparity", "sr_pair_search_band", "sr_search_pack16", "sr_search_unpack16", "sr_search_result16_dev",
     "sr_search_effective_evals", "sr_remove_outliers", "sr_box_blur", "sr_scale", "sr_disparity_to_depth",
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
     "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
@@ -77,6 +77,8 @@ def lib():
         l.sr_ctx_stream.argtypes = [C.c_void_p]
         l.sr_search_result_dev.restype = C.c_void_p
         l.sr_search_result_dev.argtypes = [C.c_void_p, C.c_void_p]
+        l.sr_search_result16_dev.restype = C.c_void_p
+        l.sr_search_result16_dev.argtypes = [C.c_void_p, C.c_void_p]
         l.sr_ctx_destroy.restype = None
         l.sr_ctx_destroy.argtypes = [C.c_void_p]
         l.sr_pair_destroy.restype = None
@@ -231,6 +233,16 @@ class Pair:
         self.ctx.check(self.ctx._l.sr_search_download(self.ctx.h, self.h, C.c_void_p(out.ctypes.data),
                                                       C.c_size_t(out.strides[0]), int(row0), int(row1)))
         return out
+
+    def pack16(self, row0, row1):
+        """Narrows rows of the CV_64F result to the int16 wire format (sr_search_pack16)."""
+        self.ctx.check(self.ctx._l.sr_search_pack16(self.ctx.h, self.h, int(row0), int(row1)))
+
+    def unpack16(self, row0, row1):
+        self.ctx.check(self.ctx._l.sr_search_unpack16(self.ctx.h, self.h, int(row0), int(row1)))
+
+    def result16_ptr(self):
+        return int(self.ctx._l.sr_search_result16_dev(self.ctx.h, self.h))
 
     def search_band(self, left, right, params, row0, row1, out=None):
         """sr_pair_search_band: rows [row0,row1) from host images; out=None keeps the band in HBM."""

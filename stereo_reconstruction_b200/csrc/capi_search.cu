@@ -29,6 +29,20 @@ static int validate(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p) {
 // chunk c-1 (copy stream 1) overlap; only the first upload and the last download are exposed.
 // Applies where output rows are independent (Right variant, tile kernel, no raster smoothing rule)
 // and both host sides are pinned (a pageable buffer needs a staging memcpy that serialises anyway).
+// ---- int16 wire format of integer disparity maps (band gather) ------------------------------------
+__global__ void pack16_kernel(const double* __restrict__ src, short* __restrict__ dst, size_t n, int* __restrict__ status) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double v = src[i];
+    int q = (int)v;
+    if ((double)q != v || q < -32768 || q > 32767) { *status = SR_E_BADARG; q = 0; }
+    dst[i] = (short)q;
+}
+__global__ void unpack16_kernel(const short* __restrict__ src, double* __restrict__ dst, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = (double)src[i];
+}
+
 static bool host_pinned(const void* p) {
     cudaPointerAttributes attr;
     bool pinned = cudaPointerGetAttributes(&attr, p) == cudaSuccess &&
@@ -268,6 +282,7 @@ int sr_search_download(sr_ctx* ctx, sr_pair* pair, double* disp_out, size_t out_
     }
     int status[2];
     SR_CUDA(ctx, cudaMemcpy(status, pair->maxblock, sizeof status, cudaMemcpyDeviceToHost));
+    if (status[1] == SR_E_BADARG) return sr_fail(ctx, status[1], "sr_search_pack16: the map holds values that are not integers in int16 range");
     if (status[1] != SR_OK) return sr_fail(ctx, status[1], "the grown window runs past the left image (cv::Exception in the reference)");
     return SR_OK;
 }
@@ -277,6 +292,39 @@ int sr_search_max_block(sr_ctx* ctx, sr_pair* pair, int* max_block) {
     SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     SR_CUDA(ctx, cudaMemcpy(max_block, pair->maxblock, sizeof(int), cudaMemcpyDeviceToHost));
     return SR_OK;
+}
+
+static int rows16(sr_ctx* ctx, sr_pair* pair, int& row0, int& row1) {
+    if (!ctx || !pair) return sr_fail(ctx, SR_E_BADARG, "NULL argument");
+    if (row0 < 0) row0 = 0;
+    if (row1 > pair->oh) row1 = pair->oh;
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (!pair->out16) SR_CUDA(ctx, cudaMalloc((void**)&pair->out16, pair->npx_cap * sizeof(short)));
+    return SR_OK;
+}
+
+int sr_search_pack16(sr_ctx* ctx, sr_pair* pair, int row0, int row1) {
+    int rc = rows16(ctx, pair, row0, row1);
+    if (rc != SR_OK || row1 <= row0) return rc;
+    size_t n = (size_t)(row1 - row0) * pair->ow, off = (size_t)row0 * pair->ow;
+    pack16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(pair->out + off, pair->out16 + off, n, pair->maxblock + 1);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
+int sr_search_unpack16(sr_ctx* ctx, sr_pair* pair, int row0, int row1) {
+    int rc = rows16(ctx, pair, row0, row1);
+    if (rc != SR_OK || row1 <= row0) return rc;
+    size_t n = (size_t)(row1 - row0) * pair->ow, off = (size_t)row0 * pair->ow;
+    unpack16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(pair->out16 + off, pair->out + off, n);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
+void* sr_search_result16_dev(sr_ctx* ctx, sr_pair* pair) {
+    int r0 = 0, r1 = 0;
+    if (rows16(ctx, pair, r0, r1) != SR_OK) return nullptr;
+    return (void*)pair->out16;
 }
 
 int sr_search_left_disparity(sr_ctx* ctx, sr_pair* pair, int32_t* disp_left, size_t out_pitch) {

@@ -70,6 +70,7 @@ struct sr_pair {
     double* alt = nullptr;
     double* out = nullptr;                // result, ow x oh, tight
     float* outf = nullptr;                // float copy for the reconstruction pipeline
+    short* out16 = nullptr;               // int16 wire format of the result (band gather)
     int* maxblock = nullptr;              // device scalar
     unsigned long long* evals = nullptr;  // device scalar
     size_t npx_cap = 0;

@@ -34,6 +34,25 @@ def result_tensor(pair, device):
     return torch.as_tensor(_DevArray(pair.result_ptr(), (pair.h2, pair.w2), "<f8"), device=device)
 
 
+def result16_tensor(pair, device):
+    """The int16 wire-format buffer of a sr_pair (sr_search_result16_dev) as a torch tensor view."""
+    return torch.as_tensor(_DevArray(pair.result16_ptr(), (pair.h2, pair.w2), "<i2"), device=device)
+
+
+def gather_bands16(pair, full16, h, rank, world, group=None):
+    """Band gather in the int16 wire format (a quarter of the CV_64F bytes): every rank narrows its band,
+    the bands travel as int16, rank 0 widens the received rows back into its CV_64F result.  Call with the
+    pair's stream current (torch.cuda.stream(ExternalStream(ctx.stream)))."""
+    if world == 1:
+        return
+    r0, r1 = band_rows(h, rank, world)
+    if rank != 0:
+        pair.pack16(r0, r1)
+    gather_bands(full16.view(torch.uint8), h, rank, world, group)   # NCCL has no int16: the rows travel as bytes
+    if rank == 0:
+        pair.unpack16(r1, h)       # rank 0 owns rows [0, r1); the rest arrived as int16
+
+
 def gather_bands(full, h, rank, world, group=None):
     """`full` is an (h, w) tensor on every rank whose rows band_rows(h, rank, world) hold this rank's
     band.  After the call rank 0's `full` holds every band.  Point-to-point, no padding."""

@@ -160,3 +160,29 @@ def test_pair_search_band_from_host(sr, ctx, orc, monkeypatch, pinned):
     finally:
         for x in hs:
             capi.free_pinned(x)
+
+
+def test_int16_wire_format(sr, ctx, orc):
+    """sr_search_pack16 / sr_search_unpack16: integer maps (incl. the reference's negative "-x" values) survive
+    the int16 round trip bit-exactly; a sub-pixel map is refused."""
+    capi = sr.capi
+    w1, w2, h, D = 90, 120, 40, 16                   # w1 < w2: columns without a candidate store -x
+    L, R = synth(orc, w2, h, 0, D, seed=5)
+    L = np.ascontiguousarray(L[:, :w1])
+    pair = capi.Pair(ctx, w1, h, w2, h)
+    pair.upload(L, R)
+    p = capi.search_params(block=9, min_disp=0, max_disp=D, smooth=1.0)
+    pair.run(p)
+    want = pair.download(p)
+    assert (want < 0).any()
+    pair.pack16(0, h)
+    pair.run(capi.search_params(block=5, min_disp=0, max_disp=D, smooth=1.0))   # overwrite the CV_64F result
+    pair.unpack16(3, h - 2)
+    got = pair.download(p)
+    np.testing.assert_array_equal(got[3:h - 2], want[3:h - 2])
+    ps = capi.search_params(block=9, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD, subpixel=True)
+    pair.run(ps)
+    pair.pack16(0, h)
+    with pytest.raises(capi.SrError):
+        pair.download(ps)
+    pair.close()

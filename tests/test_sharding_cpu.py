@@ -35,9 +35,25 @@ def _worker(rank, world, port, q):
     full = torch.zeros((h, w), dtype=torch.float64)
     full[r0:r1] = torch.from_numpy(band[r0:r1])
     sharding.gather_bands(full, h, rank, world)
+    # the int16 wire-format gather (gather_bands16) with a CPU stand-in for capi.Pair's pack16 / unpack16
+    class FakePair:
+        def __init__(self, t):
+            self.full = t
+            self.full16 = torch.zeros(t.shape, dtype=torch.int16)
+
+        def pack16(self, a, b):
+            self.full16[a:b] = self.full[a:b].to(torch.int16)
+
+        def unpack16(self, a, b):
+            self.full[a:b] = self.full16[a:b].to(torch.float64)
+
+    full2 = torch.zeros((h, w), dtype=torch.float64)
+    full2[r0:r1] = torch.from_numpy(band[r0:r1])
+    fp = FakePair(full2)
+    sharding.gather_bands16(fp, fp.full16, h, rank, world)
     if rank == 0:
         want = orc.block_search_right_fast(L, R, B, 0, D, 1.0, nthreads=1)
-        q.put(bool(np.array_equal(full.numpy(), want)))
+        q.put(bool(np.array_equal(full.numpy(), want)) and bool(np.array_equal(full2.numpy(), want)))
     assert sharding.pairs_of_rank(5, rank, world) == list(range(rank, 5, world))
     dist.barrier()
     dist.destroy_process_group()
