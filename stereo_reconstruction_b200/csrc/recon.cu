@@ -2,6 +2,7 @@
 // Every kernel is O(1) work per pixel and HBM-bound; arithmetic follows the reference's operation
 // order exactly (no FMA contraction: the library is compiled with --fmad=false; IEEE division
 // and square root are nvcc defaults), so results are bit-identical to the CPU code.
+#include <cstdlib>
 #include "sr_internal.cuh"
 #include "recon.cuh"
 
@@ -50,12 +51,178 @@ __global__ void blur_cols_kernel(const double* __restrict__ rows, int w, int h, 
     }
 }
 
+// ---- the same blur, order-free --------------------------------------------------------------------
+// The recurrences above are sequential (one thread per row / column: latency-bound, 1.1 ms for a
+// 1436x992 map with k = 500).  When every partial sum is EXACTLY representable in fp64 the order of
+// the additions does not matter and the window sums can come from parallel prefix sums with the
+// identical result.  blur_exact_check_kernel proves that on the device: all nonzero inputs are multiples
+// of 2^q with |v| < 2^E, any signed sum of N <= 2k^2 of them is a multiple of 2^q below N*2^E, exact iff
+// E - q + ceil(log2 N) <= 53.  (Always true for the reference's 8-bit hand-off, main.cpp:41-50, and for
+// sub-pixel maps within a 2^10 dynamic range.)  Both kernel families are launched; each returns at once
+// when the flag says the other one applies -- no host round trip.
+__global__ void blur_exact_check_kernel(const float* __restrict__ src, size_t n, int* __restrict__ flag /* [emax+1, qmin, bad] */) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int E = -1000, q = 1000, bad = 0;
+    for (; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        uint32_t b = __float_as_uint(src[i]);
+        uint32_t ex = (b >> 23) & 0xFFu, man = b & 0x7FFFFFu;
+        if (ex == 0xFFu || (ex == 0 && man != 0)) { bad = 1; continue; }   // inf / NaN / denormal: keep the recurrence
+        if (ex == 0) continue;                                              // zero
+        uint32_t m = man | 0x800000u;
+        int e = (int)ex - 127;
+        E = max(E, e + 1);
+        q = min(q, e - 23 + (__ffs(m) - 1));
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        E = max(E, __shfl_xor_sync(0xffffffffu, E, off));
+        q = min(q, __shfl_xor_sync(0xffffffffu, q, off));
+        bad |= __shfl_xor_sync(0xffffffffu, bad, off);
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMax(flag, E); atomicMin(flag + 1, q); if (bad) atomicOr(flag + 2, 1); }
+}
+__device__ __forceinline__ bool blur_is_exact(const int* flag, int k) {
+    if (flag[2]) return false;
+    if (flag[0] <= -1000) return true;                                      // all zeros
+    int logn = 1;
+    long long nn = 2LL * k * k;
+    while ((1LL << logn) < nn) logn++;
+    return flag[0] - flag[1] + logn <= 53;
+}
+
+// One CTA per row: inclusive prefix sums of the reflect-101 extended row in shared memory, then
+// rowsum[x] = PE[x + k - 1] - PE[x - 1].
+#define BLUR_T 256
+__global__ void __launch_bounds__(BLUR_T) blur_rows_fast_kernel(const float* __restrict__ src, int w, int h, int k,
+                                                                double* __restrict__ rows, const int* __restrict__ flag) {
+    extern __shared__ double pe[];               // w + k - 1 prefix values
+    __shared__ double wsum[BLUR_T / 32];
+    if (!blur_is_exact(flag, k)) return;
+    const int y = blockIdx.x, t = threadIdx.x, a = k / 2, we = w + k - 1;
+    const float* s = src + (size_t)y * w;
+    const int C = (we + BLUR_T - 1) / BLUR_T, j0 = t * C, j1 = min(j0 + C, we);
+    double acc = 0;
+    for (int j = j0; j < j1; j++) { acc += (double)s[reflect101(j - a, w)]; pe[j] = acc; }
+    // exclusive scan of the per-thread totals
+    double v = acc;
+    for (int off = 1; off < 32; off <<= 1) { double u = __shfl_up_sync(0xffffffffu, v, off); if ((t & 31) >= off) v += u; }
+    if ((t & 31) == 31) wsum[t >> 5] = v;
+    __syncthreads();
+    double base = v - acc;
+    for (int i = 0; i < (t >> 5); i++) base += wsum[i];
+    for (int j = j0; j < j1; j++) pe[j] += base;
+    __syncthreads();
+    double* o = rows + (size_t)y * w;
+    for (int x = t; x < w; x += BLUR_T) o[x] = pe[x + k - 1] - (x > 0 ? pe[x - 1] : 0.0);
+}
+
+// Columns: segment sums -> per-column exclusive scan of the segments -> prefix array PE (h + k - 1 rows)
+// -> dst = (float)((PE[y + k - 1] - PE[y - 1]) * scale).  Threads run along x (coalesced).
+#define BLUR_NSEG 64
+__global__ void blur_cols_seg_kernel(const double* __restrict__ rows, int w, int h, int k, double* __restrict__ seg,
+                                     const int* __restrict__ flag) {
+    if (!blur_is_exact(flag, k)) return;
+    int x = blockIdx.x * blockDim.x + threadIdx.x, sgi = blockIdx.y;
+    if (x >= w) return;
+    const int a = k / 2, he = h + k - 1, SL = (he + BLUR_NSEG - 1) / BLUR_NSEG;
+    const int j0 = sgi * SL, j1 = min(j0 + SL, he);
+    double acc = 0;
+    for (int j = j0; j < j1; j++) acc += rows[(size_t)reflect101(j - a, h) * w + x];
+    seg[(size_t)sgi * w + x] = acc;
+}
+__global__ void blur_cols_prefix_kernel(const double* __restrict__ rows, int w, int h, int k, const double* __restrict__ seg,
+                                        double* __restrict__ pe, const int* __restrict__ flag) {
+    if (!blur_is_exact(flag, k)) return;
+    int x = blockIdx.x * blockDim.x + threadIdx.x, sgi = blockIdx.y;
+    if (x >= w) return;
+    const int a = k / 2, he = h + k - 1, SL = (he + BLUR_NSEG - 1) / BLUR_NSEG;
+    const int j0 = sgi * SL, j1 = min(j0 + SL, he);
+    double acc = 0;
+    for (int i = 0; i < sgi; i++) acc += seg[(size_t)i * w + x];
+    for (int j = j0; j < j1; j++) { acc += rows[(size_t)reflect101(j - a, h) * w + x]; pe[(size_t)j * w + x] = acc; }
+}
+__global__ void blur_cols_out_kernel(const double* __restrict__ pe, int w, int h, int k, float* __restrict__ dst,
+                                     const int* __restrict__ flag) {
+    if (!blur_is_exact(flag, k)) return;
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= w) return;
+    double scale = 1.0 / ((double)k * (double)k);
+    double s0 = pe[(size_t)(y + k - 1) * w + x] - (y > 0 ? pe[(size_t)(y - 1) * w + x] : 0.0);
+    dst[(size_t)y * w + x] = (float)(s0 * scale);
+}
+// the sequential kernels, skipped when the order-free path applies
+__global__ void blur_rows_seq_kernel(const float* __restrict__ src, int w, int h, int k, double* __restrict__ rows,
+                                     const int* __restrict__ flag) {
+    if (blur_is_exact(flag, k)) return;
+    int y = blockIdx.x * blockDim.x + threadIdx.x;
+    if (y >= h) return;
+    const float* s = src + (size_t)y * w;
+    double* o = rows + (size_t)y * w;
+    int a = k / 2;
+    double acc = 0;
+    for (int i = 0; i < k; i++) acc += (double)s[reflect101(i - a, w)];
+    o[0] = acc;
+    for (int x = 1; x < w; x++) {
+        acc += (double)s[reflect101(x + k - 1 - a, w)] - (double)s[reflect101(x - 1 - a, w)];
+        o[x] = acc;
+    }
+}
+__global__ void blur_cols_seq_kernel(const double* __restrict__ rows, int w, int h, int k, float* __restrict__ dst,
+                                     const int* __restrict__ flag) {
+    if (blur_is_exact(flag, k)) return;
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= w) return;
+    int a = k / 2;
+    double scale = 1.0 / ((double)k * (double)k);
+    double sum = 0;
+    for (int i = 0; i < k - 1; i++) sum += rows[(size_t)reflect101(i - a, h) * w + x];
+    for (int y = 0; y < h; y++) {
+        double s0 = sum + rows[(size_t)reflect101(y - a + k - 1, h) * w + x];
+        dst[(size_t)y * w + x] = (float)(s0 * scale);
+        sum = s0 - rows[(size_t)reflect101(y - a, h) * w + x];
+    }
+}
+
 int recon_box_blur(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, int k) {
     double* rows = (double*)sr_scratch(ctx, 1, (size_t)w * h * sizeof(double));
     if (!rows) return SR_E_CUDA;
-    blur_rows_kernel<<<cdiv(h, 64), 64, 0, ctx->stream>>>(d_src, w, h, k, rows);
+    static const char* slow_env = getenv("SR_BLUR_SEQUENTIAL");   // test hook: force the recurrence kernels
+    const bool force_seq = slow_env && atoi(slow_env) != 0;
+    const size_t smem = (size_t)(w + k - 1) * sizeof(double);
+    if (force_seq || smem > 200 * 1024 || k < 1) {
+        blur_rows_kernel<<<cdiv(h, 64), 64, 0, ctx->stream>>>(d_src, w, h, k, rows);
+        SR_LAUNCHED(ctx);
+        blur_cols_kernel<<<cdiv(w, 64), 64, 0, ctx->stream>>>(rows, w, h, k, d_dst);
+        SR_LAUNCHED(ctx);
+        return SR_OK;
+    }
+    const int he = h + k - 1;
+    // scratch: prefix array (he x w) + segment sums (NSEG x w) + 4-int flag
+    char* buf = (char*)sr_scratch(ctx, 15, ((size_t)he * w + (size_t)BLUR_NSEG * w) * sizeof(double) + 64);
+    if (!buf) return SR_E_CUDA;
+    double* pe = (double*)buf; double* seg = pe + (size_t)he * w; int* flag = (int*)(seg + (size_t)BLUR_NSEG * w);
+    static const int flag_init[4] = {-1000, 1000, 0, 0};
+    SR_CUDA(ctx, cudaMemcpyAsync(flag, flag_init, sizeof flag_init, cudaMemcpyHostToDevice, ctx->stream));
+    size_t n = (size_t)w * h;
+    blur_exact_check_kernel<<<148 * 4, 256, 0, ctx->stream>>>(d_src, n, flag);
     SR_LAUNCHED(ctx);
-    blur_cols_kernel<<<cdiv(w, 64), 64, 0, ctx->stream>>>(rows, w, h, k, d_dst);
+    static bool configured = false;
+    if (!configured) {
+        SR_CUDA(ctx, cudaFuncSetAttribute(blur_rows_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured = true;
+    }
+    blur_rows_fast_kernel<<<h, BLUR_T, smem, ctx->stream>>>(d_src, w, h, k, rows, flag);
+    SR_LAUNCHED(ctx);
+    dim3 gs(cdiv(w, 128), BLUR_NSEG);
+    blur_cols_seg_kernel<<<gs, 128, 0, ctx->stream>>>(rows, w, h, k, seg, flag);
+    SR_LAUNCHED(ctx);
+    blur_cols_prefix_kernel<<<gs, 128, 0, ctx->stream>>>(rows, w, h, k, seg, pe, flag);
+    SR_LAUNCHED(ctx);
+    blur_cols_out_kernel<<<dim3(cdiv(w, 128), h), 128, 0, ctx->stream>>>(pe, w, h, k, d_dst, flag);
+    SR_LAUNCHED(ctx);
+    // inputs outside the proof (huge dynamic range, inf/NaN): the recurrences, exactly as OpenCV runs them
+    blur_rows_seq_kernel<<<cdiv(h, 64), 64, 0, ctx->stream>>>(d_src, w, h, k, rows, flag);
+    SR_LAUNCHED(ctx);
+    blur_cols_seq_kernel<<<cdiv(w, 64), 64, 0, ctx->stream>>>(rows, w, h, k, d_dst, flag);
     SR_LAUNCHED(ctx);
     return SR_OK;
 }

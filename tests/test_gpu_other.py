@@ -269,3 +269,28 @@ def test_ext_ncc_sliding_kernel(sr, ctx, orc, shape):
     gots = bs.computeDisparityMapRight(1.0, subpixel=True)
     np.testing.assert_array_equal(gots, sp.astype(np.float64))
     assert np.abs(gots - sp).max() <= 1e-3       # north_star tolerance (met exactly)
+
+
+@pytest.mark.parametrize("case", ["u8_integers", "subpixel_narrow", "wide_dynamic_range", "with_inf", "all_zero", "k_larger_than_image"])
+def test_box_blur_order_free_and_sequential_paths(sr, ctx, orc, case):
+    """cv::blur(32F, k x k) of removeDisparityOutliers: the prefix-sum path (taken when every partial sum is
+    exactly representable in fp64) and the sequential OpenCV recurrences (any other input) both equal the
+    oracle's literal RowSum/ColumnSum restatement bit for bit."""
+    rng = np.random.default_rng(17)
+    h, w, k = 77, 133, 21
+    if case == "u8_integers":
+        d = rng.integers(0, 256, (h, w)).astype(np.float32)
+    elif case == "subpixel_narrow":
+        d = (rng.integers(1 << 10, 1 << 19, (h, w)) / 1024.0).astype(np.float32)       # [1, 512), 10 fractional bits
+    elif case == "wide_dynamic_range":
+        d = (rng.standard_normal((h, w)) * 10.0 ** rng.integers(-12, 12, (h, w))).astype(np.float32)
+    elif case == "with_inf":
+        d = rng.integers(0, 256, (h, w)).astype(np.float32); d[5, 7] = np.inf; d[40, 100] = -np.inf
+    elif case == "all_zero":
+        d = np.zeros((h, w), np.float32)
+    else:
+        d = rng.integers(0, 64, (h, w)).astype(np.float32); k = 301                    # window wider and taller than the map
+    with np.errstate(invalid="ignore", over="ignore"):
+        want = orc.box_blur(d, k)
+    got = sr.reconstruction.boxBlur(d, k, ctx=ctx)
+    assert got.tobytes() == want.tobytes()

@@ -50,6 +50,35 @@ if "c1" not in skip:
         search_case("config1-shape", 1436, 992, 145, 17, "ssd", smooth=sm)
     search_case("config2-shape-lr", 1436, 992, 145, 17, "ssd", lr_check=True)
     search_case("config2-shape-lr-subpix", 1436, 992, 145, 17, "sad", lr_check=True, subpixel=True)
+    # main.cpp:40-65 as one device pipeline on the config-1/2 shape: search (block 17, smooth 0.9) -> 8-bit hand-off ->
+    # outlier removal (k = 500) -> depth -> vertices -> faces; the disparity map never leaves HBM (outputs NULL = timing
+    # of the kernels only, n_faces is the only D2H)
+    import ctypes as C
+    w, h, D = 1436, 992, 145
+    L, R = synth.synth_pair(0xB200, 0, w, h, 0, D)
+    pair = capi.Pair(ctx, w, h, w, h)
+    pair.upload(L, R)
+    p = capi.search_params(block=17, min_disp=0, max_disp=D, smooth=0.9)
+    nf = C.c_uint32(0)
+    null = C.c_void_p(None)
+
+    def pipeline():
+        pair.run(p)
+        ctx.check(ctx._l.sr_pair_reconstruct(ctx.h, pair.h, 1, 500, C.c_float(1.5), C.c_float(0.8), C.c_float(2000.0), C.c_float(1.0),
+                                             C.c_float(2000.0), C.c_float(2000.0), C.c_float(w / 2), C.c_float(h / 2), C.c_float(1.0),
+                                             null, null, null, null, C.byref(nf)))
+    for _ in range(2):
+        pipeline()
+    ctx.sync()
+    t0 = time.perf_counter()
+    for _ in range(a.iters):
+        pipeline()
+    ctx.sync()
+    dt = (time.perf_counter() - t0) / a.iters
+    print(json.dumps({"case": "main.cpp-pipeline-resident", "w": w, "h": h, "D": D, "block": 17, "smooth": 0.9,
+                      "ms": round(dt * 1e3, 4), "faces": int(nf.value),
+                      "note": "search + u8 hand-off + removeDisparityOutliers(500) + depth + back-projection + face list, host-timed incl. the n_faces read"}), flush=True)
+    pair.close()
 if "c3" not in skip:
     for block in (5, 9, 15):
         for cost in ("ssd", "sad", "ncc"):
