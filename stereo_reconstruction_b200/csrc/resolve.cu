@@ -225,20 +225,21 @@ __global__ void __launch_bounds__(32) smooth_raster_warp_kernel(int rows, int wo
             F0[k] = (up[k] & a1) | (~up[k] & a0);
             F1[k] = (up[k] & a2) | (~up[k] & a1);
         }
-        // transfer function of this lane's KW words
+        // this lane's KW words resolved for both possible carries into the lane; their last carries are the
+        // lane's transfer function
+        uint32_t z0[KW], z1[KW];
         uint32_t c0 = 0, c1 = 1;
 #pragma unroll
         for (int k = 0; k < KW; k++) {
-            c0 = chain_word(F0[k], F1[k], c0, monotone) >> 31;
-            c1 = chain_word(F0[k], F1[k], c1, monotone) >> 31;
+            z0[k] = chain_word(F0[k], F1[k], c0, monotone); c0 = z0[k] >> 31;
+            z1[k] = chain_word(F0[k], F1[k], c1, monotone); c1 = z1[k] >> 31;
         }
         uint32_t G = __ballot_sync(0xffffffffu, c0), P = __ballot_sync(0xffffffffu, c1);
         uint32_t zz = chain_word(G, P, 0u, monotone);         // carry out of every lane (x == 0 has carry-in 0)
-        uint32_t c = ((zz << 1) >> lane) & 1u;                // carry into this lane
+        const bool cin = ((zz << 1) >> lane) & 1u;            // carry into this lane: picks one of the two solutions
 #pragma unroll
         for (int k = 0; k < KW; k++) {
-            uint32_t z = chain_word(F0[k], F1[k], c, monotone);
-            c = z >> 31;
+            uint32_t z = cin ? z1[k] : z0[k];
             up[k] = z;
             if (w0 + k < words) zbits[(size_t)y * words + w0 + k] = z;
         }
