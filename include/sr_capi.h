@@ -79,6 +79,10 @@ const char* sr_version(void);
 /* Pinned host memory for callers that want direct DMA (e.g. a cv::MatAllocator). */
 int sr_host_alloc(void** p, size_t bytes);
 int sr_host_free(void* p);
+/* Pins an existing host buffer (cv::Mat data, std::vector storage, ...) in place so that uploads / downloads
+ * are direct DMA and sr_block_search can overlap them with the search; undo with sr_host_unregister. */
+int sr_host_register(void* p, size_t bytes);
+int sr_host_unregister(void* p);
 /* The context's CUDA stream (cudaStream_t) and a CUDA-event stopwatch on it. */
 void* sr_ctx_stream(sr_ctx* ctx);
 int sr_ctx_sync(sr_ctx* ctx);

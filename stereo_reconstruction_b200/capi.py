@@ -48,7 +48,7 @@ SYMBOLS = [
     "sr_ctx_create", "sr_ctx_destroy", "sr_last_error", "sr_version", "sr_host_alloc", "sr_host_free",
     "sr_ctx_stream", "sr_ctx_sync", "sr_timer_start", "sr_timer_stop", "sr_kernel_launches", "sr_last_kernel",
     "sr_block_search", "sr_block_search_batch", "sr_pair_create", "sr_pair_destroy", "sr_pair_upload",
-    "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block", "sr_search_left_disparity", "sr_pair_search_band", "sr_search_pack16", "sr_search_unpack16", "sr_search_result16_dev",
+    "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block", "sr_search_left_disparity", "sr_pair_search_band", "sr_host_register", "sr_host_unregister", "sr_search_pack16", "sr_search_unpack16", "sr_search_result16_dev",
     "sr_search_effective_evals", "sr_remove_outliers", "sr_box_blur", "sr_scale", "sr_disparity_to_depth",
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
     "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
@@ -182,6 +182,17 @@ def pinned_empty(shape, dtype):
     arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
     arr.flags.writeable = True
     return arr, p
+
+
+def host_register(a):
+    """Pins a numpy array's memory in place (sr_host_register); pair with host_unregister."""
+    rc = lib().sr_host_register(C.c_void_p(a.ctypes.data), C.c_size_t(a.nbytes))
+    if rc != OK:
+        raise SrError(rc, "sr_host_register failed")
+
+
+def host_unregister(a):
+    lib().sr_host_unregister(C.c_void_p(a.ctypes.data))
 
 
 def free_pinned(p):

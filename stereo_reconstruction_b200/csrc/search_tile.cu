@@ -78,13 +78,17 @@ __device__ __forceinline__ uint4 lds128(uint32_t saddr) {
 template <int COST, bool ADD>
 __device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], uint32_t slot, uint32_t lane_b,
                                                 const uint32_t (&uo)[5], uint32_t colmask) {
-    uint4 la = lds128((slot + uo[0]) + lane_b);
+    // all nine LDS.128 of the row first (36 registers: the WTA's key / halo registers are dead here), then the
+    // 64 pointwise updates: the load latency is paid once per phase instead of once per 16-column group
+    uint4 lv[5], rv[4];
+#pragma unroll
+    for (int k = 0; k < 5; k++) lv[k] = lds128((slot + uo[k]) + lane_b);
+#pragma unroll
+    for (int k = 0; k < 4; k++) rv[k] = lds128(slot + lane_b + 16 * k);
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        uint4 lbv = lds128((slot + uo[k + 1]) + lane_b);
-        uint4 rr = lds128(slot + lane_b + 16 * k);
-        uint32_t l7[7] = {la.x, la.y, la.z, la.w, lbv.x, lbv.y, lbv.z};
-        uint32_t r4[4] = {rr.x, rr.y, rr.z, rr.w};
+        uint32_t l7[7] = {lv[k].x, lv[k].y, lv[k].z, lv[k].w, lv[k + 1].x, lv[k + 1].y, lv[k + 1].z};
+        uint32_t r4[4] = {rv[k].x, rv[k].y, rv[k].z, rv[k].w};
 #pragma unroll
         for (int jj = 0; jj < 4; jj++)
 #pragma unroll
@@ -92,7 +96,6 @@ __device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], uint32_
                 if (ADD) col[4 * k + jj][t] = pcost_add<COST>(l7[jj + t], r4[jj], col[4 * k + jj][t]);
                 else col[4 * k + jj][t] -= pcost_add<COST>(l7[jj + t], r4[jj], 0u);
             }
-        la = lbv;
     }
     if (colmask != 0xFFFFu) {
 #pragma unroll

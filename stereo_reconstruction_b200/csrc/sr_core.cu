@@ -107,6 +107,13 @@ int sr_host_alloc(void** p, size_t bytes) {
     return cudaMallocHost(p, bytes ? bytes : 1) == cudaSuccess ? SR_OK : SR_E_CUDA;
 }
 int sr_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? SR_OK : SR_E_CUDA; }
+int sr_host_register(void* p, size_t bytes) {
+    if (!p || !bytes) return SR_E_BADARG;
+    cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); return SR_OK; }
+    return e == cudaSuccess ? SR_OK : SR_E_CUDA;
+}
+int sr_host_unregister(void* p) { return p && cudaHostUnregister(p) == cudaSuccess ? SR_OK : SR_E_CUDA; }
 
 void* sr_ctx_stream(sr_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 int sr_ctx_sync(sr_ctx* ctx) {

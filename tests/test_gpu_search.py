@@ -186,3 +186,24 @@ def test_int16_wire_format(sr, ctx, orc):
     with pytest.raises(capi.SrError):
         pair.download(ps)
     pair.close()
+
+
+def test_host_register_enables_the_pipeline(sr, ctx, orc, monkeypatch):
+    """sr_host_register pins caller-owned buffers in place (a cv::Mat's data): sr_block_search then takes the
+    row-chunk pipeline exactly as with sr_host_alloc memory."""
+    capi = sr.capi
+    w, h, D = 640, 300, 40
+    L, R = synth(orc, w, h, 0, D, seed=19)
+    out = np.zeros((h, w), np.float64)
+    monkeypatch.setenv("SR_PIPE_CHUNKS", "4")
+    p = capi.search_params(block=9, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD)
+    for a in (L, R, out):
+        capi.host_register(a)
+    try:
+        n0 = ctx.launches
+        capi.block_search(ctx, L, R, p, out=out)
+        assert ctx.launches - n0 >= 4 * 2
+        np.testing.assert_array_equal(out, orc.block_search_right_fast(L, R, 9, 0, D, 1.0, cost=1))
+    finally:
+        for a in (L, R, out):
+            capi.host_unregister(a)
