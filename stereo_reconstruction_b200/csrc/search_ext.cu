@@ -58,6 +58,7 @@ struct ExtGeom {
     int row0;             // first output row of the launch (grid.y rows from here)
     int ix0, ix1, iy0, iy1;   // pixels inside [ix0,ix1) x [iy0,iy1) are someone else's (NCC interior): skipped
     int row1;                 // end row of the launch when the border frame is enumerated compactly
+    int no_black;             // 1: the black-pixel rule is applied by a later kernel (mirror-packed searches)
 };
 
 // Universal extension kernel: one thread per reference pixel.
@@ -153,7 +154,7 @@ __global__ void __launch_bounds__(128) ncc_border_warp_kernel(const uint32_t* __
     size_t o = (size_t)y * g.wr + x;
     int dbest = 0;
     float dsub = 0.0f;
-    if (y < g.height && (__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) != 0) {
+    if (y < g.height && (g.no_black || (__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) != 0)) {
         int l = min(x, g.half), r = min(g.wr - x - 1, g.half), u = min(y, g.half), dn = min(g.hr - y - 1, g.half);
         int ww = l + r, wh = u + dn;
         long long n = (long long)ww * wh * 3;
@@ -240,7 +241,7 @@ __global__ void __launch_bounds__(128) ncc_merge_kernel(const uint32_t* __restri
     size_t o = (size_t)y * g.wr + x;
     int dbest = 0;
     float dsub = 0.0f;
-    if ((__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) != 0) {
+    if (g.no_black || (__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) != 0) {
         float best = -INFINITY; int bd = -1;
         for (int p = 0; p < npass; p++) {
             float s = __ldg(pscore + (size_t)p * stride + o);
@@ -279,6 +280,15 @@ __global__ void __launch_bounds__(128) left_from_mirror_planes_kernel(const uint
         }
     }
     disp[(size_t)y * w1 + x] = dbest;
+}
+
+// mirrored-coordinate map (column w1-1-x) of a search on the mirror-packed pair -> left map, black rule on L
+__global__ void __launch_bounds__(128) unflip_left_kernel(const uint32_t* __restrict__ Lp, int pitchL, int w1, int h1, int height,
+                                                          const int* __restrict__ disp_m, int* __restrict__ disp) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= w1) return;
+    bool on = y < height && (__ldg(Lp + (size_t)y * pitchL + x) & 0xFFFFFFu) != 0;
+    disp[(size_t)y * w1 + x] = on ? disp_m[(size_t)y * w1 + (w1 - 1 - x)] : 0;
 }
 
 // LR check + conversion to the CV_64F output map.
@@ -352,7 +362,7 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
         sg.dlo = dlo; sg.dhi = dhi > w1 ? w1 : dhi; if (sg.dhi < sg.dlo) sg.dhi = sg.dlo;
         sg.row0 = row0; sg.row1 = row1;
         float* ps = nullptr; int* pd = nullptr;
-        int handled = sg.dhi > sg.dlo ? sr_launch_search_ncc(ctx, pair, sg, &ps, &pd) : 0;
+        int handled = sg.dhi > sg.dlo ? sr_launch_search_ncc(ctx, pair, sg, &ps, &pd, &pair->ncc_tab) : 0;
         if (handled < 0) return handled;
         if (handled) {
             ncc_tiled = true;
@@ -398,7 +408,7 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
         // [x-h, x+h) for x = w1-1-xc, its column range [0, w1-1) is the left image's, and its break rule
         // d < w1 - xc - min(w1-1-xc, h) is d <= x - min(x, h).  Needs w1 <= w2 (no partner beyond R).
         bool mirrored = false;
-        if (p->cost != SR_COST_NCC && half >= 1 && half <= 8 && w1 > 1 && h1 > 1 && w1 <= w2) {
+        if (half >= 1 && half <= 8 && w1 > 1 && h1 > 1 && w1 <= w2) {
             int rc;
             if (!pair->Lm.base) {
                 if ((rc = sr_alloc_packed(ctx, &pair->Lm, w1, h1, w1 + 704)) != SR_OK) return rc;
@@ -412,15 +422,46 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
             sg.row0 = 0; sg.row1 = h1;
             PackedImage keepL = pair->L, keepR = pair->R;
             pair->L = pair->Rm; pair->R = pair->Lm;   // tile roles: "left" = searched image, "right" = reference image
-            int handled = sr_launch_search_tile(ctx, pair, sg, p->cost, 0);
+            int handled = 0;
+            float* ps = nullptr; int* pd = nullptr;
+            if (p->cost != SR_COST_NCC) handled = sr_launch_search_tile(ctx, pair, sg, p->cost, 0);
+            else if (sg.dhi > sg.dlo) handled = sr_launch_search_ncc(ctx, pair, sg, &ps, &pd, &pair->ncc_tab_m);
+            PackedImage mL = pair->L, mR = pair->R;
             pair->L = keepL; pair->R = keepR;
             if (handled < 0) return handled;
-            if (handled) {
+            if (handled && p->cost != SR_COST_NCC) {
                 mirrored = true;
                 left_from_mirror_planes_kernel<<<dim3(cdiv(w1, 128), h1), 128, 0, ctx->stream>>>(
                     pair->L.px, pair->L.pitch, w1, h1, g.height, pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase, disp_l);
                 SR_LAUNCHED(ctx);
                 ctx->last_kernel = tiled ? "tile+ext+mirror" : "ext-direct+mirror";
+            } else if (handled) {
+                // NCC: interior from the (score, d) planes, border frame by the warp-per-pixel kernel, both in mirrored
+                // coordinates without the black rule; the un-flip applies it on the left image
+                mirrored = true;
+                int* disp_m = (int*)sr_scratch(ctx, 13, pair->npx_cap * sizeof(int));
+                if (!disp_m) return SR_E_CUDA;
+                ExtGeom gm{w1, h1, w1, h2, g.height, half, sg.dlo, sg.dhi, 0, p->cost, 0};
+                gm.no_black = 1; gm.row1 = h1;
+                gm.ix0 = half; gm.ix1 = w1 - half; gm.iy0 = half;
+                gm.iy1 = h1 < g.height ? h1 : g.height;
+                if (gm.iy1 > h1 - half) gm.iy1 = h1 - half;
+                if (gm.iy1 > h2 - half) gm.iy1 = h2 - half;
+                if (gm.iy1 < gm.iy0) gm.iy1 = gm.iy0;
+                if (gm.iy1 > gm.iy0 && gm.ix1 > gm.ix0) {
+                    ncc_merge_kernel<<<dim3(cdiv(gm.ix1 - gm.ix0, 128), gm.iy1 - gm.iy0), 128, 0, ctx->stream>>>(
+                        mL.px, mL.pitch, mR.px, mR.pitch, gm, ps, pd, pair->npx_cap, pair->npass, 0, disp_m, nullptr);
+                    SR_LAUNCHED(ctx);
+                } else { gm.ix1 = gm.ix0 + 1; gm.iy1 = gm.iy0; }   // no interior: every pixel is "border" (ix1 > ix0 keeps the compact form)
+                long nborder = (long)h1 * w1 - (long)(gm.iy1 - gm.iy0) * (gm.ix1 - gm.ix0);
+                if (nborder > 0) {
+                    ncc_border_warp_kernel<<<(unsigned)((nborder * 32 + 127) / 128), 128, 0, ctx->stream>>>(
+                        mL.px, mL.pitch, mR.px, mR.pitch, gm, nborder, disp_m, nullptr);
+                    SR_LAUNCHED(ctx);
+                }
+                unflip_left_kernel<<<dim3(cdiv(w1, 128), h1), 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, w1, h1, g.height, disp_m, disp_l);
+                SR_LAUNCHED(ctx);
+                ctx->last_kernel = ncc_tiled ? "ncc-tile+ext+mirror" : "ext-direct+mirror";
             }
         }
         if (!mirrored) {

@@ -352,7 +352,7 @@ static int build_tables(sr_ctx* ctx, const PackedImage& img, int half, int ya, i
 
 // Interior pixels of the right-referenced NCC search -> per-pass (score, d) planes in ctx scratch 0.
 // Returns 1 when it ran, 0 when the shape is not supported (caller falls back), < 0 on error.
-int sr_launch_search_ncc(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, float** pscore, int** pdisp) {
+int sr_launch_search_ncc(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, float** pscore, int** pdisp, void** tab) {
     const int h = g.half;
     if (h < 1 || h > 8) return 0;
     if (g.w2 < 2 * h + 2 || g.h2 < 2 * h + 2 || g.w1 < 2 * h + 2 || g.h1 < 2 * h + 2) return 0;
@@ -373,13 +373,14 @@ int sr_launch_search_ncc(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, float*
     // "no candidate" everywhere: score NaN (never > best), d = -1
     SR_CUDA(ctx, cudaMemsetAsync(planes, 0xFF, (size_t)a.npass * npx * 2 * sizeof(uint32_t), ctx->stream));
     if (r1 <= r0) return 1;
-    if (!pair->ncc_tab) {
+    // tables of the images currently bound to pair->L / pair->R (the mirrored search binds its own pair and table)
+    if (!*tab) {
         size_t nl = (size_t)pair->L.pitch * pair->L.h, nr = (size_t)pair->R.pitch * pair->R.h;
-        SR_CUDA(ctx, cudaMalloc(&pair->ncc_tab, (2 * nl + 2 * nr) * 4));
-        SR_CUDA(ctx, cudaMemsetAsync(pair->ncc_tab, 0, (2 * nl + 2 * nr) * 4, ctx->stream));
+        SR_CUDA(ctx, cudaMalloc(tab, (2 * nl + 2 * nr) * 4));
+        SR_CUDA(ctx, cudaMemsetAsync(*tab, 0, (2 * nl + 2 * nr) * 4, ctx->stream));
     }
     size_t nl = (size_t)pair->L.pitch * pair->L.h, nr = (size_t)pair->R.pitch * pair->R.h;
-    int32_t* nsl = (int32_t*)pair->ncc_tab; float* rl = (float*)(nsl + nl);
+    int32_t* nsl = (int32_t*)*tab; float* rl = (float*)(nsl + nl);
     int32_t* srt = (int32_t*)(rl + nl); float* rrt = (float*)(srt + nr);
     int rc;
     if ((rc = build_tables(ctx, pair->L, h, r0, r1, 1, nsl, rl)) != SR_OK) return rc;

@@ -77,6 +77,7 @@ struct sr_pair {
     int last_row0 = 0, last_row1 = 0;
     bool evals_valid = false;
     void* ncc_tab = nullptr;              // window-moment tables of the NCC search (search_ncc.cu)
+    void* ncc_tab_m = nullptr;            // the same for the mirror-packed pair (left-referenced NCC search)
     const int* disp_left = nullptr;       // left-referenced map of the last lr_check run (ctx scratch)
     SearchGeom last_geom;
 };
@@ -123,6 +124,6 @@ int sr_launch_search_left(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, d
 int sr_launch_search_linear(sr_ctx* ctx, sr_pair* pair, double smooth);
 int sr_launch_count_evals(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g);
 // NCC through sliding sums: interior pixels -> per-pass (score, d) planes (search_ncc.cu)
-int sr_launch_search_ncc(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, float** pscore, int** pdisp);
+int sr_launch_search_ncc(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, float** pscore, int** pdisp, void** tab);
 // NCC / sub-pixel / LR-check extension path (search_ext.cu)
 int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1);

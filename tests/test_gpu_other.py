@@ -209,7 +209,7 @@ def test_batch_api(sr, ctx, orc):
         np.testing.assert_array_equal(outs[i], sp.astype(np.float64))
 
 
-@pytest.mark.parametrize("cost", [0, 1])
+@pytest.mark.parametrize("cost", [0, 1, 2])
 @pytest.mark.parametrize("shape", [
     # (w1, h1, w2, h2, block, min_d, max_d, quant)
     (280, 50, 280, 50, 9, 0, 40, False),
