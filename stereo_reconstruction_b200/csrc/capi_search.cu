@@ -187,7 +187,10 @@ int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row
     pair->evals_valid = false;
     pair->disp_left = nullptr;
     {
-        int init0[2] = {p->block, SR_OK};   // "max block size" (BlockSearch.cpp:98) and the device status word
+        // "max block size" (BlockSearch.cpp:98) and the device status word.  A small pageable H2D copy (staged by the
+        // driver at call time) on purpose: a 1-thread kernel would have to wait for an SM behind the previous chunk's
+        // one-CTA-per-SM search grid and measurably delays the row-chunk pipeline.
+        int init0[2] = {p->block, SR_OK};
         SR_CUDA(ctx, cudaMemcpyAsync(pair->maxblock, init0, sizeof init0, cudaMemcpyHostToDevice, ctx->stream));
     }
     if (p->variant == SR_VARIANT_LEFT) {
@@ -226,8 +229,6 @@ int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row
         return sr_fail(ctx, SR_E_BADARG, "row bands need smooth == 1 (the smoothing rule is a raster dependency)");
     pair->ow = g.w2; pair->oh = g.h2;
     pair->last_row0 = g.row0; pair->last_row1 = g.row1;
-    int init[2] = {p->block, SR_OK};
-    SR_CUDA(ctx, cudaMemcpyAsync(pair->maxblock, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
     bool degenerate = g.half == 0 || g.w2 == 1 || g.h2 == 1;  // empty windows: every cost is NaN
     int handled = 0;
     if (!p->var_block && !degenerate) {

@@ -327,8 +327,6 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
     row1 = row1 > h2 ? h2 : row1;
     if (p->lr_check && (row0 != 0 || row1 != h2)) return sr_fail(ctx, SR_E_BADARG, "lr_check needs the full image (no row bands)");
     pair->ow = w2; pair->oh = h2; pair->last_row0 = row0; pair->last_row1 = row1;
-    int init[2] = {p->block, SR_OK};
-    SR_CUDA(ctx, cudaMemcpyAsync(pair->maxblock, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
     if (row1 <= row0) return SR_OK;
     size_t npx = pair->npx_cap;
     int* disp_r = (int*)sr_scratch(ctx, 14, npx * 4 * 2);
