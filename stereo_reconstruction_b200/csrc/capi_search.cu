@@ -1,6 +1,8 @@
 // capi_search.cu -- WindowSearch entry points of the C-ABI (dispatch, download, one-shot calls).
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 #include "sr_internal.cuh"
 
 static int rows_fit(int h1, int h2, int half) {
@@ -66,16 +68,20 @@ static int pipeline_chunks(const sr_pair* pair, const sr_search_params* p, int r
     return c < 1 ? 1 : c;
 }
 
-// first row of chunk c of n (c == n: the end) when `rows` rows are cut into n chunks whose first and
-// last chunk have edge_w (< 1) times the weight of the inner ones
+// First row of chunk c of n (c == n: the end) when `rows` rows are cut into n weighted chunks: a short first
+// chunk starts the search early; the last two chunks shrink (their downloads queue behind each other once the
+// search is over, so little data should be left by then); the chunks in between are equal.
 static int chunk_start(int rows, int n, int c, int half) {
     if (c <= 0) return 0;
     if (c >= n) return rows;
-    const char* env = getenv("SR_PIPE_EDGE");
-    double edge_w = env ? atof(env) : 0.45;
-    if (n < 3 || edge_w <= 0.0 || edge_w > 1.0) edge_w = 1.0;
-    double total = (n - 2) + 2 * edge_w;
-    double upto = edge_w + (c - 1);            // weight of chunks 0..c-1
+    static const char* e0 = getenv("SR_PIPE_EDGE");
+    static const char* e1 = getenv("SR_PIPE_EDGE_LAST");
+    static const char* e2 = getenv("SR_PIPE_EDGE_PEN");
+    double w_first = e0 ? atof(e0) : 0.45, w_last = e1 ? atof(e1) : 0.3, w_pen = e2 ? atof(e2) : 0.6;
+    if (n < 4) { w_first = w_last = w_pen = 1.0; }
+    auto weight = [&](int i) { return i == 0 ? w_first : i == n - 1 ? w_last : i == n - 2 ? w_pen : 1.0; };
+    double total = 0, upto = 0;
+    for (int i = 0; i < n; i++) { total += weight(i); if (i < c) upto += weight(i); }
     int r = (int)(rows * upto / total + 0.5);
     int minrows = 2 * half + 2;
     if (r < c * minrows) r = c * minrows;       // every chunk keeps at least a window's worth of rows
@@ -119,6 +125,14 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     SR_CUDA(ctx, cudaStreamWaitEvent(s_up, ev_start, 0));
     SR_CUDA(ctx, cudaStreamWaitEvent(s_down, ev_start, 0));
     SR_CUDA(ctx, cudaStreamWaitEvent(ctx->aux[2], ev_start, 0));
+    // SR_PIPE_TRACE=1: per-chunk timeline (ms since the start of the call) on stderr, development aid
+    static const bool trace = getenv("SR_PIPE_TRACE") && atoi(getenv("SR_PIPE_TRACE")) != 0;
+    std::vector<cudaEvent_t> tev;
+    if (trace) {
+        tev.resize(4 * nch + 1);
+        for (auto& e : tev) cudaEventCreate(&e);
+        cudaEventRecord(tev[4 * nch], compute);
+    }
     int up0 = band0 - half > 0 ? band0 - half : 0;   // first image row the band's windows read
     int upL = up0 < pair->h1 ? up0 : pair->h1, upR = up0 < pair->h2 ? up0 : pair->h2, rc = SR_OK;
     const size_t rowL = (size_t)left->w * 3, rowR = (size_t)right->w * 3;
@@ -154,22 +168,35 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
         // the last wave of chunk c leaves idle (one 512-thread CTA per SM, so no other overlap exists)
         cudaStream_t cs = (c & 1) ? ctx->aux[2] : compute;
         SR_CUDA(ctx, cudaEventRecord(ctx->pipe_ev[2 * c], s_up));
+        if (trace) cudaEventRecord(tev[4 * c], s_up);
         SR_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->pipe_ev[2 * c], 0));
+        if (trace) cudaEventRecord(tev[4 * c + 1], cs);
         ctx->stream = cs;
         rc = sr_search_run(ctx, pair, p, r0, r1);
         ctx->stream = compute;
         if (rc != SR_OK) break;
+        if (trace) cudaEventRecord(tev[4 * c + 2], cs);
         if (!disp_out) continue;
         SR_CUDA(ctx, cudaEventRecord(ctx->pipe_ev[2 * c + 1], cs));
         SR_CUDA(ctx, cudaStreamWaitEvent(s_down, ctx->pipe_ev[2 * c + 1], 0));
         cudaError_t e = cudaMemcpy2DAsync((char*)disp_out + (size_t)r0 * out_pitch, out_pitch, pair->out + (size_t)r0 * ow, rowb, rowb,
                                           r1 - r0, cudaMemcpyDeviceToHost, s_down);
         if (e != cudaSuccess) rc = sr_cuda_check(ctx, e, "cudaMemcpy2DAsync(D2H rows)");
+        if (trace) cudaEventRecord(tev[4 * c + 3], s_down);
     }
     cudaStreamSynchronize(s_up);
     cudaStreamSynchronize(compute);
     cudaStreamSynchronize(ctx->aux[2]);
     cudaStreamSynchronize(s_down);
+    if (trace) {
+        for (int c = 0; c < nch && rc == SR_OK; c++) {
+            float t[4] = {0, 0, 0, 0};
+            for (int k = 0; k < 4; k++)
+                if (k < 3 || disp_out) cudaEventElapsedTime(&t[k], tev[4 * nch], tev[4 * c + k]);
+            fprintf(stderr, "[pipe] chunk %d: upload done %.3f  search start %.3f  end %.3f  download done %.3f\n", c, t[0], t[1], t[2], t[3]);
+        }
+        for (auto& e : tev) cudaEventDestroy(e);
+    }
     if (rc != SR_OK) return rc;
     pair->last_row0 = band0; pair->last_row1 = band1;
     pair->last_geom.row0 = band0; pair->last_geom.row1 = band1;
