@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(128) ext_direct_kernel(const uint32_t* __restr
 __global__ void __launch_bounds__(128) ncc_border_warp_kernel(const uint32_t* __restrict__ Lp, int pitchL,
                                                               const uint32_t* __restrict__ Rp, int pitchR, ExtGeom g,
                                                               long npix, int* __restrict__ disp, float* __restrict__ subpix) {
+    __shared__ uint32_t rwin[4][256];                        // one right window per warp
     const int lane = threadIdx.x & 31;
     long idx = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (idx >= npix) return;
@@ -159,9 +160,33 @@ __global__ void __launch_bounds__(128) ncc_border_warp_kernel(const uint32_t* __
         int ww = l + r, wh = u + dn;
         long long n = (long long)ww * wh * 3;
         int dmax = min(g.dhi, g.wo - x - r);                 // candidates d in [dlo, dmax): before the break
+        // the right window is the same for every candidate: staged once per warp, its moments summed once
+        uint32_t* rw = rwin[threadIdx.x >> 5];
+        const int npw = ww * wh;                              // <= 16 x 16 (half <= 8 on this path)
+        uint32_t s_r = 0, s_rr = 0;
+        for (int i = lane; i < npw; i += 32) {
+            uint32_t q = __ldg(Rp + (size_t)(y - u + i / ww) * pitchR + (x - l + i % ww));
+            rw[i] = q;
+            s_r = __dp4a(q, 0x01010101u, s_r); s_rr = __dp4a(q, q, s_rr);
+        }
+        s_r = __reduce_add_sync(0xffffffffu, s_r); s_rr = __reduce_add_sync(0xffffffffu, s_rr);
+        __syncwarp();
+        auto cost_of = [&](int d) -> float {
+            if (!n) return INFINITY;
+            uint32_t sl = 0, sll = 0, slr = 0;                // window totals fit 32 bits (<= 256 pixels)
+            for (int rr_ = 0; rr_ < wh; rr_++) {
+                const uint32_t* lrow = Lp + (size_t)(y - u + rr_) * pitchL + (x + d - l);
+                for (int i = 0; i < ww; i++) {
+                    uint32_t lp = __ldg(lrow + i), q = rw[rr_ * ww + i];
+                    sl = __dp4a(lp, 0x01010101u, sl); sll = __dp4a(lp, lp, sll); slr = __dp4a(lp, q, slr);
+                }
+            }
+            WStats st = {(long long)sl, (long long)s_r, (long long)sll, (long long)s_rr, (long long)slr, 0, 0};
+            return ncc_cost(st, n);
+        };
         float best = INFINITY; int bd = -1;
         for (int d = g.dlo + lane; d < dmax; d += 32) {
-            float c = n ? ncc_cost(window_stats(Lp, pitchL, x + d - l, Rp, pitchR, x - l, y - u, ww, wh, true), n) : INFINITY;
+            float c = cost_of(d);
             if (c < best) { best = c; bd = d; }
         }
 #pragma unroll
@@ -178,10 +203,7 @@ __global__ void __launch_bounds__(128) ncc_border_warp_kernel(const uint32_t* __
             if (subpix && bd - 1 >= g.dlo && bd + 1 < dmax) {
                 // lanes 0 / 1 recompute the two neighbours of the winner
                 float cn = INFINITY;
-                if (lane < 2) {
-                    int d = bd - 1 + 2 * lane;
-                    cn = n ? ncc_cost(window_stats(Lp, pitchL, x + d - l, Rp, pitchR, x - l, y - u, ww, wh, true), n) : INFINITY;
-                }
+                if (lane < 2) cn = cost_of(bd - 1 + 2 * lane);
                 float cm = __shfl_sync(0xffffffffu, cn, 0), cp = __shfl_sync(0xffffffffu, cn, 1);
                 if (isfinite(cm) && isfinite(cp)) dsub = parabola(dsub, cm, best, cp);
             }
