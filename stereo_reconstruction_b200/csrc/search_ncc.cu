@@ -11,8 +11,9 @@
 //   * horizontal window sums S_lr by an in-register sliding sum, halo columns from the next lane(s) by SHFL;
 //   * the d-independent window moments come from tables (ncc_tables: -S_l and rl per left window,
 //     S_r and rr per right window, indexed by the window's first column), staged per row with cp.async;
-//   * per candidate: num as one 64-bit IMAD.WIDE chain, (float)num exactly via a hi/lo split and one FFMA,
-//     two FMULs, compare/select against the running best (strict >: the first disparity wins ties);
+//   * per candidate: num as one 64-bit IMAD.WIDE chain, (float)num by the hardware I2F.S64 (round to nearest, the
+//     conversion the CPU performs; measured faster than an exact hi/lo magic-number split + FFMA, which costs six
+//     issue slots), two FMULs, compare/select against the running best (strict >: the first disparity wins ties);
 //   * (score, d) pairs of the 16 warps are merged through shared memory, one pair per pass of 64
 //     disparities goes to HBM, the passes are merged by ncc_merge_kernel (search_ext.cu).
 // Shared-memory rows use "2 data chunks + 1 pad chunk" per lane (48 B lane stride): LDS.128 conflict-free.
@@ -81,16 +82,6 @@ __device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], uint32_
         }
 }
 
-// (float)num for |num| < 2^38, exactly as a correctly rounded int64 -> fp32 conversion:
-// num = hi * 2^16 + lo with both halves converted exactly by the magic-number trick, one FFMA rounds.
-__device__ __forceinline__ float ll2float_small(long long num) {
-    uint32_t lo32 = (uint32_t)num, hi32 = (uint32_t)((unsigned long long)num >> 32);
-    int hi = (int)__funnelshift_r(lo32, hi32, 16);                       // num >> 16 (arithmetic: |num| < 2^47)
-    float hi_f = __fadd_rn(__int_as_float(hi + 0x4B400000), -12582912.0f);
-    float lo_f = __fadd_rn(__uint_as_float((lo32 & 0xFFFFu) | 0x4B000000u), -8388608.0f);
-    return __fmaf_rn(hi_f, 65536.0f, lo_f);
-}
-
 // Window sums + scores + running best for one output row.  tb: shared address of this row's table slot.
 template <int H2, bool MASKED>
 __device__ __forceinline__ void window_best(const uint32_t (&col)[XT][DT], float (&best)[XT], int (&bd)[XT], uint32_t tb,
@@ -127,7 +118,7 @@ __device__ __forceinline__ void window_best(const uint32_t (&col)[XT][DT], float
         for (int j = 0; j < XT; j++) {
             // num = n * S_lr - S_l * S_r  (|num| < 2^36)
             long long num = (long long)((unsigned long long)S * N) + (long long)nsl[j + t] * (long long)sr[j];
-            float score = __fmul_rn(__fmul_rn(ll2float_small(num), rl[j + t]), rr[j]);
+            float score = __fmul_rn(__fmul_rn(__ll2float_rn(num), rl[j + t]), rr[j]);
             bool better = score > best[j];
             if (MASKED) {
                 int x = x0 + j;
