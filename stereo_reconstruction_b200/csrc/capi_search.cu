@@ -125,6 +125,8 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     SR_CUDA(ctx, cudaStreamWaitEvent(s_up, ev_start, 0));
     SR_CUDA(ctx, cudaStreamWaitEvent(s_down, ev_start, 0));
     SR_CUDA(ctx, cudaStreamWaitEvent(ctx->aux[2], ev_start, 0));
+    SR_CUDA(ctx, cudaStreamWaitEvent(ctx->aux[3], ev_start, 0));
+    static const int ncs = getenv("SR_PIPE_STREAMS") ? atoi(getenv("SR_PIPE_STREAMS")) : 2;
     // SR_PIPE_TRACE=1: per-chunk timeline (ms since the start of the call) on stderr, development aid
     static const bool trace = getenv("SR_PIPE_TRACE") && atoi(getenv("SR_PIPE_TRACE")) != 0;
     std::vector<cudaEvent_t> tev;
@@ -166,7 +168,8 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
         if (rc != SR_OK) break;
         // chunks alternate between two compute streams: the first CTAs of chunk c+1 fill the SMs that
         // the last wave of chunk c leaves idle (one 512-thread CTA per SM, so no other overlap exists)
-        cudaStream_t cs = (c & 1) ? ctx->aux[2] : compute;
+        const int si = ncs >= 3 ? c % 3 : ncs == 2 ? (c & 1) : 0;
+        cudaStream_t cs = si == 0 ? compute : ctx->aux[1 + si];
         SR_CUDA(ctx, cudaEventRecord(ctx->pipe_ev[2 * c], s_up));
         if (trace) cudaEventRecord(tev[4 * c], s_up);
         SR_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->pipe_ev[2 * c], 0));
@@ -187,6 +190,7 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     cudaStreamSynchronize(s_up);
     cudaStreamSynchronize(compute);
     cudaStreamSynchronize(ctx->aux[2]);
+    cudaStreamSynchronize(ctx->aux[3]);
     cudaStreamSynchronize(s_down);
     if (trace) {
         for (int c = 0; c < nch && rc == SR_OK; c++) {

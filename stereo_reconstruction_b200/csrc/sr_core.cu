@@ -70,6 +70,7 @@ int sr_ctx_create(int device, sr_ctx** out) {
         (e = cudaStreamCreateWithPriority(&c->aux[0], cudaStreamNonBlocking, prio_hi)) != cudaSuccess ||
         (e = cudaStreamCreateWithPriority(&c->aux[1], cudaStreamNonBlocking, prio_hi)) != cudaSuccess ||
         (e = cudaStreamCreateWithPriority(&c->aux[2], cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
+        (e = cudaStreamCreateWithPriority(&c->aux[3], cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
         (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
         (e = cudaEventCreate(&c->kev0)) != cudaSuccess || (e = cudaEventCreate(&c->kev1)) != cudaSuccess) {
         int rc = sr_cuda_check(nullptr, e, "stream/event creation");
@@ -96,6 +97,7 @@ void sr_ctx_destroy(sr_ctx* ctx) {
     cudaStreamDestroy(ctx->aux[0]);
     cudaStreamDestroy(ctx->aux[1]);
     cudaStreamDestroy(ctx->aux[2]);
+    cudaStreamDestroy(ctx->aux[3]);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -19,7 +19,7 @@ struct DevBuf {
 struct sr_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaStream_t aux[3] = {nullptr, nullptr, nullptr};  // copy streams of the pipelines + second compute stream
+    cudaStream_t aux[4] = {nullptr, nullptr, nullptr, nullptr};  // copy streams of the pipelines + extra compute streams
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t kev0 = nullptr, kev1 = nullptr;  // around the dominant search kernel of the last run
     bool kev_valid = false;
