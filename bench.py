@@ -286,6 +286,17 @@ def main():
         e2e_t.append(time.perf_counter() - t0)
     barrier()
     clocks = sampler.stop() if sampler else None
+    # the same call with pageable buffers (what a cv::Mat holds): staged through pinned memory by host threads
+    pageable_ms = None
+    if world == 1:
+        out_pg = np.zeros((h, w), np.float64)
+        for _ in range(2):
+            capi.block_search(ctx, L, R, params, out=out_pg)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            capi.block_search(ctx, L, R, params, out=out_pg)
+        pageable_ms = (time.perf_counter() - t0) / 3 * 1e3
+        del out_pg
     t_e2e = torch.tensor([float(np.mean(e2e_t))], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
@@ -324,7 +335,8 @@ def main():
             "nominal_value": w * h * D / (ms_per_step * 1e-3) / 1e6,
             "e2e": {"value": total_evals / e2e_s / 1e6, "unit": "MDE/s", "ms_per_step": e2e_s * 1e3,
                     "h2d_bytes_per_step": int(h2d_rows * w * 3 * 2), "d2h_bytes_per_step": int(w * h * 8),
-                    "api": "sr_block_search (pinned host buffers)" if world == 1 else "sr_pair_search_band (band rows + halo H2D, chunked) + NCCL gather + sr_search_download of the gathered bands"},
+                    "pageable_ms_per_step": pageable_ms,
+                    "api": "sr_block_search (pinned host buffers; pageable_ms_per_step = same call on pageable buffers)" if world == 1 else "sr_pair_search_band (band rows + halo H2D, chunked) + NCCL gather + sr_search_download of the gathered bands"},
             "gpu_launches": int(launches),
             "kernel_family": ctx.last_kernel,
             "clocks": clocks,

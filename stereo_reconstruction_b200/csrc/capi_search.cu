@@ -2,6 +2,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <thread>
 #include <vector>
 #include "sr_internal.cuh"
 
@@ -30,7 +32,7 @@ static int validate(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p) {
 // H2D + pack of chunk c+1 (copy stream 0), search + resolve of chunk c (compute stream) and D2H of
 // chunk c-1 (copy stream 1) overlap; only the first upload and the last download are exposed.
 // Applies where output rows are independent (Right variant, tile kernel, no raster smoothing rule)
-// and both host sides are pinned (a pageable buffer needs a staging memcpy that serialises anyway).
+// Pageable host buffers pass through pinned staging, filled and drained chunk by chunk by the staging threads.
 // ---- int16 wire format of integer disparity maps (band gather) ------------------------------------
 __global__ void pack16_kernel(const double* __restrict__ src, short* __restrict__ dst, size_t n, int* __restrict__ status) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -97,12 +99,57 @@ static bool can_pipeline(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const
     if (pair->w2 == 1 || pair->h2 == 1) return false;
     if (!rows_fit(pair->h1, pair->h2, (p->block - 1) / 2)) return false;
     if (pipeline_chunks(pair, p) < 2) return false;
-    return host_pinned(left->bgr) && host_pinned(right->bgr) && host_pinned(disp_out);
+    return true;   // pageable buffers go through the staging threads (host_stage.cu)
 }
 
 // rows [band0, band1) of the output only (row-band sharding: a rank uploads just the image rows its band
 // and the window halo need); disp_out == nullptr leaves the band in HBM (sr_search_result_dev) for a
 // device-side gather.
+
+// Host side of the pipeline when a buffer is pageable (a cv::Mat): the staging threads copy the image rows
+// of chunk c into pinned staging before the main thread queues that chunk's H2D, and copy finished output
+// chunks from pinned staging to the caller's buffer as their D2H events complete.
+namespace {
+struct PipeChunk { int r0, r1, l0, l1, q0, q1; };   // output rows; left / right image rows this chunk adds
+struct PipeStage {
+    std::vector<PipeChunk> ch;
+    const sr_image *left, *right;
+    char *sL, *sR, *sO;                  // pinned staging (nullptr: that side is pinned already)
+    char* out; size_t out_pitch, rowL, rowR, rowb;
+    std::vector<std::atomic<int>> in_done, out_ready;
+    std::atomic<int> abort{0};
+    explicit PipeStage(int n) : ch(n), in_done(n), out_ready(n) {
+        for (int i = 0; i < n; i++) { in_done[i].store(0); out_ready[i].store(0); }
+    }
+};
+inline void cpu_relax() {
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#endif
+}
+bool wait_count(const std::atomic<int>& f, int want, const std::atomic<int>& abort) {
+    for (int spins = 0; f.load(std::memory_order_acquire) < want; spins++) {
+        if (abort.load(std::memory_order_relaxed)) return false;
+        if (spins < 4000) cpu_relax(); else std::this_thread::yield();
+    }
+    return true;
+}
+void pipe_stage_worker(int t, int nthreads, void* arg) {
+    PipeStage* j = (PipeStage*)arg;
+    const int n = (int)j->ch.size();
+    for (int c = 0; c < n; c++) {
+        const PipeChunk& k = j->ch[c];
+        if (j->sR) sr_stage_stripe(j->sR, j->rowR, (const char*)j->right->bgr, j->right->pitch, j->rowR, k.q0, k.q1, t, nthreads);
+        if (j->sL) sr_stage_stripe(j->sL, j->rowL, (const char*)j->left->bgr, j->left->pitch, j->rowL, k.l0, k.l1, t, nthreads);
+        j->in_done[c].fetch_add(1, std::memory_order_release);
+    }
+    if (!j->sO) return;
+    for (int c = 0; c < n; c++) {
+        if (!wait_count(j->out_ready[c], 1, j->abort)) return;
+        sr_stage_stripe(j->out, j->out_pitch, j->sO, j->rowb, j->rowb, j->ch[c].r0, j->ch[c].r1, t, nthreads);
+    }
+}
+}  // namespace
 
 static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_image* right,
                                   const sr_search_params* p, double* disp_out, size_t out_pitch, int band0, int band1) {
@@ -113,19 +160,58 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     if (disp_out && out_pitch < rowb) return sr_fail(ctx, SR_E_BADARG, "output pitch %zu smaller than a row (%zu)", out_pitch, rowb);
     if (left->pitch < (size_t)left->w * 3 || right->pitch < (size_t)right->w * 3)
         return sr_fail(ctx, SR_E_BADARG, "image pitch smaller than a row");
-    while ((int)ctx->pipe_ev.size() < 2 * nch + 1) {
+    while ((int)ctx->pipe_ev.size() < 3 * nch + 1) {
         cudaEvent_t e;
         SR_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         ctx->pipe_ev.push_back(e);
     }
+    const size_t rowL = (size_t)left->w * 3, rowR = (size_t)right->w * 3;
+    // chunk table.  Uneven chunks: a short first chunk starts the search early, short last chunks leave a
+    // short exposed download; the chunks in between are larger (fewer partial waves in the search kernel)
+    PipeStage job(nch);
+    {
+        int up0 = band0 - half > 0 ? band0 - half : 0;   // first image row the band's windows read
+        int upL = up0 < pair->h1 ? up0 : pair->h1, upR = up0 < pair->h2 ? up0 : pair->h2;
+        for (int c = 0; c < nch; c++) {
+            PipeChunk& k = job.ch[c];
+            k.r0 = band0 + chunk_start(oh, nch, c, half);
+            k.r1 = band0 + chunk_start(oh, nch, c + 1, half);
+            // input rows this chunk needs: window rows [r0 - half, r1 + half) of both images
+            int needR = k.r1 + half + 1 < pair->h2 ? k.r1 + half + 1 : pair->h2;
+            int needL = k.r1 + half + 1 < pair->h1 ? k.r1 + half + 1 : pair->h1;
+            if (c == nch - 1 && band1 >= pair->h2) { needR = pair->h2; needL = pair->h1; }
+            k.q0 = upR; k.q1 = needR > upR ? needR : upR; upR = k.q1;
+            k.l0 = upL; k.l1 = needL > upL ? needL : upL; upL = k.l1;
+        }
+    }
+    // pageable sides go through pinned staging, filled / drained by the staging threads
+    const bool stL = !host_pinned(left->bgr), stR = !host_pinned(right->bgr), stO = disp_out && !host_pinned(disp_out);
+    sr_stage_pool* pool = nullptr;
+    job.left = left; job.right = right;
+    job.sL = job.sR = job.sO = nullptr;
+    job.out = (char*)disp_out; job.out_pitch = out_pitch; job.rowL = rowL; job.rowR = rowR; job.rowb = rowb;
+    if (stL || stR || stO) {
+        if (!(pool = sr_stage_pool_get(ctx))) return SR_E_CUDA;
+        if (stL && !(job.sL = (char*)sr_pinned(ctx, 0, rowL * pair->h1))) return SR_E_CUDA;
+        if (stR && !(job.sR = (char*)sr_pinned(ctx, 1, rowR * pair->h2))) return SR_E_CUDA;
+        if (stO && !(job.sO = (char*)sr_pinned(ctx, 2, rowb * pair->h2))) return SR_E_CUDA;
+        sr_stage_run(pool, pipe_stage_worker, &job);
+    }
+    const int nst = pool ? sr_stage_threads(pool) : 0;
+    const char* srcL = stL ? job.sL : (const char*)left->bgr;
+    const char* srcR = stR ? job.sR : (const char*)right->bgr;
+    const size_t pitL = stL ? rowL : left->pitch, pitR = stR ? rowR : right->pitch;
+    char* dstO = stO ? job.sO : (char*)disp_out;
+    const size_t pitO = stO ? rowb : out_pitch;
+
     cudaStream_t compute = ctx->stream, s_up = ctx->aux[0], s_down = ctx->aux[1];
+    int rc = SR_OK;
+    auto cuda_ok = [&](cudaError_t e, const char* what) { if (e != cudaSuccess && rc == SR_OK) rc = sr_cuda_check(ctx, e, what); return rc == SR_OK; };
     // the copy streams start after whatever the compute stream still has queued (previous call)
-    cudaEvent_t ev_start = ctx->pipe_ev[2 * nch];
-    SR_CUDA(ctx, cudaEventRecord(ev_start, compute));
-    SR_CUDA(ctx, cudaStreamWaitEvent(s_up, ev_start, 0));
-    SR_CUDA(ctx, cudaStreamWaitEvent(s_down, ev_start, 0));
-    SR_CUDA(ctx, cudaStreamWaitEvent(ctx->aux[2], ev_start, 0));
-    SR_CUDA(ctx, cudaStreamWaitEvent(ctx->aux[3], ev_start, 0));
+    cudaEvent_t ev_start = ctx->pipe_ev[3 * nch];
+    cuda_ok(cudaEventRecord(ev_start, compute), "cudaEventRecord");
+    for (cudaStream_t s : {s_up, s_down, ctx->aux[2], ctx->aux[3]}) cuda_ok(cudaStreamWaitEvent(s, ev_start, 0), "cudaStreamWaitEvent");
+    // compute streams the chunks rotate over (measured on 4K/512: 1 -> 2.74 ms, 2 -> 2.37 ms, 3 -> 2.42 ms)
     static const int ncs = getenv("SR_PIPE_STREAMS") ? atoi(getenv("SR_PIPE_STREAMS")) : 2;
     // SR_PIPE_TRACE=1: per-chunk timeline (ms since the start of the call) on stderr, development aid
     static const bool trace = getenv("SR_PIPE_TRACE") && atoi(getenv("SR_PIPE_TRACE")) != 0;
@@ -135,33 +221,21 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
         for (auto& e : tev) cudaEventCreate(&e);
         cudaEventRecord(tev[4 * nch], compute);
     }
-    int up0 = band0 - half > 0 ? band0 - half : 0;   // first image row the band's windows read
-    int upL = up0 < pair->h1 ? up0 : pair->h1, upR = up0 < pair->h2 ? up0 : pair->h2, rc = SR_OK;
-    const size_t rowL = (size_t)left->w * 3, rowR = (size_t)right->w * 3;
     for (int c = 0; c < nch && rc == SR_OK; c++) {
-        // uneven chunks: a short first chunk starts the search early, a short last chunk leaves a short
-        // exposed download; the chunks in between are larger (fewer partial waves in the search kernel)
-        int r0 = band0 + chunk_start(oh, nch, c, half), r1 = band0 + chunk_start(oh, nch, c + 1, half);
-        // input rows this chunk needs: window rows [r0 - half, r1 + half) of both images
-        int needR = r1 + half + 1 < pair->h2 ? r1 + half + 1 : pair->h2;
-        int needL = r1 + half + 1 < pair->h1 ? r1 + half + 1 : pair->h1;
-        if (c == nch - 1 && band1 >= pair->h2) { needR = pair->h2; needL = pair->h1; }
+        const PipeChunk& k = job.ch[c];
+        if ((stL || stR) && !wait_count(job.in_done[c], nst, job.abort)) break;
         {
             cudaStream_t saved = ctx->stream;
             ctx->stream = s_up;
-            if (needR > upR) {
-                cudaError_t e = cudaMemcpy2DAsync(pair->rawR + (size_t)upR * rowR, rowR, right->bgr + (size_t)upR * right->pitch,
-                                                  right->pitch, rowR, needR - upR, cudaMemcpyHostToDevice, s_up);
-                if (e != cudaSuccess) rc = sr_cuda_check(ctx, e, "cudaMemcpy2DAsync(H2D right rows)");
-                if (rc == SR_OK) rc = sr_launch_pack_rows(ctx, pair->rawR, rowR, right->w, upR, needR, &pair->R);
-                upR = needR;
+            if (k.q1 > k.q0) {
+                if (cuda_ok(cudaMemcpy2DAsync(pair->rawR + (size_t)k.q0 * rowR, rowR, srcR + (size_t)k.q0 * pitR, pitR, rowR, k.q1 - k.q0,
+                                              cudaMemcpyHostToDevice, s_up), "cudaMemcpy2DAsync(H2D right rows)"))
+                    rc = sr_launch_pack_rows(ctx, pair->rawR, rowR, right->w, k.q0, k.q1, &pair->R);
             }
-            if (rc == SR_OK && needL > upL) {
-                cudaError_t e = cudaMemcpy2DAsync(pair->rawL + (size_t)upL * rowL, rowL, left->bgr + (size_t)upL * left->pitch,
-                                                  left->pitch, rowL, needL - upL, cudaMemcpyHostToDevice, s_up);
-                if (e != cudaSuccess) rc = sr_cuda_check(ctx, e, "cudaMemcpy2DAsync(H2D left rows)");
-                if (rc == SR_OK) rc = sr_launch_pack_rows(ctx, pair->rawL, rowL, left->w, upL, needL, &pair->L);
-                upL = needL;
+            if (rc == SR_OK && k.l1 > k.l0) {
+                if (cuda_ok(cudaMemcpy2DAsync(pair->rawL + (size_t)k.l0 * rowL, rowL, srcL + (size_t)k.l0 * pitL, pitL, rowL, k.l1 - k.l0,
+                                              cudaMemcpyHostToDevice, s_up), "cudaMemcpy2DAsync(H2D left rows)"))
+                    rc = sr_launch_pack_rows(ctx, pair->rawL, rowL, left->w, k.l0, k.l1, &pair->L);
             }
             ctx->stream = saved;
         }
@@ -170,22 +244,31 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
         // the last wave of chunk c leaves idle (one 512-thread CTA per SM, so no other overlap exists)
         const int si = ncs >= 3 ? c % 3 : ncs == 2 ? (c & 1) : 0;
         cudaStream_t cs = si == 0 ? compute : ctx->aux[1 + si];
-        SR_CUDA(ctx, cudaEventRecord(ctx->pipe_ev[2 * c], s_up));
+        if (!cuda_ok(cudaEventRecord(ctx->pipe_ev[3 * c], s_up), "cudaEventRecord")) break;
         if (trace) cudaEventRecord(tev[4 * c], s_up);
-        SR_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->pipe_ev[2 * c], 0));
+        if (!cuda_ok(cudaStreamWaitEvent(cs, ctx->pipe_ev[3 * c], 0), "cudaStreamWaitEvent")) break;
         if (trace) cudaEventRecord(tev[4 * c + 1], cs);
         ctx->stream = cs;
-        rc = sr_search_run(ctx, pair, p, r0, r1);
+        rc = sr_search_run(ctx, pair, p, k.r0, k.r1);
         ctx->stream = compute;
         if (rc != SR_OK) break;
         if (trace) cudaEventRecord(tev[4 * c + 2], cs);
         if (!disp_out) continue;
-        SR_CUDA(ctx, cudaEventRecord(ctx->pipe_ev[2 * c + 1], cs));
-        SR_CUDA(ctx, cudaStreamWaitEvent(s_down, ctx->pipe_ev[2 * c + 1], 0));
-        cudaError_t e = cudaMemcpy2DAsync((char*)disp_out + (size_t)r0 * out_pitch, out_pitch, pair->out + (size_t)r0 * ow, rowb, rowb,
-                                          r1 - r0, cudaMemcpyDeviceToHost, s_down);
-        if (e != cudaSuccess) rc = sr_cuda_check(ctx, e, "cudaMemcpy2DAsync(D2H rows)");
+        if (!cuda_ok(cudaEventRecord(ctx->pipe_ev[3 * c + 1], cs), "cudaEventRecord")) break;
+        if (!cuda_ok(cudaStreamWaitEvent(s_down, ctx->pipe_ev[3 * c + 1], 0), "cudaStreamWaitEvent")) break;
+        if (!cuda_ok(cudaMemcpy2DAsync(dstO + (size_t)k.r0 * pitO, pitO, pair->out + (size_t)k.r0 * ow, rowb, rowb, k.r1 - k.r0,
+                                       cudaMemcpyDeviceToHost, s_down), "cudaMemcpy2DAsync(D2H rows)")) break;
+        if (stO && !cuda_ok(cudaEventRecord(ctx->pipe_ev[3 * c + 2], s_down), "cudaEventRecord")) break;
         if (trace) cudaEventRecord(tev[4 * c + 3], s_down);
+    }
+    if (pool) {
+        // hand finished output chunks to the staging threads in order; on an error release them instead
+        for (int c = 0; c < nch && stO && rc == SR_OK; c++) {
+            if (cuda_ok(cudaEventSynchronize(ctx->pipe_ev[3 * c + 2]), "cudaEventSynchronize"))
+                job.out_ready[c].store(1, std::memory_order_release);
+        }
+        if (rc != SR_OK) job.abort.store(1);
+        sr_stage_wait(pool);
     }
     cudaStreamSynchronize(s_up);
     cudaStreamSynchronize(compute);
@@ -309,8 +392,7 @@ int sr_search_download(sr_ctx* ctx, sr_pair* pair, double* disp_out, size_t out_
         if (!st) return SR_E_CUDA;
         SR_CUDA(ctx, cudaMemcpyAsync(st, src, rowb * rows, cudaMemcpyDeviceToHost, ctx->stream));
         SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        if (out_pitch == rowb) memcpy(dst, st, rowb * rows);
-        else for (int y = 0; y < rows; y++) memcpy((char*)dst + (size_t)y * out_pitch, (char*)st + (size_t)y * rowb, rowb);
+        sr_stage_copy_rows(ctx, dst, out_pitch, st, rowb, rowb, rows);
     }
     int status[2];
     SR_CUDA(ctx, cudaMemcpy(status, pair->maxblock, sizeof status, cudaMemcpyDeviceToHost));

@@ -85,6 +85,7 @@ void sr_ctx_destroy(sr_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    sr_stage_pool_destroy(ctx->stage_pool);
     for (sr_pair* p : ctx->batch_pairs) sr_pair_destroy(ctx, p);
     ctx->batch_pairs.clear();
     for (cudaEvent_t e : ctx->pipe_ev) cudaEventDestroy(e);
@@ -256,13 +257,12 @@ static int upload_one(sr_ctx* ctx, const sr_image* im, uint8_t* raw, PackedImage
     if (pinned) {
         SR_CUDA(ctx, cudaMemcpy2DAsync(raw, row, im->bgr, im->pitch, row, im->h, cudaMemcpyHostToDevice, ctx->stream));
     } else {
-        // pageable source: stage through the context's pinned buffer (one memcpy, one DMA);
+        // pageable source: stage through the context's pinned buffer (striped host copy, one DMA);
         // the buffer is reused, so the previous upload's DMA must have drained
         SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         uint8_t* st = (uint8_t*)sr_pinned(ctx, slot, row * im->h);
         if (!st) return SR_E_CUDA;
-        if (im->pitch == row) memcpy(st, im->bgr, row * im->h);
-        else for (int y = 0; y < im->h; y++) memcpy(st + (size_t)y * row, im->bgr + (size_t)y * im->pitch, row);
+        sr_stage_copy_rows(ctx, st, row, im->bgr, im->pitch, row, im->h);
         SR_CUDA(ctx, cudaMemcpyAsync(raw, st, row * im->h, cudaMemcpyHostToDevice, ctx->stream));
     }
     return sr_launch_pack(ctx, raw, row, im->w, im->h, pk);

@@ -16,6 +16,8 @@ struct DevBuf {
     size_t cap = 0;
 };
 
+struct sr_stage_pool;   // host threads for pageable <-> pinned staging copies (host_stage.cu)
+
 struct sr_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -31,6 +33,7 @@ struct sr_ctx {
     size_t pinned_cap[4] = {0, 0, 0, 0};
     std::vector<sr_pair*> batch_pairs;
     std::vector<cudaEvent_t> pipe_ev;  // events of the row-chunk pipeline of sr_block_search
+    sr_stage_pool* stage_pool = nullptr;
     void* nccl_comm = nullptr;
     int rank = 0, nranks = 1;
 };
@@ -86,6 +89,18 @@ int sr_fail(sr_ctx* ctx, int code, const char* fmt, ...);
 int sr_cuda_check(sr_ctx* ctx, cudaError_t e, const char* what);
 void* sr_scratch(sr_ctx* ctx, int slot, size_t bytes);  // nullptr on failure (error set)
 void* sr_pinned(sr_ctx* ctx, int slot, size_t bytes);
+
+// ---- host staging pool (host_stage.cu) ----
+sr_stage_pool* sr_stage_pool_get(sr_ctx* ctx);   // created on first use; nullptr when no thread can be started
+void sr_stage_pool_destroy(sr_stage_pool* p);
+int sr_stage_threads(const sr_stage_pool* p);
+void sr_stage_run(sr_stage_pool* p, void (*fn)(int t, int nthreads, void* arg), void* arg);   // returns at once
+void sr_stage_wait(sr_stage_pool* p);
+// thread t's share of rows [row0, row1) (row indices apply to both sides)
+void sr_stage_stripe(char* dst, size_t dpitch, const char* src, size_t spitch, size_t rowbytes, int row0, int row1,
+                     int t, int nthreads);
+// blocking host copy of `rows` rows, striped over the pool when it is large enough to pay for the wake-up
+int sr_stage_copy_rows(sr_ctx* ctx, void* dst, size_t dpitch, const void* src, size_t spitch, size_t rowbytes, int rows);
 
 #define SR_CUDA(ctx, call)                                              \
     do {                                                                \

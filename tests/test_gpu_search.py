@@ -128,6 +128,39 @@ def test_one_shot_row_chunk_pipeline(sr, ctx, orc, monkeypatch, cost, block, min
         capi.free_pinned(lh); capi.free_pinned(rh); capi.free_pinned(oh_)
 
 
+@pytest.mark.parametrize("pin", ["none", "left", "out"])
+def test_row_chunk_pipeline_pageable_sides(sr, ctx, orc, monkeypatch, pin):
+    """Pageable host buffers (cv::Mat memory) take the same pipeline through the staging threads
+    (host_stage.cu): any mix of pinned and pageable sides, row pitches wider than the rows, chunks with
+    fewer rows than there are staging threads."""
+    capi = sr.capi
+    w, h, D, block = 520, 260, 32, 7
+    L, R = synth(orc, w, h, 0, D, seed=23)
+    want = orc.block_search_right_fast(L, R, block, 0, D, 1.0, cost=1)
+    monkeypatch.setenv("SR_PIPE_CHUNKS", "6")
+    p = capi.search_params(block=block, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD)
+    Lw = np.zeros((h, w + 7, 3), np.uint8); Rw = np.zeros((h, w + 2, 3), np.uint8)
+    Lw[:, :w] = L; Rw[:, :w] = R
+    outw = np.full((h, w + 3), -7.0)
+    hs = []
+    try:
+        if pin == "left":
+            Lw, hh = capi.pinned_empty((h, w + 7, 3), np.uint8); hs.append(hh)
+            Lw[:, :w] = L
+        if pin == "out":
+            outw, hh = capi.pinned_empty((h, w + 3), np.float64); hs.append(hh)
+            outw[...] = -7.0
+        for _ in range(2):       # the second call reuses the staging buffers and the thread pool
+            n0 = ctx.launches
+            capi.block_search(ctx, Lw[:, :w], Rw[:, :w], p, out=outw[:, :w])
+            assert ctx.launches - n0 >= 6 * 2
+            np.testing.assert_array_equal(np.asarray(outw[:, :w]), want)
+            assert (np.asarray(outw[:, w:]) == -7.0).all()
+    finally:
+        for hh in hs:
+            capi.free_pinned(hh)
+
+
 @pytest.mark.parametrize("pinned", [True, False])
 def test_pair_search_band_from_host(sr, ctx, orc, monkeypatch, pinned):
     """sr_pair_search_band (one rank's share of a row-band sharded pair): partial upload with halo rows,
