@@ -218,6 +218,21 @@ def main():
     full = sharding.result_tensor(pair, dev)
     full16 = sharding.result16_tensor(pair, dev) if world > 1 else None   # int16 wire format of the band gather
     total_evals = synth.effective_evals(w, w, h, block, 0, D)
+    # band gather: stores into rank 0's HBM over NVLink (capi_peer.cu); NCCL point-to-point where peer mapping fails
+    peer = None
+    if world > 1 and os.environ.get("SR_GATHER", "peer") != "nccl":
+        try:
+            peer = sharding.PeerGather(pair, h, rank, world)
+        except RuntimeError as e:
+            if rank == 0:
+                print(f"[bench] {e}; gathering over NCCL", file=sys.stderr, flush=True)
+
+    def gather():
+        if peer is not None:
+            peer.gather()
+        else:
+            with torch.cuda.stream(ext):
+                sharding.gather_bands16(pair, full16, h, rank, world)
 
     half = (block - 1) // 2
     h2d_rows = h if world == 1 else sum(min(b1 + half + 1, h) - max(b0 - half, 0)
@@ -232,8 +247,7 @@ def main():
     def step_resident():
         pair.run(params, r0, r1)
         if world > 1:
-            with torch.cuda.stream(ext):
-                sharding.gather_bands16(pair, full16, h, rank, world)
+            gather()
 
     def step_e2e():
         if world == 1:
@@ -242,8 +256,7 @@ def main():
             # every rank: H2D of its band's image rows (+ halo), band search, by row chunks (sr_pair_search_band);
             # rank 0 streams its own band back to the host inside that pipeline, the others keep theirs in HBM
             pair.search_band(Lp, Rp, params, r0, r1, out=outp if rank == 0 else None)
-            with torch.cuda.stream(ext):
-                sharding.gather_bands16(pair, full16, h, rank, world)
+            gather()
             if rank == 0:
                 ext.synchronize()
                 pair.download(params, out=outp, row0=r1, row1=h)   # the gathered bands (rank 0 owns rows [0, r1))
@@ -306,6 +319,10 @@ def main():
     if rank == 0:
         res = pair.download(params)
         checksum = float(res.sum())
+        gather_ok = None
+        if world > 1:
+            pair.run(params)                 # the whole pair on this GPU: the gathered bands must reproduce it
+            gather_ok = bool(np.array_equal(res, pair.download(params)))
         band_evals = synth.effective_evals(w, w, r1 - r0, block, 0, D)
         k_ms = float(np.mean(kern_ms)) if kern_ms else None
         ops = OPS_PER_EVAL[cost]
@@ -328,7 +345,9 @@ def main():
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: synthetic {w}x{h} rectified pair, {D} disparities, {block}x{block} "
                                    f"{cost.upper()}, smooth 1.0 (BASELINE.json configs)",
-                       "sharding": "row bands + NCCL gather to rank 0 (int16 wire format, widened on rank 0)" if world > 1 else "single GPU",
+                       "sharding": ("single GPU" if world == 1 else
+                                    "row bands; gather = int16 stores into rank 0's HBM over NVLink (peer memory), widened by rank 0 as the flags arrive" if peer is not None else
+                                    "row bands + NCCL gather to rank 0 (int16 wire format, widened on rank 0)"),
                        "l2": "384 MB written between timed iterations", "evals": "effective (reference break rule)",
                        "nominal_MDE": w * h * D / 1e6, "effective_MDE": total_evals / 1e6},
             "pairs_per_s": 1e3 / ms_per_step,
@@ -336,13 +355,15 @@ def main():
             "e2e": {"value": total_evals / e2e_s / 1e6, "unit": "MDE/s", "ms_per_step": e2e_s * 1e3,
                     "h2d_bytes_per_step": int(h2d_rows * w * 3 * 2), "d2h_bytes_per_step": int(w * h * 8),
                     "pageable_ms_per_step": pageable_ms,
-                    "api": "sr_block_search (pinned host buffers; pageable_ms_per_step = same call on pageable buffers)" if world == 1 else "sr_pair_search_band (band rows + halo H2D, chunked) + NCCL gather + sr_search_download of the gathered bands"},
+                    "api": "sr_block_search (pinned host buffers; pageable_ms_per_step = same call on pageable buffers)" if world == 1 else "sr_pair_search_band (band rows + halo H2D, chunked) + band gather + sr_search_download of the gathered bands"},
             "gpu_launches": int(launches),
             "kernel_family": ctx.last_kernel,
             "clocks": clocks,
             "roofline": roofline,
             "result_checksum": checksum,
         }
+        if world > 1:
+            line["gathered_map_equals_single_gpu"] = gather_ok
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, L, R, w, h, D, block, cost)
         print(json.dumps(line), flush=True)

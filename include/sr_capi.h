@@ -146,6 +146,24 @@ void* sr_search_result_dev(sr_ctx* ctx, sr_pair* pair);
 int sr_search_pack16(sr_ctx* ctx, sr_pair* pair, int row0, int row1);
 int sr_search_unpack16(sr_ctx* ctx, sr_pair* pair, int row0, int row1);
 void* sr_search_result16_dev(sr_ctx* ctx, sr_pair* pair);
+/* Band gather over peer memory (NVLink / NVSwitch), the gather of SURVEY.md 8e without a collective library on
+ * the data path.  Rank 0 (the root) exports a gather window of its pair as a CUDA IPC handle (64 bytes; carry
+ * them to the other ranks by any means, e.g. torch.distributed.broadcast_object_list); the other ranks attach
+ * to it.  Per step `seq` (1, 2, 3, ... -- the same number on every rank): rank r > 0 calls
+ * sr_search_push_band after its band search -- one kernel narrows rows [row0,row1) to the int16 wire format,
+ * stores them into the root's HBM and publishes the step in the root's flag word of rank r; the root calls
+ * sr_search_collect_bands after its own band search -- one kernel widens every other rank's rows (bands of
+ * sr_band_rows(h, r, nranks)) into its CV_64F result as their flags arrive and acknowledges the step, which
+ * lets the pushers overwrite the window.  All asynchronous on the context stream; a band that does not arrive
+ * within ~1 s sets the pair's status (reported by sr_search_download) instead of hanging the GPU.
+ * sr_pair_peer_attach_local attaches to a root pair of the same process (single-GPU tests of the protocol). */
+#define SR_PEER_HANDLE_BYTES 64
+int sr_pair_peer_export(sr_ctx* ctx, sr_pair* pair, void* handle);
+int sr_pair_peer_attach(sr_ctx* ctx, sr_pair* pair, const void* handle);
+int sr_pair_peer_attach_local(sr_ctx* ctx, sr_pair* pair, sr_pair* root);
+int sr_pair_peer_detach(sr_ctx* ctx, sr_pair* pair);
+int sr_search_push_band(sr_ctx* ctx, sr_pair* pair, int row0, int row1, int rank, unsigned seq);
+int sr_search_collect_bands(sr_ctx* ctx, sr_pair* pair, int nranks, unsigned seq);
 int sr_search_max_block(sr_ctx* ctx, sr_pair* pair, int* max_block);
 /* The left-referenced integer disparity map (w1 x h1, int32) that the last run with lr_check = 1
  * computed for the consistency test (extension); SR_E_BADARG when there is none. */

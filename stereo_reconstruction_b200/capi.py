@@ -49,6 +49,7 @@ SYMBOLS = [
     "sr_ctx_stream", "sr_ctx_sync", "sr_timer_start", "sr_timer_stop", "sr_kernel_launches", "sr_last_kernel",
     "sr_block_search", "sr_block_search_batch", "sr_pair_create", "sr_pair_destroy", "sr_pair_upload",
     "sr_search_run", "sr_search_download", "sr_search_result_dev", "sr_search_max_block", "sr_search_left_disparity", "sr_pair_search_band", "sr_host_register", "sr_host_unregister", "sr_search_pack16", "sr_search_unpack16", "sr_search_result16_dev",
+    "sr_pair_peer_export", "sr_pair_peer_attach", "sr_pair_peer_attach_local", "sr_pair_peer_detach", "sr_search_push_band", "sr_search_collect_bands",
     "sr_search_effective_evals", "sr_remove_outliers", "sr_box_blur", "sr_scale", "sr_disparity_to_depth",
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
     "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
@@ -254,6 +255,30 @@ class Pair:
 
     def result16_ptr(self):
         return int(self.ctx._l.sr_search_result16_dev(self.ctx.h, self.h))
+
+    # ---- band gather over peer memory (include/sr_capi.h: sr_pair_peer_*) ----
+    def peer_export(self):
+        """Root: creates the gather window, returns its CUDA IPC handle (64 bytes)."""
+        buf = C.create_string_buffer(64)
+        self.ctx.check(self.ctx._l.sr_pair_peer_export(self.ctx.h, self.h, buf))
+        return buf.raw
+
+    def peer_attach(self, handle):
+        """Other ranks (other processes): maps the root's window."""
+        self.ctx.check(self.ctx._l.sr_pair_peer_attach(self.ctx.h, self.h, C.c_char_p(bytes(handle))))
+
+    def peer_attach_local(self, root):
+        """Same-process stand-in for peer_attach (single-GPU tests of the protocol)."""
+        self.ctx.check(self.ctx._l.sr_pair_peer_attach_local(self.ctx.h, self.h, root.h))
+
+    def peer_detach(self):
+        self.ctx.check(self.ctx._l.sr_pair_peer_detach(self.ctx.h, self.h))
+
+    def push_band(self, row0, row1, rank, seq):
+        self.ctx.check(self.ctx._l.sr_search_push_band(self.ctx.h, self.h, int(row0), int(row1), int(rank), C.c_uint(int(seq))))
+
+    def collect_bands(self, nranks, seq):
+        self.ctx.check(self.ctx._l.sr_search_collect_bands(self.ctx.h, self.h, int(nranks), C.c_uint(int(seq))))
 
     def search_band(self, left, right, params, row0, row1, out=None):
         """sr_pair_search_band: rows [row0,row1) from host images; out=None keeps the band in HBM."""

@@ -397,6 +397,7 @@ int sr_search_download(sr_ctx* ctx, sr_pair* pair, double* disp_out, size_t out_
     int status[2];
     SR_CUDA(ctx, cudaMemcpy(status, pair->maxblock, sizeof status, cudaMemcpyDeviceToHost));
     if (status[1] == SR_E_BADARG) return sr_fail(ctx, status[1], "sr_search_pack16: the map holds values that are not integers in int16 range");
+    if (status[1] == SR_E_CUDA) return sr_fail(ctx, status[1], "band gather over peer memory: a rank's band did not arrive (timeout)");
     if (status[1] != SR_OK) return sr_fail(ctx, status[1], "the grown window runs past the left image (cv::Exception in the reference)");
     return SR_OK;
 }

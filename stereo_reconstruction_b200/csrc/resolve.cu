@@ -11,7 +11,7 @@
 // resolved row by row with bit-parallel carry propagation (one 32-pixel word per thread).
 #include "sr_internal.cuh"
 
-struct Planes { const uint32_t* planes; size_t stride; int npass, dbase; };
+struct Planes { const uint32_t* planes; size_t stride; int npass, dbase, shift; };
 
 struct PixRec {
     bool skip;                  // black pixel / unvisited row -> 0.0
@@ -33,12 +33,13 @@ __device__ __forceinline__ PixRec load_rec(int from_direct, int have_c0, size_t 
         r.skip = y >= g.height || (__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) == 0;
         int l = min(x, g.half), rr = min(g.w2 - x - 1, g.half), u = min(y, g.half), dn = min(g.h2 - y - 1, g.half);
         r.n = (l + rr) * (u + dn);
-        // first minimum over the passes' key planes (cost*64 + d_local; passes ascend in d,
-        // strict < keeps the smaller d on ties)
+        // first minimum over the key planes (cost << shift | candidate index; one plane per pass of 64
+        // candidates, or one plane for all when the tile kernel folded them; passes ascend in d, strict <
+        // keeps the smaller d on ties)
         uint32_t bc = 0xFFFFFFFFu; int bd = 0;
         for (int p = 0; p < pl.npass; p++) {
             uint32_t k = __ldg(pl.planes + (size_t)p * pl.stride + i);
-            if (k != 0xFFFFFFFFu && (k >> 6) < bc) { bc = k >> 6; bd = pl.dbase + 64 * p + (int)(k & 63u); }
+            if (k != 0xFFFFFFFFu && (k >> pl.shift) < bc) { bc = k >> pl.shift; bd = pl.dbase + 64 * p + (int)(k & ((1u << pl.shift) - 1u)); }
         }
         r.cr = bc == 0xFFFFFFFFu ? SR_NONE64 : (unsigned long long)bc;
         r.dr = bd;
@@ -264,7 +265,7 @@ __global__ void smooth_expand_kernel(SearchGeom g, int words, const uint32_t* __
 int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, double smooth, int from_direct, int have_c0) {
     int rows = g.row1 - g.row0;
     if (rows <= 0) return SR_OK;
-    Planes pl{pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase};
+    Planes pl{pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase, pair->key_shift};
     dim3 grid(cdiv(g.w2, 128), rows);
     bool plain = smooth == 1.0 || !have_c0;
     if (plain) {

@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(128) ncc_border_warp_kernel(const uint32_t* __
 __global__ void __launch_bounds__(128) ext_from_planes_kernel(const uint32_t* __restrict__ Lp, int pitchL,
                                                               const uint32_t* __restrict__ Rp, int pitchR, ExtGeom g,
                                                               const uint32_t* __restrict__ planes, size_t stride, int npass,
-                                                              int dbase, int want_subpix, int* __restrict__ disp,
+                                                              int dbase, int shift, int want_subpix, int* __restrict__ disp,
                                                               float* __restrict__ subpix) {
     int x = blockIdx.x * blockDim.x + threadIdx.x, y = g.row0 + blockIdx.y;
     if (x >= g.wr) return;
@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(128) ext_from_planes_kernel(const uint32_t* __
         uint32_t bc = 0xFFFFFFFFu; int bd = -1;
         for (int p = 0; p < npass; p++) {
             uint32_t k = __ldg(planes + (size_t)p * stride + o);
-            if (k != 0xFFFFFFFFu && (k >> 6) < bc) { bc = k >> 6; bd = dbase + 64 * p + (int)(k & 63u); }
+            if (k != 0xFFFFFFFFu && (k >> shift) < bc) { bc = k >> shift; bd = dbase + 64 * p + (int)(k & ((1u << shift) - 1u)); }
         }
         if (bd >= 0) {
             dbest = bd;
@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(128) ncc_merge_kernel(const uint32_t* __restri
 // output column xc of that search is left-image column w1-1-xc (see sr_search_run_ext).
 __global__ void __launch_bounds__(128) left_from_mirror_planes_kernel(const uint32_t* __restrict__ Lp, int pitchL, int w1, int h1,
                                                                       int height, const uint32_t* __restrict__ planes, size_t stride,
-                                                                      int npass, int dbase, int* __restrict__ disp) {
+                                                                      int npass, int dbase, int shift, int* __restrict__ disp) {
     int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
     if (x >= w1) return;
     int dbest = 0;
@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(128) left_from_mirror_planes_kernel(const uint
         uint32_t bc = 0xFFFFFFFFu;
         for (int p = 0; p < npass; p++) {
             uint32_t k = __ldg(planes + (size_t)p * stride + o);
-            if (k != 0xFFFFFFFFu && (k >> 6) < bc) { bc = k >> 6; dbest = dbase + 64 * p + (int)(k & 63u); }
+            if (k != 0xFFFFFFFFu && (k >> shift) < bc) { bc = k >> shift; dbest = dbase + 64 * p + (int)(k & ((1u << shift) - 1u)); }
         }
     }
     disp[(size_t)y * w1 + x] = dbest;
@@ -370,7 +370,7 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
             tiled = true;
             ext_from_planes_kernel<<<dim3(cdiv(w2, 128), row1 - row0), 128, 0, ctx->stream>>>(
                 pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, pair->planes, pair->npx_cap,
-                pair->npass, pair->plane_dbase, p->subpixel, disp_r, subpix);
+                pair->npass, pair->plane_dbase, pair->key_shift, p->subpixel, disp_r, subpix);
             SR_LAUNCHED(ctx);
         }
     }
@@ -452,7 +452,7 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
             if (handled && p->cost != SR_COST_NCC) {
                 mirrored = true;
                 left_from_mirror_planes_kernel<<<dim3(cdiv(w1, 128), h1), 128, 0, ctx->stream>>>(
-                    pair->L.px, pair->L.pitch, w1, h1, g.height, pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase, disp_l);
+                    pair->L.px, pair->L.pitch, w1, h1, g.height, pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase, pair->key_shift, disp_l);
                 SR_LAUNCHED(ctx);
                 ctx->last_kernel = tiled ? "tile+ext+mirror" : "ext-direct+mirror";
             } else if (handled) {

@@ -119,7 +119,8 @@ struct TileArgs {
     int npass;
     int row0, row1;      // output rows (already clipped to min(h1,h2))
     int band;            // rows per CTA band
-    uint32_t k64;        // == 64, passed as data so that key = S*64+d stays one IMAD (FMA pipe)
+    uint32_t k64;        // key = S*k64 + d_key as one IMAD (FMA pipe); 64 with one plane per pass, 2^shift when merged
+    int merged;          // 1: one plane for all passes, key = cost << shift | (d - dbase), folded in with RED.MIN
     uint32_t kp1, km1;   // == 1, == 0xFFFFFFFF (-1): IMAD-based sliding sums
     int red_mode;        // 1: half of the warps merge the previous row's keys at the end of the iteration
 };
@@ -199,6 +200,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int pass = (int)(gridDim.z - 1 - blockIdx.z);        // heaviest (masked / ragged) passes are scheduled first
     const int dcta = a.dbase + pass * (DT * NW);               // first disparity of the pass (multiple of 4)
     const int d0 = dcta + DT * warp;                            // this warp's 4 disparities
+    const uint32_t dkey0 = (uint32_t)(DT * warp + (a.merged ? pass * (DT * NW) : 0));   // candidate index in the key
     const bool late_sub = (warp >> 2) & 1;
     const bool red_late = a.red_mode && ((warp >> 3) & 1);   // spreads the LDS burst of the key merge over the iteration
 
@@ -221,6 +223,8 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const bool active = d0 < dlim_tile;                         // warps with at least one candidate
     if (dcta >= dlim_tile) {
         // nothing to search in this (tile, pass): the planes still get their "no candidate" keys
+        // (the merged plane is preset to them)
+        if (a.merged) return;
         for (int y = yb0 + warp; y < yb1; y += NW)
             for (int q = lane; q < TILE_OUT; q += 32) {
                 int x = CB + h + q;
@@ -264,7 +268,8 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int xq = CB + h + rq;
     const bool red_on = rgrp < 31 && xq >= 0 && xq < a.w2;
     const uint32_t red_b = keys_base + 4u * (20 * rgrp + (lane & 15));
-    uint32_t* pl = a.planes + (size_t)pass * a.plane_stride + (size_t)yb0 * a.w2 + xq;
+    uint32_t* pl = a.planes + (a.merged ? (size_t)0 : (size_t)pass * a.plane_stride) + (size_t)yb0 * a.w2 + xq;
+    const bool merged = a.merged != 0;
     auto reduce_row = [&](uint32_t buf) {
         if (red_on) {
             uint32_t kk[NW];
@@ -273,7 +278,10 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
             uint32_t k = 0xFFFFFFFFu;
 #pragma unroll
             for (int w = 0; w < NW; w++) k = min(k, kk[w]);
-            *pl = k;
+            // merged: the key carries the global candidate index, so the first minimum over all passes is one
+            // fire-and-forget RED.MIN in L2 (the plane is preset to "none")
+            if (merged) { if (k != 0xFFFFFFFFu) atomicMin(pl, k); }
+            else *pl = k;
         }
         pl += a.w2;
     };
@@ -306,8 +314,8 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
                 uint32_t keys[XT];
 #pragma unroll
                 for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
-                if (needmask) window_wta<H2, true>(col, keys, k64, a.kp1, a.km1, (uint32_t)(DT * warp), d0, cb + h, a);
-                else window_wta<H2, false>(col, keys, k64, a.kp1, a.km1, (uint32_t)(DT * warp), d0, cb + h, a);
+                if (needmask) window_wta<H2, true>(col, keys, k64, a.kp1, a.km1, dkey0, d0, cb + h, a);
+                else window_wta<H2, false>(col, keys, k64, a.kp1, a.km1, dkey0, d0, cb + h, a);
 #pragma unroll
                 for (int k = 0; k < 4; k++)
                     sts128(key_st + buf + 16 * k, keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
@@ -371,7 +379,7 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     a.w1 = g.w1; a.h1 = g.h1; a.w2 = g.w2; a.h2 = g.h2; a.half = g.half;
     a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
     a.npass = (g.dhi - a.dbase + 63) / 64;
-    a.row0 = g.row0; a.row1 = r1; a.k64 = 64; a.kp1 = 1u; a.km1 = 0xFFFFFFFFu;
+    a.row0 = g.row0; a.row1 = r1; a.k64 = 64; a.merged = 0; a.kp1 = 1u; a.km1 = 0xFFFFFFFFu;
     static const char* rm_env = getenv("SR_TILE_REDMODE");
     a.red_mode = rm_env ? atoi(rm_env) : 1;
     int ntx = (g.w2 + XT - g.half + TILE_OUT - 1) / TILE_OUT;
@@ -381,11 +389,23 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
         pair->npass = 0;
         return 1;
     }
-    // one u32 key plane per pass (merged by the resolve kernels): no read-modify-write in the hot loop
-    pair->npass = a.npass; pair->plane_dbase = a.dbase;
-    pair->planes = (uint32_t*)sr_scratch(ctx, 0, (size_t)a.npass * pair->npx_cap * sizeof(uint32_t));
+    // Key planes.  Where cost and candidate index fit one u32 together (cost << shift | d - dbase), all passes
+    // fold into ONE plane with RED.MIN: the plane stays in L2, the kernel's DRAM writes drop from npass planes to
+    // one and the resolve pass reads one plane.  Otherwise (SSD on large windows / ranges) one plane per pass
+    // with key = cost*64 + d_local, merged by the resolve kernels.
+    int shift = 6;
+    while ((64 << (shift - 6)) < a.npass * 64) shift++;
+    unsigned long long cmax = (unsigned long long)g.block * g.block * 3ull * (cost == SR_COST_SAD ? 255ull : 65025ull);
+    static const char* mg_env = getenv("SR_TILE_MERGE");    // tuning / test override
+    a.merged = a.npass > 1 && ((cmax + 1) << shift) < 0xFFFFFFFFull && !(mg_env && atoi(mg_env) == 0);
+    if (!a.merged) shift = 6;
+    a.k64 = 1u << shift;
+    pair->npass = a.merged ? 1 : a.npass; pair->plane_dbase = a.dbase; pair->key_shift = shift;
+    pair->planes = (uint32_t*)sr_scratch(ctx, 0, (size_t)pair->npass * pair->npx_cap * sizeof(uint32_t));
     if (!pair->planes) return SR_E_CUDA;
     a.planes = pair->planes; a.plane_stride = pair->npx_cap;
+    if (a.merged)
+        SR_CUDA(ctx, cudaMemsetAsync(pair->planes + (size_t)g.row0 * g.w2, 0xFF, (size_t)(r1 - g.row0) * g.w2 * sizeof(uint32_t), ctx->stream));
     // bands: CTAs = ntx * npass * nbands, one CTA per SM at a time; minimise waves * (band + warm-up rows)
     const int sms = 148;
     int maxnb = rows / (2 * g.half + 2);

@@ -241,6 +241,7 @@ int sr_pair_create(sr_ctx* ctx, int w1, int h1, int w2, int h2, sr_pair** out) {
 void sr_pair_destroy(sr_ctx* ctx, sr_pair* p) {
     if (!p) return;
     if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
+    sr_pair_peer_detach(ctx, p); cudaFree(p->peer_counter);
     cudaFree(p->L.base); cudaFree(p->R.base); cudaFree(p->Lm.base); cudaFree(p->Rm.base); cudaFree(p->ncc_tab); cudaFree(p->ncc_tab_m); cudaFree(p->out16); cudaFree(p->rawL); cudaFree(p->rawR);
     cudaFree(p->best); cudaFree(p->c0); cudaFree(p->cr); cudaFree(p->dr); cudaFree(p->nwin);
     cudaFree(p->bits); cudaFree(p->alt); cudaFree(p->out); cudaFree(p->outf); cudaFree(p->maxblock);

@@ -63,7 +63,8 @@ struct sr_pair {
     // per-pixel records of the reference-side (output) image
     int ow = 0, oh = 0;        // output size (RIGHT/LINEAR: w2 x h2; LEFT: w1 x h1)
     uint32_t* planes = nullptr;           // tile kernel: per-pass key planes (ctx scratch), cost*64 + d_local
-    int npass = 0, plane_dbase = 0;
+    int npass = 0, plane_dbase = 0;       // planes held (1 when the passes were folded into one plane), first candidate
+    int key_shift = 6;                    // key = cost << key_shift | candidate index within the plane's range
     unsigned long long* best = nullptr;   // (cost << 32 | d) first minimum over the searched range
     unsigned long long* c0 = nullptr;     // cost at d == 0 (SR_NONE64 when not a candidate)
     unsigned long long* cr = nullptr;     // wide-cost first minimum (direct kernels)
@@ -74,6 +75,9 @@ struct sr_pair {
     double* out = nullptr;                // result, ow x oh, tight
     float* outf = nullptr;                // float copy for the reconstruction pipeline
     short* out16 = nullptr;               // int16 wire format of the result (band gather)
+    void* peer_win = nullptr;             // gather window over peer memory (capi_peer.cu)
+    int peer_mode = 0;                    // 0 none, 1 root (owns the window), 2 attached through CUDA IPC, 3 attached in-process
+    unsigned* peer_counter = nullptr;     // last-block counter of the push / collect kernels
     int* maxblock = nullptr;              // device scalar
     unsigned long long* evals = nullptr;  // device scalar
     size_t npx_cap = 0;

@@ -3,8 +3,8 @@
 * config 5 (batch of pairs): pair p -> rank p % world, no collective (`pairs_of_rank`).
 * config 4 (one very large pair): rank r owns the output rows `band_rows(h, r, world)`; every rank
   holds the whole pair in HBM (the 2h-1 halo rows are simply read from it), runs the search on
-  its band and the bands are gathered to rank 0 with point-to-point sends over NCCL/NVLink
-  (`gather_bands`).  The same code runs over gloo on CPU tensors (tests/test_sharding_cpu.py).
+  its band and the bands are gathered to rank 0 -- by stores into rank 0's HBM over NVLink (`PeerGather`,
+  capi_peer.cu) or, where peer mapping is unavailable, by point-to-point sends over NCCL (`gather_bands16`).  The same code runs over gloo on CPU tensors (tests/test_sharding_cpu.py).
 """
 import torch
 import torch.distributed as dist
@@ -51,6 +51,43 @@ def gather_bands16(pair, full16, h, rank, world, group=None):
     gather_bands(full16.view(torch.uint8), h, rank, world, group)   # NCCL has no int16: the rows travel as bytes
     if rank == 0:
         pair.unpack16(r1, h)       # rank 0 owns rows [0, r1); the rest arrived as int16
+
+
+class PeerGather:
+    """Band gather over peer memory (capi_peer.cu): rank 0 exports a gather window of its pair, the other ranks map
+    it through CUDA IPC and store their int16 bands straight into rank 0's HBM over NVLink; rank 0's collect
+    kernel widens each band as its flag arrives.  torch.distributed only carries the 64-byte handle, once.
+    `gather()` is asynchronous on the pair's context stream; every rank must call it once per step."""
+
+    def __init__(self, pair, h, rank, world, group=None):
+        self.pair, self.h, self.rank, self.world, self.seq = pair, h, rank, world, 0
+        if world == 1:
+            return
+        box = [pair.peer_export() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0, group=group)
+        err = 0
+        if rank != 0:
+            try:
+                pair.peer_attach(box[0])
+            except capi.SrError:
+                err = 1
+        # every rank takes the same route: one failed mapping sends all of them back to the NCCL gather
+        flag = torch.tensor([err], dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device()))
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=group)
+        if int(flag.item()):
+            if rank != 0 and not err:
+                pair.peer_detach()
+            raise RuntimeError("peer memory mapping is not available between these ranks")
+
+    def gather(self):
+        if self.world == 1:
+            return
+        self.seq += 1
+        if self.rank == 0:
+            self.pair.collect_bands(self.world, self.seq)
+        else:
+            r0, r1 = band_rows(self.h, self.rank, self.world)
+            self.pair.push_band(r0, r1, self.rank, self.seq)
 
 
 def gather_bands(full, h, rank, world, group=None):

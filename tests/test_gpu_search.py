@@ -240,3 +240,54 @@ def test_host_register_enables_the_pipeline(sr, ctx, orc, monkeypatch):
     finally:
         for a in (L, R, out):
             capi.host_unregister(a)
+
+
+@pytest.mark.parametrize("w", [404, 403])       # rows that start on / off the 4-element store alignment
+def test_peer_memory_band_gather_protocol(sr, orc, w):
+    """Band gather over peer memory (capi_peer.cu) with the peers standing in as pair objects of one process:
+    three "ranks" search their bands, ranks 1 and 2 push int16 rows into the root's window, the root collects.
+    Several steps on changing images exercise the step flags and the acknowledgement that guards the window."""
+    capi = sr.capi
+    h, D, block, world = 157, 24, 7, 3
+    ctxs = [capi.Context(0) for _ in range(world)]
+    pairs = [capi.Pair(c, w, h, w, h) for c in ctxs]
+    p = capi.search_params(block=block, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD)
+    try:
+        handle = pairs[0].peer_export()
+        assert len(handle) == 64
+        for r in (1, 2):
+            pairs[r].peer_attach_local(pairs[0])
+        for seq in (1, 2, 3):
+            L, R = synth(orc, w, h, 0, D, seed=40 + seq)
+            if seq == 2:
+                R[50:60, 100:140] = 0                      # black pixels: 0.0 in the map
+            want = orc.block_search_right_fast(L, R, block, 0, D, 1.0, cost=1)   # holds negative entries (-x) too
+            for r in range(world):
+                pairs[r].upload(L, R)
+                r0, r1 = capi.band_rows(h, r, world)
+                pairs[r].run(p, r0, r1)
+            # pushes first: on one GPU the collect kernel's waiting blocks would otherwise keep the SMs busy
+            for r in (2, 1):
+                r0, r1 = capi.band_rows(h, r, world)
+                pairs[r].push_band(r0, r1, r, seq)
+            pairs[0].collect_bands(world, seq)
+            np.testing.assert_array_equal(pairs[0].download(p), want, err_msg=f"step {seq}")
+        # step 4: rank 1 pushes values outside the int16 wire format (a sub-pixel map) -> refused on rank 1;
+        # rank 2's band never arrives -> the root's collect kernel gives up instead of hanging, the download reports it
+        ps = capi.search_params(block=block, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD, subpixel=True)
+        pairs[1].run(ps)
+        pairs[1].push_band(0, h, 1, 4)
+        with pytest.raises(capi.SrError) as e:
+            pairs[1].download(ps)
+        assert e.value.code == capi.E_BADARG
+        pairs[0].run(p, *capi.band_rows(h, 0, world))
+        pairs[0].collect_bands(world, 4)
+        with pytest.raises(capi.SrError, match="did not arrive"):
+            pairs[0].download(p)
+    finally:
+        for r in (1, 2):
+            pairs[r].peer_detach()
+        for q in pairs:
+            q.close()
+        for c in ctxs:
+            c.close()
