@@ -23,6 +23,8 @@
 // the pointwise cost forced to 0 outside columns [0,w2-1) and rows [0,h2-1).
 #include <cstdlib>
 #include "sr_internal.cuh"
+#include <stdio.h>
+#include <string.h>
 
 namespace {
 
@@ -118,7 +120,7 @@ struct TileArgs {
     int dbase;           // dlo rounded down to a multiple of 4
     int npass;
     int row0, row1;      // output rows (already clipped to min(h1,h2))
-    int band;            // rows per CTA band
+    const int4* work;    // work items {tile, first row, end row, pass}, one per CTA, in schedule order
     uint32_t k64;        // key = S*k64 + d_key as one IMAD (FMA pipe); 64 with one plane per pass, 2^shift when merged
     int merged;          // 1: one plane for all passes, key = cost << shift | (d - dbase), folded in with RED.MIN
     uint32_t kp1, km1;   // == 1, == 0xFFFFFFFF (-1): IMAD-based sliding sums
@@ -191,13 +193,15 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler
     const int h = a.half;
-    const int CB = -XT + TILE_OUT * (int)blockIdx.x;          // first own column of lane 0
-    const int yb0 = a.row0 + a.band * (int)blockIdx.y;
-    const int yb1 = min(yb0 + a.band, a.row1);
+    // One CTA per work item {tile, first row, end row, pass}.  The list is built on the host (tile_work_list):
+    // the hardware hands out CTAs in list order, so the order of the list is the schedule.
+    const int4 wk = __ldg(a.work + blockIdx.x);
+    const int CB = -XT + TILE_OUT * wk.x;                      // first own column of lane 0
+    const int yb0 = wk.y, yb1 = wk.z;
     if (yb0 >= yb1) return;
     const int cb = CB + XT * lane;                             // this thread's own columns [cb, cb+16)
     const uint32_t k64 = a.k64;
-    const int pass = (int)(gridDim.z - 1 - blockIdx.z);        // heaviest (masked / ragged) passes are scheduled first
+    const int pass = wk.w;
     const int dcta = a.dbase + pass * (DT * NW);               // first disparity of the pass (multiple of 4)
     const int d0 = dcta + DT * warp;                            // this warp's 4 disparities
     const uint32_t dkey0 = (uint32_t)(DT * warp + (a.merged ? pass * (DT * NW) : 0));   // candidate index in the key
@@ -335,7 +339,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
 }
 
 template <int H2, int COST>
-int launch(sr_ctx* ctx, const TileArgs& a, int ntx, int nbands) {
+int launch(sr_ctx* ctx, const TileArgs& a, int nwork) {
     constexpr int NW = 16;
     size_t smem = ((size_t)(H2 + PF + 1) * SLOT_U4 + 2 * NW * KEY_U4) * sizeof(uint4);
     static bool configured = false;
@@ -344,7 +348,7 @@ int launch(sr_ctx* ctx, const TileArgs& a, int ntx, int nbands) {
         configured = true;
     }
     SR_CUDA(ctx, cudaEventRecord(ctx->kev0, ctx->stream));
-    search_tile_kernel<H2, COST, NW><<<dim3(ntx, nbands, a.npass), NW * 32, smem, ctx->stream>>>(a);
+    search_tile_kernel<H2, COST, NW><<<nwork, NW * 32, smem, ctx->stream>>>(a);
     SR_LAUNCHED(ctx);
     SR_CUDA(ctx, cudaEventRecord(ctx->kev1, ctx->stream));
     ctx->kev_valid = true;
@@ -352,18 +356,86 @@ int launch(sr_ctx* ctx, const TileArgs& a, int ntx, int nbands) {
 }
 
 template <int COST>
-int dispatch_h2(sr_ctx* ctx, const TileArgs& a, int ntx, int nbands) {
+int dispatch_h2(sr_ctx* ctx, const TileArgs& a, int nwork) {
     switch (2 * a.half) {
-        case 2: return launch<2, COST>(ctx, a, ntx, nbands);
-        case 4: return launch<4, COST>(ctx, a, ntx, nbands);
-        case 6: return launch<6, COST>(ctx, a, ntx, nbands);
-        case 8: return launch<8, COST>(ctx, a, ntx, nbands);
-        case 10: return launch<10, COST>(ctx, a, ntx, nbands);
-        case 12: return launch<12, COST>(ctx, a, ntx, nbands);
-        case 14: return launch<14, COST>(ctx, a, ntx, nbands);
-        case 16: return launch<16, COST>(ctx, a, ntx, nbands);
+        case 2: return launch<2, COST>(ctx, a, nwork);
+        case 4: return launch<4, COST>(ctx, a, nwork);
+        case 6: return launch<6, COST>(ctx, a, nwork);
+        case 8: return launch<8, COST>(ctx, a, nwork);
+        case 10: return launch<10, COST>(ctx, a, nwork);
+        case 12: return launch<12, COST>(ctx, a, nwork);
+        case 14: return launch<14, COST>(ctx, a, nwork);
+        case 16: return launch<16, COST>(ctx, a, nwork);
         default: return 0;
     }
+}
+
+// The schedule of one launch: work items {tile, first row, end row, pass} in the order the CTAs should start.
+//  * Bands, then tiles, then passes (heaviest -- masked / ragged -- pass first): the passes of one (tile, band)
+//    run at the same time and share its image rows in L2, so DRAM reads stay near one sweep of the two images
+//    (pass-major order re-reads them once per wave: 295 MB instead of 106 MB on the 4K pair).
+//  * The last `pct` percent of the rows are cut into bands 1/div as tall: the last CTAs to start are short, so
+//    the SMs run dry together at the end of the kernel (4K/512: -6 %).
+//  * With the merged key plane, (tile, pass) combinations without a single candidate (break rule at the right
+//    image edge) are left out altogether.
+// Lists are cached per geometry on the context (the row-chunk pipeline repeats the same few shapes).
+int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx, int rows, int band, int nbands,
+                   const int4** work, int* nwork) {
+    static const char* ord_env = getenv("SR_TILE_ORDER");   // 0: pass-major (development comparison)
+    static const char* tl_env = getenv("SR_TILE_TAIL");     // "percent,divisor" tuning override
+    const int order = ord_env ? atoi(ord_env) : 1;
+    int pct = 10, div = 4;
+    if (tl_env) sscanf(tl_env, "%d,%d", &pct, &div);
+    TileWork key;
+    const int kv[TileWork::NKEY] = {g.w1, g.w2, g.half, a.dlo, a.dhi, a.row0, a.row1, a.merged, order, pct, div, band};
+    for (int i = 0; i < TileWork::NKEY; i++) key.key[i] = kv[i];
+    for (TileWork& t : ctx->tile_work)
+        if (!memcmp(t.key, key.key, sizeof key.key)) { t.stamp = ++ctx->tile_work_clock; *work = t.dev; *nwork = t.n; return SR_OK; }
+    // bands
+    std::vector<int2> bands;
+    {
+        int band2 = div > 1 ? band / div : band;
+        if (band2 < 2 * g.half + 2) band2 = 2 * g.half + 2;
+        int rows_tail = order && div > 1 && nbands >= 4 ? rows * pct / 100 : 0;
+        int nb1 = (rows - rows_tail + band - 1) / band;
+        int split = a.row0 + (nb1 * band < rows ? nb1 * band : rows);
+        for (int y = a.row0; y < split; y += band) bands.push_back(make_int2(y, y + band < split ? y + band : split));
+        for (int y = split; y < a.row1; y += band2) bands.push_back(make_int2(y, y + band2 < a.row1 ? y + band2 : a.row1));
+    }
+    auto has_candidates = [&](int tile, int pass) {
+        int x_first = -XT + TILE_OUT * tile + g.half;
+        if (x_first < 0) x_first = 0;
+        int r = g.w2 - x_first - 1 < g.half ? g.w2 - x_first - 1 : g.half;
+        int dlim = g.w1 - x_first - r < a.dhi ? g.w1 - x_first - r : a.dhi;
+        return a.dbase + 64 * pass < dlim;
+    };
+    std::vector<int4> items;
+    auto add = [&](int tile, int2 b, int pass) {
+        if (a.merged && !has_candidates(tile, pass)) return;   // planes mode: the CTA still writes its "none" keys
+        items.push_back(make_int4(tile, b.x, b.y, pass));
+    };
+    if (order) {
+        for (int2 b : bands) for (int t = 0; t < ntx; t++) for (int p = a.npass - 1; p >= 0; p--) add(t, b, p);
+    } else {
+        for (int p = a.npass - 1; p >= 0; p--) for (int2 b : bands) for (int t = 0; t < ntx; t++) add(t, b, p);
+    }
+    key.n = (int)items.size();
+    key.dev = nullptr;
+    if (key.n) {
+        if (ctx->tile_work.size() >= 64) {   // drop the least recently used list (no launch may still read it)
+            size_t lru = 0;
+            for (size_t i = 1; i < ctx->tile_work.size(); i++) if (ctx->tile_work[i].stamp < ctx->tile_work[lru].stamp) lru = i;
+            SR_CUDA(ctx, cudaDeviceSynchronize());
+            cudaFree(ctx->tile_work[lru].dev);
+            ctx->tile_work.erase(ctx->tile_work.begin() + lru);
+        }
+        SR_CUDA(ctx, cudaMalloc((void**)&key.dev, items.size() * sizeof(int4)));
+        SR_CUDA(ctx, cudaMemcpy(key.dev, items.data(), items.size() * sizeof(int4), cudaMemcpyHostToDevice));
+    }
+    key.stamp = ++ctx->tile_work_clock;
+    if (key.n) ctx->tile_work.push_back(key);
+    *work = key.dev; *nwork = key.n;
+    return SR_OK;
 }
 
 }  // namespace
@@ -412,19 +484,23 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     if (maxnb < 1) maxnb = 1;
     if (maxnb > 256) maxnb = 256;
     long bestcost = -1;
-    int nbands = 1;
+    int nbands = 1, band = rows;
     static const char* nb_env = getenv("SR_TILE_NBANDS");   // tuning override
     int nb_lo = 1;
     if (nb_env && atoi(nb_env) > 0) { nb_lo = atoi(nb_env); if (nb_lo > maxnb) nb_lo = maxnb; maxnb = nb_lo; }
     for (int nb = nb_lo; nb <= maxnb; nb++) {
-        int band = (rows + nb - 1) / nb;
-        int nbe = (rows + band - 1) / band;
+        int bnd = (rows + nb - 1) / nb;
+        int nbe = (rows + bnd - 1) / bnd;
         long ctas = (long)ntx * a.npass * nbe;
         // makespan model: CTAs are list-scheduled one per SM; durations vary (masked passes, image edges),
         // so the tail costs about one CTA duration on top of the average load
-        long c = (long)((double)(ctas + sms) / sms * (band + 2 * g.half - 1 + 2) * 16.0);
-        if (bestcost < 0 || c < bestcost) { bestcost = c; nbands = nbe; a.band = band; }
+        long c = (long)((double)(ctas + sms) / sms * (bnd + 2 * g.half - 1 + 2) * 16.0);
+        if (bestcost < 0 || c < bestcost) { bestcost = c; nbands = nbe; band = bnd; }
     }
-    if (cost == SR_COST_SAD) return dispatch_h2<SR_COST_SAD>(ctx, a, ntx, nbands);
-    return dispatch_h2<SR_COST_SSD_L2>(ctx, a, ntx, nbands);
+    int nwork = 0;
+    int rc = tile_work_list(ctx, g, a, ntx, rows, band, nbands, &a.work, &nwork);
+    if (rc != SR_OK) return rc;
+    if (nwork == 0) return 1;                                // merged plane, no (tile, pass) has a candidate: all "none"
+    if (cost == SR_COST_SAD) return dispatch_h2<SR_COST_SAD>(ctx, a, nwork);
+    return dispatch_h2<SR_COST_SSD_L2>(ctx, a, nwork);
 }

@@ -89,6 +89,7 @@ void sr_ctx_destroy(sr_ctx* ctx) {
     for (sr_pair* p : ctx->batch_pairs) sr_pair_destroy(ctx, p);
     ctx->batch_pairs.clear();
     for (cudaEvent_t e : ctx->pipe_ev) cudaEventDestroy(e);
+    for (TileWork& t : ctx->tile_work) cudaFree(t.dev);
     for (auto& b : ctx->scratch) if (b.p) cudaFree(b.p);
     for (auto& p : ctx->pinned) if (p) cudaFreeHost(p);
     cudaEventDestroy(ctx->ev0);

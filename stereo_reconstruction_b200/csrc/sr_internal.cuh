@@ -16,6 +16,15 @@ struct DevBuf {
     size_t cap = 0;
 };
 
+// cached schedule of a tile-kernel launch (search_tile.cu: tile_work_list)
+struct TileWork {
+    static constexpr int NKEY = 12;
+    int key[NKEY];
+    int4* dev = nullptr;
+    int n = 0;
+    uint64_t stamp = 0;
+};
+
 struct sr_stage_pool;   // host threads for pageable <-> pinned staging copies (host_stage.cu)
 
 struct sr_ctx {
@@ -34,6 +43,8 @@ struct sr_ctx {
     std::vector<sr_pair*> batch_pairs;
     std::vector<cudaEvent_t> pipe_ev;  // events of the row-chunk pipeline of sr_block_search
     sr_stage_pool* stage_pool = nullptr;
+    std::vector<TileWork> tile_work;   // schedules of the tile kernel, by geometry
+    uint64_t tile_work_clock = 0;
     void* nccl_comm = nullptr;
     int rank = 0, nranks = 1;
 };
