@@ -249,7 +249,9 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
         if (!cuda_ok(cudaStreamWaitEvent(cs, ctx->pipe_ev[3 * c], 0), "cudaStreamWaitEvent")) break;
         if (trace) cudaEventRecord(tev[4 * c + 1], cs);
         ctx->stream = cs;
+        ctx->more_chunks_follow = c + 1 < nch;
         rc = sr_search_run(ctx, pair, p, k.r0, k.r1);
+        ctx->more_chunks_follow = false;
         ctx->stream = compute;
         if (rc != SR_OK) break;
         if (trace) cudaEventRecord(tev[4 * c + 2], cs);

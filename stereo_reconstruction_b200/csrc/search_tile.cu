@@ -386,6 +386,7 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
     const int order = ord_env ? atoi(ord_env) : 1;
     int pct = 10, div = 4;
     if (tl_env) sscanf(tl_env, "%d,%d", &pct, &div);
+    if (ctx->more_chunks_follow) pct = 0;   // row-chunk pipeline: the next chunk's CTAs fill the end of this launch
     TileWork key;
     const int kv[TileWork::NKEY] = {g.w1, g.w2, g.half, a.dlo, a.dhi, a.row0, a.row1, a.merged, order, pct, div, band};
     for (int i = 0; i < TileWork::NKEY; i++) key.key[i] = kv[i];

@@ -45,6 +45,7 @@ struct sr_ctx {
     sr_stage_pool* stage_pool = nullptr;
     std::vector<TileWork> tile_work;   // schedules of the tile kernel, by geometry
     uint64_t tile_work_clock = 0;
+    bool more_chunks_follow = false;   // set by the row-chunk pipeline around all launches but the last chunk's
     void* nccl_comm = nullptr;
     int rank = 0, nranks = 1;
 };
