@@ -60,10 +60,11 @@ static int pipeline_chunks(const sr_pair* pair, const sr_search_params* p, int r
     const char* env = getenv("SR_PIPE_CHUNKS");   // tuning / test override
     int c = env ? atoi(env) : 0;
     if (c <= 0) {
-        // small pairs: one chunk (launch overheads dominate); large pairs: ~1 M right pixels per chunk
+        // small pairs: one chunk (launch overheads dominate); large pairs: ~0.8 M right pixels per chunk
+        // (4K pair, three compute streams: 6 chunks 2.46 ms, 8 -> 2.36, 10 -> 2.32, 12 -> 2.31)
         double px = (double)pair->w2 * rows;
-        c = (int)(px / 1.0e6);
-        if (c > 8) c = 8;
+        c = (int)(px / 0.8e6);
+        if (c > 12) c = 12;
     }
     int maxc = rows / (4 * p->block + 16);
     if (c > maxc) c = maxc;
@@ -160,7 +161,7 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     if (disp_out && out_pitch < rowb) return sr_fail(ctx, SR_E_BADARG, "output pitch %zu smaller than a row (%zu)", out_pitch, rowb);
     if (left->pitch < (size_t)left->w * 3 || right->pitch < (size_t)right->w * 3)
         return sr_fail(ctx, SR_E_BADARG, "image pitch smaller than a row");
-    while ((int)ctx->pipe_ev.size() < 3 * nch + 1) {
+    while ((int)ctx->pipe_ev.size() < 4 * nch + 1) {
         cudaEvent_t e;
         SR_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         ctx->pipe_ev.push_back(e);
@@ -204,15 +205,15 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     char* dstO = stO ? job.sO : (char*)disp_out;
     const size_t pitO = stO ? rowb : out_pitch;
 
-    cudaStream_t compute = ctx->stream, s_up = ctx->aux[0], s_down = ctx->aux[1];
+    cudaStream_t compute = ctx->stream, s_up = ctx->aux[0], s_down = ctx->aux[1], s_pack = ctx->aux[4];
     int rc = SR_OK;
     auto cuda_ok = [&](cudaError_t e, const char* what) { if (e != cudaSuccess && rc == SR_OK) rc = sr_cuda_check(ctx, e, what); return rc == SR_OK; };
     // the copy streams start after whatever the compute stream still has queued (previous call)
-    cudaEvent_t ev_start = ctx->pipe_ev[3 * nch];
+    cudaEvent_t ev_start = ctx->pipe_ev[4 * nch];
     cuda_ok(cudaEventRecord(ev_start, compute), "cudaEventRecord");
-    for (cudaStream_t s : {s_up, s_down, ctx->aux[2], ctx->aux[3]}) cuda_ok(cudaStreamWaitEvent(s, ev_start, 0), "cudaStreamWaitEvent");
-    // compute streams the chunks rotate over (measured on 4K/512: 1 -> 2.74 ms, 2 -> 2.37 ms, 3 -> 2.42 ms)
-    static const int ncs = getenv("SR_PIPE_STREAMS") ? atoi(getenv("SR_PIPE_STREAMS")) : 2;
+    for (cudaStream_t s : {s_up, s_down, s_pack, ctx->aux[2], ctx->aux[3]}) cuda_ok(cudaStreamWaitEvent(s, ev_start, 0), "cudaStreamWaitEvent");
+    // compute streams the chunks rotate over (4K/512, 10 chunks: 2 -> 2.40 ms, 3 -> 2.32 ms)
+    static const int ncs = getenv("SR_PIPE_STREAMS") ? atoi(getenv("SR_PIPE_STREAMS")) : 3;
     // SR_PIPE_TRACE=1: per-chunk timeline (ms since the start of the call) on stderr, development aid
     static const bool trace = getenv("SR_PIPE_TRACE") && atoi(getenv("SR_PIPE_TRACE")) != 0;
     std::vector<cudaEvent_t> tev;
@@ -224,29 +225,28 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     for (int c = 0; c < nch && rc == SR_OK; c++) {
         const PipeChunk& k = job.ch[c];
         if ((stL || stR) && !wait_count(job.in_done[c], nst, job.abort)) break;
-        {
-            cudaStream_t saved = ctx->stream;
-            ctx->stream = s_up;
-            if (k.q1 > k.q0) {
-                if (cuda_ok(cudaMemcpy2DAsync(pair->rawR + (size_t)k.q0 * rowR, rowR, srcR + (size_t)k.q0 * pitR, pitR, rowR, k.q1 - k.q0,
-                                              cudaMemcpyHostToDevice, s_up), "cudaMemcpy2DAsync(H2D right rows)"))
-                    rc = sr_launch_pack_rows(ctx, pair->rawR, rowR, right->w, k.q0, k.q1, &pair->R);
-            }
-            if (rc == SR_OK && k.l1 > k.l0) {
-                if (cuda_ok(cudaMemcpy2DAsync(pair->rawL + (size_t)k.l0 * rowL, rowL, srcL + (size_t)k.l0 * pitL, pitL, rowL, k.l1 - k.l0,
-                                              cudaMemcpyHostToDevice, s_up), "cudaMemcpy2DAsync(H2D left rows)"))
-                    rc = sr_launch_pack_rows(ctx, pair->rawL, rowL, left->w, k.l0, k.l1, &pair->L);
-            }
-            ctx->stream = saved;
-        }
+        // the copy stream carries nothing but copies, so the link never waits for a pack kernel to find an SM;
+        // one pack launch per chunk (both images) on a high-priority stream of its own
+        if (k.q1 > k.q0)
+            cuda_ok(cudaMemcpy2DAsync(pair->rawR + (size_t)k.q0 * rowR, rowR, srcR + (size_t)k.q0 * pitR, pitR, rowR, k.q1 - k.q0,
+                                      cudaMemcpyHostToDevice, s_up), "cudaMemcpy2DAsync(H2D right rows)");
+        if (rc == SR_OK && k.l1 > k.l0)
+            cuda_ok(cudaMemcpy2DAsync(pair->rawL + (size_t)k.l0 * rowL, rowL, srcL + (size_t)k.l0 * pitL, pitL, rowL, k.l1 - k.l0,
+                                      cudaMemcpyHostToDevice, s_up), "cudaMemcpy2DAsync(H2D left rows)");
         if (rc != SR_OK) break;
-        // chunks alternate between two compute streams: the first CTAs of chunk c+1 fill the SMs that
+        if (!cuda_ok(cudaEventRecord(ctx->pipe_ev[4 * c + 3], s_up), "cudaEventRecord")) break;
+        if (!cuda_ok(cudaStreamWaitEvent(s_pack, ctx->pipe_ev[4 * c + 3], 0), "cudaStreamWaitEvent")) break;
+        ctx->stream = s_pack;
+        rc = sr_launch_pack_rows2(ctx, pair->rawR, rowR, right->w, k.q0, k.q1, &pair->R, pair->rawL, rowL, left->w, k.l0, k.l1, &pair->L);
+        ctx->stream = compute;
+        if (rc != SR_OK) break;
+        // chunks rotate over the compute streams: the first CTAs of the next chunks fill the SMs that
         // the last wave of chunk c leaves idle (one 512-thread CTA per SM, so no other overlap exists)
         const int si = ncs >= 3 ? c % 3 : ncs == 2 ? (c & 1) : 0;
         cudaStream_t cs = si == 0 ? compute : ctx->aux[1 + si];
-        if (!cuda_ok(cudaEventRecord(ctx->pipe_ev[3 * c], s_up), "cudaEventRecord")) break;
-        if (trace) cudaEventRecord(tev[4 * c], s_up);
-        if (!cuda_ok(cudaStreamWaitEvent(cs, ctx->pipe_ev[3 * c], 0), "cudaStreamWaitEvent")) break;
+        if (!cuda_ok(cudaEventRecord(ctx->pipe_ev[4 * c], s_pack), "cudaEventRecord")) break;
+        if (trace) cudaEventRecord(tev[4 * c], s_pack);
+        if (!cuda_ok(cudaStreamWaitEvent(cs, ctx->pipe_ev[4 * c], 0), "cudaStreamWaitEvent")) break;
         if (trace) cudaEventRecord(tev[4 * c + 1], cs);
         ctx->stream = cs;
         ctx->more_chunks_follow = c + 1 < nch;
@@ -256,23 +256,24 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
         if (rc != SR_OK) break;
         if (trace) cudaEventRecord(tev[4 * c + 2], cs);
         if (!disp_out) continue;
-        if (!cuda_ok(cudaEventRecord(ctx->pipe_ev[3 * c + 1], cs), "cudaEventRecord")) break;
-        if (!cuda_ok(cudaStreamWaitEvent(s_down, ctx->pipe_ev[3 * c + 1], 0), "cudaStreamWaitEvent")) break;
+        if (!cuda_ok(cudaEventRecord(ctx->pipe_ev[4 * c + 1], cs), "cudaEventRecord")) break;
+        if (!cuda_ok(cudaStreamWaitEvent(s_down, ctx->pipe_ev[4 * c + 1], 0), "cudaStreamWaitEvent")) break;
         if (!cuda_ok(cudaMemcpy2DAsync(dstO + (size_t)k.r0 * pitO, pitO, pair->out + (size_t)k.r0 * ow, rowb, rowb, k.r1 - k.r0,
                                        cudaMemcpyDeviceToHost, s_down), "cudaMemcpy2DAsync(D2H rows)")) break;
-        if (stO && !cuda_ok(cudaEventRecord(ctx->pipe_ev[3 * c + 2], s_down), "cudaEventRecord")) break;
+        if (stO && !cuda_ok(cudaEventRecord(ctx->pipe_ev[4 * c + 2], s_down), "cudaEventRecord")) break;
         if (trace) cudaEventRecord(tev[4 * c + 3], s_down);
     }
     if (pool) {
         // hand finished output chunks to the staging threads in order; on an error release them instead
         for (int c = 0; c < nch && stO && rc == SR_OK; c++) {
-            if (cuda_ok(cudaEventSynchronize(ctx->pipe_ev[3 * c + 2]), "cudaEventSynchronize"))
+            if (cuda_ok(cudaEventSynchronize(ctx->pipe_ev[4 * c + 2]), "cudaEventSynchronize"))
                 job.out_ready[c].store(1, std::memory_order_release);
         }
         if (rc != SR_OK) job.abort.store(1);
         sr_stage_wait(pool);
     }
     cudaStreamSynchronize(s_up);
+    cudaStreamSynchronize(s_pack);
     cudaStreamSynchronize(compute);
     cudaStreamSynchronize(ctx->aux[2]);
     cudaStreamSynchronize(ctx->aux[3]);

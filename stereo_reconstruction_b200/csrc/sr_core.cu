@@ -71,6 +71,7 @@ int sr_ctx_create(int device, sr_ctx** out) {
         (e = cudaStreamCreateWithPriority(&c->aux[1], cudaStreamNonBlocking, prio_hi)) != cudaSuccess ||
         (e = cudaStreamCreateWithPriority(&c->aux[2], cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
         (e = cudaStreamCreateWithPriority(&c->aux[3], cudaStreamNonBlocking, prio_lo)) != cudaSuccess ||
+        (e = cudaStreamCreateWithPriority(&c->aux[4], cudaStreamNonBlocking, prio_hi)) != cudaSuccess ||
         (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
         (e = cudaEventCreate(&c->kev0)) != cudaSuccess || (e = cudaEventCreate(&c->kev1)) != cudaSuccess) {
         int rc = sr_cuda_check(nullptr, e, "stream/event creation");
@@ -100,6 +101,7 @@ void sr_ctx_destroy(sr_ctx* ctx) {
     cudaStreamDestroy(ctx->aux[1]);
     cudaStreamDestroy(ctx->aux[2]);
     cudaStreamDestroy(ctx->aux[3]);
+    cudaStreamDestroy(ctx->aux[4]);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -143,25 +145,60 @@ const char* sr_last_kernel(const sr_ctx* ctx) { return ctx ? ctx->last_kernel : 
 }  // extern "C"
 
 // ---- packing: BGR u8 (pitch) -> one uint32 per pixel, padded rows ---------------------------
-__global__ void pack_bgr_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, int w, int y0,
-                                uint32_t* __restrict__ dst, int pitch_px, int padl) {
-    // one thread per destination pixel of the padded row (padding written as 0)
-    int xp = blockIdx.x * blockDim.x + threadIdx.x;
-    int y = y0 + blockIdx.y;
-    if (xp >= pitch_px) return;
-    int x = xp - padl;
-    uint32_t v = 0;
-    if (x >= 0 && x < w) {
-        const uint8_t* p = raw + (size_t)y * raw_pitch + 3 * (size_t)x;
-        v = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
-    }
-    dst[(size_t)y * pitch_px + xp] = v;
+// The padding of a packed image is zeroed once at allocation; packing writes the image columns only.  One thread
+// makes four pixels: 12 source bytes from four aligned words (rows of a tight 3*w pitch start at any byte
+// offset, hence the funnel shifts), one 16-byte store.  Two images in one launch (blockIdx.z): the pipelines pack
+// while search CTAs own every SM, so each launch waits for an SM to come free.
+struct PackJob {
+    const uint8_t* raw; size_t raw_pitch; size_t raw_bytes; int w; int y0, y1;
+    uint32_t* px; int pitch_px;      // pointer to pixel (0,0), row pitch in pixels
+};
+
+__global__ void __launch_bounds__(256) pack_bgr_kernel(PackJob ja, PackJob jb) {
+    const PackJob& j = blockIdx.z ? jb : ja;
+    const int x0 = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const int y = j.y0 + blockIdx.y;
+    if (x0 >= j.w || y >= j.y1) return;
+    const size_t A = (size_t)y * j.raw_pitch + 3 * (size_t)x0;      // first source byte
+    const uint32_t* words = (const uint32_t*)j.raw;
+    const size_t wd = A >> 2, nwords = (j.raw_bytes + 3) >> 2;
+    const uint32_t sh = (uint32_t)(A & 3) * 8;
+    uint32_t w0 = __ldg(words + wd), w1 = wd + 1 < nwords ? __ldg(words + wd + 1) : 0u;
+    uint32_t w2 = wd + 2 < nwords ? __ldg(words + wd + 2) : 0u, w3 = wd + 3 < nwords ? __ldg(words + wd + 3) : 0u;
+    uint32_t t0 = __funnelshift_r(w0, w1, sh), t1 = __funnelshift_r(w1, w2, sh), t2 = __funnelshift_r(w2, w3, sh);
+    uint4 o;
+    o.x = t0 & 0xFFFFFFu;
+    o.y = __funnelshift_r(t0, t1, 24) & 0xFFFFFFu;
+    o.z = __funnelshift_r(t1, t2, 16) & 0xFFFFFFu;
+    o.w = t2 >> 8;
+    if (x0 + 1 >= j.w) o.y = 0;      // columns past the image: padding stays zero
+    if (x0 + 2 >= j.w) o.z = 0;
+    if (x0 + 3 >= j.w) o.w = 0;
+    *(uint4*)(j.px + (size_t)y * j.pitch_px + x0) = o;
+}
+
+static PackJob pack_job(const uint8_t* raw, size_t raw_pitch, int w, int h, int y0, int y1, PackedImage* img) {
+    PackJob j;
+    j.raw = raw; j.raw_pitch = raw_pitch; j.raw_bytes = raw_pitch * (size_t)h; j.w = w; j.y0 = y0; j.y1 = y1;
+    j.px = img->px; j.pitch_px = img->pitch;
+    return j;
+}
+
+int sr_launch_pack_rows2(sr_ctx* ctx, const uint8_t* rawa, size_t pitcha, int wa, int ya0, int ya1, PackedImage* imga,
+                         const uint8_t* rawb, size_t pitchb, int wb, int yb0, int yb1, PackedImage* imgb) {
+    int rows = ya1 - ya0 > yb1 - yb0 ? ya1 - ya0 : yb1 - yb0;
+    if (rows <= 0) return SR_OK;
+    int w = wa > wb ? wa : wb;
+    PackJob a = pack_job(rawa, pitcha, wa, imga->h, ya0, ya1, imga), b = pack_job(rawb, pitchb, wb, imgb->h, yb0, yb1, imgb);
+    pack_bgr_kernel<<<dim3(cdiv(w, 1024), rows, 2), 256, 0, ctx->stream>>>(a, b);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
 }
 
 int sr_launch_pack_rows(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int y0, int y1, PackedImage* img) {
     if (y1 <= y0) return SR_OK;
-    dim3 grid(cdiv(img->pitch, 256), y1 - y0);
-    pack_bgr_kernel<<<grid, 256, 0, ctx->stream>>>(raw, raw_pitch, w, y0, img->base, img->pitch, SR_PADL);
+    PackJob a = pack_job(raw, raw_pitch, w, img->h, y0, y1, img);
+    pack_bgr_kernel<<<dim3(cdiv(w, 1024), y1 - y0, 1), 256, 0, ctx->stream>>>(a, a);
     SR_LAUNCHED(ctx);
     return SR_OK;
 }
@@ -196,6 +233,7 @@ int sr_alloc_packed(sr_ctx* ctx, PackedImage* img, int w, int h, int padr) {
     img->w = w; img->h = h;
     img->pitch = ((SR_PADL + w + padr + 31) / 32) * 32;
     SR_CUDA(ctx, cudaMalloc((void**)&img->base, (size_t)img->pitch * h * sizeof(uint32_t)));
+    SR_CUDA(ctx, cudaMemset(img->base, 0, (size_t)img->pitch * h * sizeof(uint32_t)));   // the padding stays zero for good
     img->px = img->base + SR_PADL;
     return SR_OK;
 }

@@ -30,7 +30,7 @@ struct sr_stage_pool;   // host threads for pageable <-> pinned staging copies (
 struct sr_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaStream_t aux[4] = {nullptr, nullptr, nullptr, nullptr};  // copy streams of the pipelines + extra compute streams
+    cudaStream_t aux[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // 0/1: copy streams of the pipelines, 2/3: extra compute streams, 4: pack kernels (high priority)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t kev0 = nullptr, kev1 = nullptr;  // around the dominant search kernel of the last run
     bool kev_valid = false;
@@ -139,6 +139,9 @@ int sr_launch_pack(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int
 int sr_launch_pack_mirror(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int h, int wref, PackedImage* img);
 int sr_alloc_packed(sr_ctx* ctx, PackedImage* img, int w, int h, int padr);
 int sr_launch_pack_rows(sr_ctx* ctx, const uint8_t* raw, size_t raw_pitch, int w, int y0, int y1, PackedImage* img);
+// the same for two images in one launch (rows [ya0,ya1) of a, [yb0,yb1) of b)
+int sr_launch_pack_rows2(sr_ctx* ctx, const uint8_t* rawa, size_t pitcha, int wa, int ya0, int ya1, PackedImage* imga,
+                         const uint8_t* rawb, size_t pitchb, int wb, int yb0, int yb1, PackedImage* imgb);
 
 // Fast path: fixed window, SSD/SAD, first minimum over [dlo,dhi) -> pair->best.
 // Returns 1 when it handled the request, 0 when the shape is not supported (caller falls back).
