@@ -40,7 +40,7 @@ WORKLOADS = {
 OPS_PER_EVAL = {"ssd": 8, "sad": 7}
 # dram__bytes_read.sum + dram__bytes_write.sum of the search kernel from the committed ncu capture
 # (profiles/), per launch, keyed by workload; None = not captured for this workload
-NCU_TRAFFIC = {"4k512": 279182336 + 235187968}   # profiles/r01_tile_sad_4k512_ncu_full.csv (read + write bytes)
+NCU_TRAFFIC = {"4k512": 105726720 + 14286080}   # profiles/r01_tile_sad_4k512_ncu_full.csv (read + write bytes)
 
 
 def parse():
@@ -78,6 +78,14 @@ class ClockSampler:
         for ln in self.proc.stdout:
             self.lines.append(ln.strip())
 
+    def mark(self, timeout=3.0):
+        """Waits until nvidia-smi delivers its first sample (its start-up takes longer than a short timed region),
+        then marks the start of the region: only samples from here on are reported."""
+        t0 = time.time()
+        while self.proc and not self.lines and time.time() - t0 < timeout:
+            time.sleep(0.005)
+        self.start = len(self.lines)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -88,7 +96,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        start = getattr(self, "start", 0)
+        for ln in (self.lines[start:] or self.lines[-1:]):   # a region shorter than the 20 ms period: the sample just before it
             f = [t.strip() for t in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -264,6 +273,8 @@ def main():
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
     peak_dual, peak_single = ctx.int_peak()
+    if sampler:
+        sampler.mark()
     for _ in range(max(args.warmup, 3)):
         ctx.l2_flush()                       # warm-up steps look exactly like timed steps (first flush allocates)
         step_resident()
