@@ -11,6 +11,9 @@
 #include <condition_variable>
 #include <mutex>
 #include <thread>
+#if defined(__x86_64__)
+#include <emmintrin.h>
+#endif
 
 struct sr_stage_pool {
     std::vector<std::thread> th;
@@ -104,6 +107,33 @@ void sr_stage_wait(sr_stage_pool* p) {
     p->cv_done.wait(lk, [&] { return p->running == 0; });
 }
 
+// Large copies with streaming stores: the destination lines are written without being read first and without
+// displacing the source from the caches (a third less memory traffic than a write-allocate copy).  The fence
+// makes the data globally visible before the caller publishes "staged" to the thread that queues the DMA.
+static const bool g_stream_copy = !(getenv("SR_STAGE_STREAM") && atoi(getenv("SR_STAGE_STREAM")) == 0);
+static void copy_bytes(char* dst, const char* src, size_t n) {
+#if defined(__x86_64__)
+    if (g_stream_copy && n >= 16384) {
+        size_t head = (16 - ((uintptr_t)dst & 15)) & 15;
+        memcpy(dst, src, head);
+        dst += head; src += head; n -= head;
+        size_t blocks = n / 64;
+        for (size_t i = 0; i < blocks; i++) {
+            __m128i a = _mm_loadu_si128((const __m128i*)src), b = _mm_loadu_si128((const __m128i*)(src + 16));
+            __m128i c = _mm_loadu_si128((const __m128i*)(src + 32)), d = _mm_loadu_si128((const __m128i*)(src + 48));
+            _mm_stream_si128((__m128i*)dst, a);
+            _mm_stream_si128((__m128i*)(dst + 16), b);
+            _mm_stream_si128((__m128i*)(dst + 32), c);
+            _mm_stream_si128((__m128i*)(dst + 48), d);
+            src += 64; dst += 64;
+        }
+        _mm_sfence();
+        n -= blocks * 64;
+    }
+#endif
+    memcpy(dst, src, n);
+}
+
 void sr_stage_stripe(char* dst, size_t dpitch, const char* src, size_t spitch, size_t rowbytes, int row0, int row1,
                      int t, int nthreads) {
     int n = row1 - row0;
@@ -112,10 +142,10 @@ void sr_stage_stripe(char* dst, size_t dpitch, const char* src, size_t spitch, s
     int a = row0 + t * per, b = a + per < row1 ? a + per : row1;
     if (a >= b) return;
     if (dpitch == rowbytes && spitch == rowbytes) {
-        memcpy(dst + (size_t)a * dpitch, src + (size_t)a * spitch, (size_t)(b - a) * rowbytes);
+        copy_bytes(dst + (size_t)a * dpitch, src + (size_t)a * spitch, (size_t)(b - a) * rowbytes);
         return;
     }
-    for (int y = a; y < b; y++) memcpy(dst + (size_t)y * dpitch, src + (size_t)y * spitch, rowbytes);
+    for (int y = a; y < b; y++) copy_bytes(dst + (size_t)y * dpitch, src + (size_t)y * spitch, rowbytes);
 }
 
 namespace {
