@@ -1,6 +1,7 @@
 // capi_batch.cu -- sr_block_search_batch: n independent pairs of one shape (config 5), pipelined
 // H2D + pack (copy stream 0) / search kernels (compute stream) / D2H (copy stream 1) over a ring
-// of device-resident pair objects.  With pinned host buffers the three stages overlap fully.
+// of device-resident pair objects.  With pinned host buffers the three stages overlap fully; pageable buffers
+// go through pinned staging, copied by the host staging threads (host_stage.cu).
 #include "sr_internal.cuh"
 
 namespace {
@@ -45,10 +46,28 @@ extern "C" int sr_block_search_batch(sr_ctx* ctx, int n, const sr_image* left, c
     size_t rowb = (size_t)ow * sizeof(double);
     int rc = SR_OK;
     cudaStream_t compute = ctx->stream;
+    // pageable outputs (cv::Mat memory): each slot downloads into its own pinned staging; the striped host copy
+    // to the caller's buffer happens when the slot comes round again, while the GPU works on the pairs in between
+    bool stage_out = false;
+    for (int i = 0; i < n && !stage_out; i++) {
+        cudaPointerAttributes attr;
+        stage_out = !(cudaPointerGetAttributes(&attr, disp_out[i]) == cudaSuccess &&
+                      (attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged));
+        cudaGetLastError();
+    }
+    char* stage = nullptr;
+    const size_t slot_bytes = rowb * (size_t)oh;
+    if (stage_out && !(stage = (char*)sr_pinned(ctx, 3, slot_bytes * NB))) return SR_E_CUDA;
+    auto drain = [&](int i) {   // pair i's staged result -> the caller's buffer
+        cudaError_t e = cudaEventSynchronize(down[i % NB]);
+        if (e != cudaSuccess) return sr_cuda_check(ctx, e, "cudaEventSynchronize(batch D2H)");
+        return sr_stage_copy_rows(ctx, disp_out[i], out_pitch, stage + slot_bytes * (i % NB), rowb, rowb, oh);
+    };
     for (int i = 0; i < n && rc == SR_OK; i++) {
         int s = i % NB;
         sr_pair* pair = ctx->batch_pairs[s];
         if (i >= NB) {  // the slot's previous search must be done with the images, its result downloaded
+            if (stage_out && (rc = drain(i - NB)) != SR_OK) break;
             cudaStreamWaitEvent(ctx->aux[0], comp[s], 0);
             cudaStreamWaitEvent(compute, down[s], 0);
         }
@@ -64,10 +83,13 @@ extern "C" int sr_block_search_batch(sr_ctx* ctx, int n, const sr_image* left, c
         cudaEventRecord(comp[s], compute);
         cudaStreamWaitEvent(ctx->aux[1], comp[s], 0);
         if (out_pitch < rowb) { rc = sr_fail(ctx, SR_E_BADARG, "output pitch smaller than a row"); break; }
-        cudaError_t e = cudaMemcpy2DAsync(disp_out[i], out_pitch, pair->out, rowb, rowb, oh, cudaMemcpyDeviceToHost, ctx->aux[1]);
+        cudaError_t e = stage_out ? cudaMemcpyAsync(stage + slot_bytes * s, pair->out, slot_bytes, cudaMemcpyDeviceToHost, ctx->aux[1])
+                                  : cudaMemcpy2DAsync(disp_out[i], out_pitch, pair->out, rowb, rowb, oh, cudaMemcpyDeviceToHost, ctx->aux[1]);
         if (e != cudaSuccess) { rc = sr_cuda_check(ctx, e, "cudaMemcpy2DAsync(batch D2H)"); break; }
         cudaEventRecord(down[s], ctx->aux[1]);
     }
+    if (stage_out && rc == SR_OK)
+        for (int i = n > NB ? n - NB : 0; i < n && rc == SR_OK; i++) rc = drain(i);
     cudaStreamSynchronize(ctx->aux[0]);
     cudaStreamSynchronize(compute);
     cudaStreamSynchronize(ctx->aux[1]);
