@@ -56,23 +56,33 @@ __global__ void blur_cols_kernel(const double* __restrict__ rows, int w, int h, 
 // 1436x992 map with k = 500).  When every partial sum is EXACTLY representable in fp64 the order of
 // the additions does not matter and the window sums can come from parallel prefix sums with the
 // identical result.  blur_exact_check_kernel proves that on the device: all nonzero inputs are multiples
-// of 2^q with |v| < 2^E, any signed sum of N <= 2k^2 of them is a multiple of 2^q below N*2^E, exact iff
-// E - q + ceil(log2 N) <= 53.  (Always true for the reference's 8-bit hand-off, main.cpp:41-50, and for
-// sub-pixel maps within a 2^10 dynamic range.)  Both kernel families are launched; each returns at once
-// when the flag says the other one applies -- no host round trip.
-__global__ void blur_exact_check_kernel(const float* __restrict__ src, size_t n, int* __restrict__ flag /* [emax+1, qmin, bad] */) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+// of 2^q with |v| < 2^E, any signed sum of N of them is a multiple of 2^q below N*2^E, exact iff
+// E - q + ceil(log2 N) <= 53, with N = the longest prefix any kernel below forms: (h + k - 1) * k inputs in a column
+// prefix (>= the w + k - 1 of a row prefix for every map at least as tall as it is wide / k, the host takes the
+// maximum).  (Always true for the reference's 8-bit hand-off, main.cpp:41-50, and for sub-pixel maps within a 2^10
+// dynamic range.)  Both kernel families are launched; each returns at once when the flag says the other one
+// applies -- no host round trip.
+__device__ __forceinline__ void exact_acc(uint32_t b, int& E, int& q, int& bad) {
+    uint32_t ex = (b >> 23) & 0xFFu, man = b & 0x7FFFFFu;
+    if (ex == 0xFFu || (ex == 0 && man != 0)) { bad = 1; return; }   // inf / NaN / denormal: keep the recurrence
+    if (ex == 0) return;                                              // zero
+    uint32_t m = man | 0x800000u;
+    int e = (int)ex - 127;
+    E = max(E, e + 1);
+    q = min(q, e - 23 + (__ffs(m) - 1));
+}
+// nvec = number of 16-byte words read with vector loads (two per thread in flight); the tail is read by element
+__global__ void blur_exact_check_kernel(const float* __restrict__ src, size_t n, size_t nvec, int* __restrict__ flag /* [emax+1, qmin, bad] */) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x, tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     int E = -1000, q = 1000, bad = 0;
-    for (; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        uint32_t b = __float_as_uint(src[i]);
-        uint32_t ex = (b >> 23) & 0xFFu, man = b & 0x7FFFFFu;
-        if (ex == 0xFFu || (ex == 0 && man != 0)) { bad = 1; continue; }   // inf / NaN / denormal: keep the recurrence
-        if (ex == 0) continue;                                              // zero
-        uint32_t m = man | 0x800000u;
-        int e = (int)ex - 127;
-        E = max(E, e + 1);
-        q = min(q, e - 23 + (__ffs(m) - 1));
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    for (size_t i = tid; i < nvec; i += 2 * stride) {
+        uint4 a = s4[i];
+        uint4 b = i + stride < nvec ? s4[i + stride] : make_uint4(0u, 0u, 0u, 0u);   // zeros are neutral
+        exact_acc(a.x, E, q, bad); exact_acc(a.y, E, q, bad); exact_acc(a.z, E, q, bad); exact_acc(a.w, E, q, bad);
+        exact_acc(b.x, E, q, bad); exact_acc(b.y, E, q, bad); exact_acc(b.z, E, q, bad); exact_acc(b.w, E, q, bad);
     }
+    for (size_t i = 4 * nvec + tid; i < n; i += stride) exact_acc(__float_as_uint(src[i]), E, q, bad);
     for (int off = 16; off > 0; off >>= 1) {
         E = max(E, __shfl_xor_sync(0xffffffffu, E, off));
         q = min(q, __shfl_xor_sync(0xffffffffu, q, off));
@@ -80,28 +90,37 @@ __global__ void blur_exact_check_kernel(const float* __restrict__ src, size_t n,
     }
     if ((threadIdx.x & 31) == 0) { atomicMax(flag, E); atomicMin(flag + 1, q); if (bad) atomicOr(flag + 2, 1); }
 }
-__device__ __forceinline__ bool blur_is_exact(const int* flag, int k) {
+// logn = ceil(log2 N) of the comment above (host: blur_logn)
+__device__ __forceinline__ bool blur_is_exact(const int* flag, int logn) {
     if (flag[2]) return false;
     if (flag[0] <= -1000) return true;                                      // all zeros
-    int logn = 1;
-    long long nn = 2LL * k * k;
-    while ((1LL << logn) < nn) logn++;
     return flag[0] - flag[1] + logn <= 53;
 }
+static int blur_logn(int w, int h, int k) {
+    long long nn = (long long)(h + k - 1) * k, rw = (long long)w + k - 1;
+    if (rw > nn) nn = rw;
+    if (2LL * k * k > nn) nn = 2LL * k * k;
+    int logn = 1;
+    while ((1LL << logn) < nn) logn++;
+    return logn;
+}
 
-// One CTA per row: inclusive prefix sums of the reflect-101 extended row in shared memory, then
-// rowsum[x] = PE[x + k - 1] - PE[x - 1].
+// One CTA per row: the reflect-101 extended row is staged in shared memory with coalesced loads, turned into
+// inclusive prefix sums there (per-thread chunks of odd length: conflict-free 64-bit accesses, then a scan of
+// the chunk totals), and rowsum[x] = PE[x + k - 1] - PE[x - 1].
 #define BLUR_T 256
-__global__ void __launch_bounds__(BLUR_T) blur_rows_fast_kernel(const float* __restrict__ src, int w, int h, int k,
+__global__ void __launch_bounds__(BLUR_T) blur_rows_fast_kernel(const float* __restrict__ src, int w, int h, int k, int logn,
                                                                 double* __restrict__ rows, const int* __restrict__ flag) {
     extern __shared__ double pe[];               // w + k - 1 prefix values
     __shared__ double wsum[BLUR_T / 32];
-    if (!blur_is_exact(flag, k)) return;
+    if (!blur_is_exact(flag, logn)) return;
     const int y = blockIdx.x, t = threadIdx.x, a = k / 2, we = w + k - 1;
     const float* s = src + (size_t)y * w;
-    const int C = (we + BLUR_T - 1) / BLUR_T, j0 = t * C, j1 = min(j0 + C, we);
+    for (int j = t; j < we; j += BLUR_T) pe[j] = (double)s[reflect101(j - a, w)];
+    __syncthreads();
+    const int C = ((we + BLUR_T - 1) / BLUR_T) | 1, j0 = min(t * C, we), j1 = min(j0 + C, we);
     double acc = 0;
-    for (int j = j0; j < j1; j++) { acc += (double)s[reflect101(j - a, w)]; pe[j] = acc; }
+    for (int j = j0; j < j1; j++) { acc += pe[j]; pe[j] = acc; }
     // exclusive scan of the per-thread totals
     double v = acc;
     for (int off = 1; off < 32; off <<= 1) { double u = __shfl_up_sync(0xffffffffu, v, off); if ((t & 31) >= off) v += u; }
@@ -118,41 +137,67 @@ __global__ void __launch_bounds__(BLUR_T) blur_rows_fast_kernel(const float* __r
 // Columns: segment sums -> per-column exclusive scan of the segments -> prefix array PE (h + k - 1 rows)
 // -> dst = (float)((PE[y + k - 1] - PE[y - 1]) * scale).  Threads run along x (coalesced).
 #define BLUR_NSEG 64
-__global__ void blur_cols_seg_kernel(const double* __restrict__ rows, int w, int h, int k, double* __restrict__ seg,
+__global__ void blur_cols_seg_kernel(const double* __restrict__ rows, int w, int h, int k, int logn, double* __restrict__ seg,
                                      const int* __restrict__ flag) {
-    if (!blur_is_exact(flag, k)) return;
+    if (!blur_is_exact(flag, logn)) return;
     int x = blockIdx.x * blockDim.x + threadIdx.x, sgi = blockIdx.y;
     if (x >= w) return;
     const int a = k / 2, he = h + k - 1, SL = (he + BLUR_NSEG - 1) / BLUR_NSEG;
     const int j0 = sgi * SL, j1 = min(j0 + SL, he);
-    double acc = 0;
-    for (int j = j0; j < j1; j++) acc += rows[(size_t)reflect101(j - a, h) * w + x];
-    seg[(size_t)sgi * w + x] = acc;
+    // four loads in flight; any order of the additions gives the same (exact) sum
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    int j = j0;
+    for (; j + 3 < j1; j += 4) {
+        double r0 = rows[(size_t)reflect101(j - a, h) * w + x], r1 = rows[(size_t)reflect101(j + 1 - a, h) * w + x];
+        double r2 = rows[(size_t)reflect101(j + 2 - a, h) * w + x], r3 = rows[(size_t)reflect101(j + 3 - a, h) * w + x];
+        a0 += r0; a1 += r1; a2 += r2; a3 += r3;
+    }
+    for (; j < j1; j++) a0 += rows[(size_t)reflect101(j - a, h) * w + x];
+    seg[(size_t)sgi * w + x] = (a0 + a1) + (a2 + a3);
 }
-__global__ void blur_cols_prefix_kernel(const double* __restrict__ rows, int w, int h, int k, const double* __restrict__ seg,
-                                        double* __restrict__ pe, const int* __restrict__ flag) {
-    if (!blur_is_exact(flag, k)) return;
+__global__ void blur_cols_prefix_kernel(const double* __restrict__ rows, int w, int h, int k, int logn,
+                                        const double* __restrict__ seg, double* __restrict__ pe, const int* __restrict__ flag) {
+    if (!blur_is_exact(flag, logn)) return;
     int x = blockIdx.x * blockDim.x + threadIdx.x, sgi = blockIdx.y;
     if (x >= w) return;
     const int a = k / 2, he = h + k - 1, SL = (he + BLUR_NSEG - 1) / BLUR_NSEG;
     const int j0 = sgi * SL, j1 = min(j0 + SL, he);
     double acc = 0;
     for (int i = 0; i < sgi; i++) acc += seg[(size_t)i * w + x];
-    for (int j = j0; j < j1; j++) { acc += rows[(size_t)reflect101(j - a, h) * w + x]; pe[(size_t)j * w + x] = acc; }
+    int j = j0;
+    for (; j + 3 < j1; j += 4) {
+        double r0 = rows[(size_t)reflect101(j - a, h) * w + x], r1 = rows[(size_t)reflect101(j + 1 - a, h) * w + x];
+        double r2 = rows[(size_t)reflect101(j + 2 - a, h) * w + x], r3 = rows[(size_t)reflect101(j + 3 - a, h) * w + x];
+        acc += r0; pe[(size_t)j * w + x] = acc;
+        acc += r1; pe[(size_t)(j + 1) * w + x] = acc;
+        acc += r2; pe[(size_t)(j + 2) * w + x] = acc;
+        acc += r3; pe[(size_t)(j + 3) * w + x] = acc;
+    }
+    for (; j < j1; j++) { acc += rows[(size_t)reflect101(j - a, h) * w + x]; pe[(size_t)j * w + x] = acc; }
 }
-__global__ void blur_cols_out_kernel(const double* __restrict__ pe, int w, int h, int k, float* __restrict__ dst,
+// two columns per thread: 16-byte loads of both prefix rows when the row pitch allows (w even)
+__global__ void blur_cols_out_kernel(const double* __restrict__ pe, int w, int h, int k, int logn, float* __restrict__ dst,
                                      const int* __restrict__ flag) {
-    if (!blur_is_exact(flag, k)) return;
-    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (!blur_is_exact(flag, logn)) return;
+    int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x), y = blockIdx.y;
     if (x >= w) return;
-    double scale = 1.0 / ((double)k * (double)k);
-    double s0 = pe[(size_t)(y + k - 1) * w + x] - (y > 0 ? pe[(size_t)(y - 1) * w + x] : 0.0);
-    dst[(size_t)y * w + x] = (float)(s0 * scale);
+    const double scale = 1.0 / ((double)k * (double)k);
+    const double* hi = pe + (size_t)(y + k - 1) * w + x;
+    const double* lo = pe + (size_t)(y > 0 ? y - 1 : 0) * w + x;
+    float* o = dst + (size_t)y * w + x;
+    if ((w & 1) == 0) {
+        double2 ph = *reinterpret_cast<const double2*>(hi);
+        double2 pl = y > 0 ? *reinterpret_cast<const double2*>(lo) : make_double2(0.0, 0.0);
+        *reinterpret_cast<float2*>(o) = make_float2((float)((ph.x - pl.x) * scale), (float)((ph.y - pl.y) * scale));
+    } else {
+        o[0] = (float)((hi[0] - (y > 0 ? lo[0] : 0.0)) * scale);
+        if (x + 1 < w) o[1] = (float)((hi[1] - (y > 0 ? lo[1] : 0.0)) * scale);
+    }
 }
 // the sequential kernels, skipped when the order-free path applies
-__global__ void blur_rows_seq_kernel(const float* __restrict__ src, int w, int h, int k, double* __restrict__ rows,
+__global__ void blur_rows_seq_kernel(const float* __restrict__ src, int w, int h, int k, int logn, double* __restrict__ rows,
                                      const int* __restrict__ flag) {
-    if (blur_is_exact(flag, k)) return;
+    if (blur_is_exact(flag, logn)) return;
     int y = blockIdx.x * blockDim.x + threadIdx.x;
     if (y >= h) return;
     const float* s = src + (size_t)y * w;
@@ -166,9 +211,9 @@ __global__ void blur_rows_seq_kernel(const float* __restrict__ src, int w, int h
         o[x] = acc;
     }
 }
-__global__ void blur_cols_seq_kernel(const double* __restrict__ rows, int w, int h, int k, float* __restrict__ dst,
+__global__ void blur_cols_seq_kernel(const double* __restrict__ rows, int w, int h, int k, int logn, float* __restrict__ dst,
                                      const int* __restrict__ flag) {
-    if (blur_is_exact(flag, k)) return;
+    if (blur_is_exact(flag, logn)) return;
     int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= w) return;
     int a = k / 2;
@@ -203,37 +248,48 @@ int recon_box_blur(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, 
     static const int flag_init[4] = {-1000, 1000, 0, 0};
     SR_CUDA(ctx, cudaMemcpyAsync(flag, flag_init, sizeof flag_init, cudaMemcpyHostToDevice, ctx->stream));
     size_t n = (size_t)w * h;
-    blur_exact_check_kernel<<<148 * 4, 256, 0, ctx->stream>>>(d_src, n, flag);
+    const int logn = blur_logn(w, h, k);
+    const size_t nvec = ((uintptr_t)d_src & 15) ? 0 : n / 4;
+    blur_exact_check_kernel<<<148 * 8, 256, 0, ctx->stream>>>(d_src, n, nvec, flag);
     SR_LAUNCHED(ctx);
     static bool configured = false;
     if (!configured) {
         SR_CUDA(ctx, cudaFuncSetAttribute(blur_rows_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         configured = true;
     }
-    blur_rows_fast_kernel<<<h, BLUR_T, smem, ctx->stream>>>(d_src, w, h, k, rows, flag);
+    blur_rows_fast_kernel<<<h, BLUR_T, smem, ctx->stream>>>(d_src, w, h, k, logn, rows, flag);
     SR_LAUNCHED(ctx);
     dim3 gs(cdiv(w, 128), BLUR_NSEG);
-    blur_cols_seg_kernel<<<gs, 128, 0, ctx->stream>>>(rows, w, h, k, seg, flag);
+    blur_cols_seg_kernel<<<gs, 128, 0, ctx->stream>>>(rows, w, h, k, logn, seg, flag);
     SR_LAUNCHED(ctx);
-    blur_cols_prefix_kernel<<<gs, 128, 0, ctx->stream>>>(rows, w, h, k, seg, pe, flag);
+    blur_cols_prefix_kernel<<<gs, 128, 0, ctx->stream>>>(rows, w, h, k, logn, seg, pe, flag);
     SR_LAUNCHED(ctx);
-    blur_cols_out_kernel<<<dim3(cdiv(w, 128), h), 128, 0, ctx->stream>>>(pe, w, h, k, d_dst, flag);
+    blur_cols_out_kernel<<<dim3(cdiv(w, 256), h), 128, 0, ctx->stream>>>(pe, w, h, k, logn, d_dst, flag);
     SR_LAUNCHED(ctx);
     // inputs outside the proof (huge dynamic range, inf/NaN): the recurrences, exactly as OpenCV runs them
-    blur_rows_seq_kernel<<<cdiv(h, 64), 64, 0, ctx->stream>>>(d_src, w, h, k, rows, flag);
+    blur_rows_seq_kernel<<<cdiv(h, 64), 64, 0, ctx->stream>>>(d_src, w, h, k, logn, rows, flag);
     SR_LAUNCHED(ctx);
-    blur_cols_seq_kernel<<<cdiv(w, 64), 64, 0, ctx->stream>>>(rows, w, h, k, d_dst, flag);
+    blur_cols_seq_kernel<<<cdiv(w, 64), 64, 0, ctx->stream>>>(rows, w, h, k, logn, d_dst, flag);
     SR_LAUNCHED(ctx);
     return SR_OK;
 }
 
-// reconstruction.cpp:11-17
+// reconstruction.cpp:11-17.  Four pixels per thread (16-byte loads of both maps when vec != 0).
+__device__ __forceinline__ float outlier1(float d, float b, float thr_front, float thr_back) {
+    return (d > thr_front * b || d < thr_back * b) ? b : d;
+}
 __global__ void outlier_replace_kernel(float* __restrict__ disp, const float* __restrict__ blurred, size_t n,
-                                       float thr_front, float thr_back) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+                                       float thr_front, float thr_back, int vec) {
+    size_t i = 4 * ((size_t)blockIdx.x * blockDim.x + threadIdx.x);
     if (i >= n) return;
-    float d = disp[i], b = blurred[i];
-    if (d > thr_front * b || d < thr_back * b) disp[i] = b;
+    if (vec && i + 3 < n) {
+        float4 d = *reinterpret_cast<const float4*>(disp + i), b = *reinterpret_cast<const float4*>(blurred + i);
+        d.x = outlier1(d.x, b.x, thr_front, thr_back); d.y = outlier1(d.y, b.y, thr_front, thr_back);
+        d.z = outlier1(d.z, b.z, thr_front, thr_back); d.w = outlier1(d.w, b.w, thr_front, thr_back);
+        *reinterpret_cast<float4*>(disp + i) = d;
+    } else {
+        for (size_t e = min(i + 4, n); i < e; i++) disp[i] = outlier1(disp[i], blurred[i], thr_front, thr_back);
+    }
 }
 
 int recon_remove_outliers(sr_ctx* ctx, float* d_disp, int w, int h, int k, float thr_front, float thr_back) {
@@ -242,7 +298,8 @@ int recon_remove_outliers(sr_ctx* ctx, float* d_disp, int w, int h, int k, float
     int rc = recon_box_blur(ctx, d_disp, blurred, w, h, k);
     if (rc != SR_OK) return rc;
     size_t n = (size_t)w * h;
-    outlier_replace_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_disp, blurred, n, thr_front, thr_back);
+    const int vec = (((uintptr_t)d_disp | (uintptr_t)blurred) & 15) == 0;
+    outlier_replace_kernel<<<(unsigned)((n + 1023) / 1024), 256, 0, ctx->stream>>>(d_disp, blurred, n, thr_front, thr_back, vec);
     SR_LAUNCHED(ctx);
     return SR_OK;
 }
@@ -350,16 +407,23 @@ __global__ void __launch_bounds__(FACE_THREADS) face_count_kernel(const sr_verte
     }
 }
 
-// single-CTA exclusive scan of the block totals (in place); total -> block_total[nblocks]
+// single-CTA exclusive scan of the block totals (in place), four per thread and 4096 per sweep (16-byte loads: the
+// array is 16-byte aligned and padded, see recon_mesh_faces); total -> block_total[nblocks]
 __global__ void __launch_bounds__(1024) face_scan_kernel(uint32_t* __restrict__ block_total, unsigned nblocks) {
     __shared__ uint32_t wsum[32];
     __shared__ uint32_t carry;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
-    for (unsigned base = 0; base < nblocks; base += 1024) {
-        unsigned i = base + threadIdx.x;
-        uint32_t v = i < nblocks ? block_total[i] : 0u;
-        uint32_t inc = v;
+    for (unsigned base = 0; base < nblocks; base += 4096) {
+        unsigned i = base + 4 * threadIdx.x;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (i < nblocks) {
+            v = *reinterpret_cast<const uint4*>(block_total + i);
+            if (i + 1 >= nblocks) v.y = 0;
+            if (i + 2 >= nblocks) v.z = 0;
+            if (i + 3 >= nblocks) v.w = 0;
+        }
+        uint32_t tot = v.x + v.y + v.z + v.w, inc = tot;
         for (int o = 1; o < 32; o <<= 1) {
             uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
             if ((threadIdx.x & 31) >= o) inc += t;
@@ -375,10 +439,16 @@ __global__ void __launch_bounds__(1024) face_scan_kernel(uint32_t* __restrict__ 
             wsum[threadIdx.x] = si - s;  // exclusive warp offsets
         }
         __syncthreads();
-        uint32_t excl = carry + wsum[threadIdx.x >> 5] + inc - v;
-        if (i < nblocks) block_total[i] = excl;
+        uint32_t excl = carry + wsum[threadIdx.x >> 5] + inc - tot;
+        if (i + 3 < nblocks) {
+            *reinterpret_cast<uint4*>(block_total + i) = make_uint4(excl, excl + v.x, excl + v.x + v.y, excl + v.x + v.y + v.z);
+        } else if (i < nblocks) {
+            block_total[i] = excl;
+            if (i + 1 < nblocks) block_total[i + 1] = excl + v.x;
+            if (i + 2 < nblocks) block_total[i + 2] = excl + v.x + v.y;
+        }
         __syncthreads();
-        if (threadIdx.x == 1023) carry = excl + v;
+        if (threadIdx.x == 1023) carry = excl + tot;
         __syncthreads();
     }
     if (threadIdx.x == 0) block_total[nblocks] = carry;
@@ -412,7 +482,7 @@ int recon_mesh_faces(sr_ctx* ctx, const sr_vertex* d_vert, int w, int h, float t
     if (w < 2 || h < 2) return SR_OK;
     unsigned ncells = (unsigned)(w - 1) * (unsigned)(h - 1);
     unsigned nblocks = (ncells + FACE_THREADS - 1) / FACE_THREADS;
-    uint8_t* flags = (uint8_t*)sr_scratch(ctx, 3, (size_t)ncells + ((size_t)nblocks + 1) * 4 + 16);
+    uint8_t* flags = (uint8_t*)sr_scratch(ctx, 3, (size_t)ncells + ((size_t)nblocks + 1) * 4 + 32);
     if (!flags) return SR_E_CUDA;
     uint32_t* block_total = (uint32_t*)(flags + (((size_t)ncells + 15) & ~(size_t)15));
     face_count_kernel<<<nblocks, FACE_THREADS, 0, ctx->stream>>>(d_vert, w, h, thr, ncells, flags, block_total);
@@ -429,20 +499,27 @@ int recon_mesh_faces(sr_ctx* ctx, const sr_vertex* d_vert, int w, int h, float t
 }
 
 // main.cpp:41-50: CV_64F -> 8-bit PNG (rint half-even, saturate) -> float32; or a plain cast.
-__global__ void quantize_kernel(const double* __restrict__ disp, float* __restrict__ out, size_t n, int quantize_u8) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ float quantize1(double v, int quantize_u8) {
+    if (!quantize_u8) return (float)v;
+    long long q = (v != v) ? 0 : __double2ll_rn(fmax(-1e9, fmin(1e9, v)));
+    q = q < 0 ? 0 : (q > 255 ? 255 : q);
+    return (float)q;
+}
+// four pixels per thread: two 16-byte loads in flight, one 16-byte store (vec != 0: both arrays 16-byte aligned)
+__global__ void quantize_kernel(const double* __restrict__ disp, float* __restrict__ out, size_t n, int quantize_u8, int vec) {
+    size_t i = 4 * ((size_t)blockIdx.x * blockDim.x + threadIdx.x);
     if (i >= n) return;
-    double v = disp[i];
-    if (quantize_u8) {
-        long long q = (v != v) ? 0 : __double2ll_rn(fmax(-1e9, fmin(1e9, v)));
-        q = q < 0 ? 0 : (q > 255 ? 255 : q);
-        out[i] = (float)q;
+    if (vec && i + 3 < n) {
+        double2 a = *reinterpret_cast<const double2*>(disp + i), b = *reinterpret_cast<const double2*>(disp + i + 2);
+        *reinterpret_cast<float4*>(out + i) = make_float4(quantize1(a.x, quantize_u8), quantize1(a.y, quantize_u8),
+                                                           quantize1(b.x, quantize_u8), quantize1(b.y, quantize_u8));
     } else {
-        out[i] = (float)v;
+        for (size_t e = min(i + 4, n); i < e; i++) out[i] = quantize1(disp[i], quantize_u8);
     }
 }
 int recon_quantize(sr_ctx* ctx, const double* d_disp, float* d_out, size_t n, int quantize_u8) {
-    quantize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_disp, d_out, n, quantize_u8);
+    const int vec = (((uintptr_t)d_disp | (uintptr_t)d_out) & 15) == 0;
+    quantize_kernel<<<(unsigned)((n + 1023) / 1024), 256, 0, ctx->stream>>>(d_disp, d_out, n, quantize_u8, vec);
     SR_LAUNCHED(ctx);
     return SR_OK;
 }

@@ -271,7 +271,8 @@ def test_ext_ncc_sliding_kernel(sr, ctx, orc, shape):
     assert np.abs(gots - sp).max() <= 1e-3       # north_star tolerance (met exactly)
 
 
-@pytest.mark.parametrize("case", ["u8_integers", "subpixel_narrow", "wide_dynamic_range", "with_inf", "all_zero", "k_larger_than_image"])
+@pytest.mark.parametrize("case", ["u8_integers", "subpixel_narrow", "wide_dynamic_range", "with_inf", "all_zero", "k_larger_than_image",
+                                  "near_exact_limit", "even_width"])
 def test_box_blur_order_free_and_sequential_paths(sr, ctx, orc, case):
     """cv::blur(32F, k x k) of removeDisparityOutliers: the prefix-sum path (taken when every partial sum is
     exactly representable in fp64) and the sequential OpenCV recurrences (any other input) both equal the
@@ -288,9 +289,33 @@ def test_box_blur_order_free_and_sequential_paths(sr, ctx, orc, case):
         d = rng.integers(0, 256, (h, w)).astype(np.float32); d[5, 7] = np.inf; d[40, 100] = -np.inf
     elif case == "all_zero":
         d = np.zeros((h, w), np.float32)
+    elif case == "near_exact_limit":
+        # 46 bits between the largest value and the smallest set bit: window sums (<= 2 k^2 terms) still fit 53 bits,
+        # a column prefix over (h + k - 1) * k terms does not -- the exactness proof has to count the prefix length
+        k = 3
+        d = (rng.integers(1, 1 << 24, (h, w)).astype(np.float64) * 2.0 ** (22 * rng.integers(0, 2, (h, w)))).astype(np.float32)
+    elif case == "even_width":
+        w = 134                                                                          # 16-byte loads of two columns
+        d = rng.integers(0, 256, (h, w)).astype(np.float32)
     else:
         d = rng.integers(0, 64, (h, w)).astype(np.float32); k = 301                    # window wider and taller than the map
     with np.errstate(invalid="ignore", over="ignore"):
         want = orc.box_blur(d, k)
     got = sr.reconstruction.boxBlur(d, k, ctx=ctx)
     assert got.tobytes() == want.tobytes()
+
+
+
+def test_mesh_faces_large_map(sr, ctx, orc):
+    """Face list of a map with more than 4096 scan blocks (several sweeps of the block-total scan, ragged tail)."""
+    R = sr.reconstruction
+    bgr, disp, K = _recon_inputs(orc, 1203, 997)
+    h, w = disp.shape
+    depth = R.convertDisparityToDepth(disp, K[0, 0], 1.0, ctx=ctx)
+    v = R.backproject(bgr, depth, K, ctx=ctx)
+    want_v = orc.backproject(bgr, depth, K[0, 0], K[1, 1], K[0, 2], K[1, 2])
+    assert v.tobytes() == want_v.tobytes()
+    for thr in (2.0, 1e9):
+        np.testing.assert_array_equal(R.meshFaces(v, w, h, thr, ctx=ctx), orc.mesh_faces(want_v, w, h, thr))
+    d = disp.copy(); R.removeDisparityOutliers(d, 75, 1.5, 0.8, ctx=ctx)
+    np.testing.assert_array_equal(d, orc.remove_outliers(disp, 75, 1.5, 0.8))
