@@ -102,20 +102,22 @@ int sr_mesh_faces(sr_ctx* ctx, const sr_vertex* v, int w, int h, float thr, uint
 static int reconstruct_device(sr_ctx* ctx, float* d_disp, const uint8_t* d_bgr, int w, int h, int ksize, float thr_front,
                               float thr_back, float focal, float baseline, float fx, float fy, float cx, float cy,
                               float thr_mesh, float* disp_filtered, float* depth, sr_vertex* vertices, uint32_t* tri,
-                              uint32_t* n_faces) {
+                              uint32_t* n_faces, int disp_is_u8 = 0) {
     size_t n = (size_t)w * h;
     size_t cells = (size_t)(w > 1 ? w - 1 : 0) * (h > 1 ? h - 1 : 0);
     float* d_depth = (float*)sr_scratch(ctx, SL_DEPTH, n * 4);
     sr_vertex* d_v = (sr_vertex*)sr_scratch(ctx, SL_VERT, n * sizeof(sr_vertex));
     uint32_t* d_t = tri ? (uint32_t*)sr_scratch(ctx, SL_TRI, (cells ? cells : 1) * 6 * 4) : nullptr;
     if (!d_depth || !d_v || (tri && !d_t)) return SR_E_CUDA;
-    if (ksize > 0) TRY(recon_remove_outliers(ctx, d_disp, w, h, ksize, thr_front, thr_back));   // main.cpp:53
+    if (ksize > 0) TRY(recon_remove_outliers(ctx, d_disp, w, h, ksize, thr_front, thr_back, disp_is_u8));   // main.cpp:53
     if (disp_filtered) TRY(down2d(ctx, disp_filtered, (size_t)w * 4, d_disp, (size_t)w * 4, (size_t)w * 4, h));
-    TRY(recon_depth_backproject(ctx, d_disp, nullptr, d_bgr, (size_t)w * 3, w, h, focal, baseline, fx, fy, cx, cy, d_depth, d_v));  // main.cpp:56-65
+    // main.cpp:56-65; with a face list wanted, the validity flags come out of the same pass
+    if (n_faces) TRY(recon_depth_backproject_faces(ctx, d_disp, d_bgr, (size_t)w * 3, w, h, focal, baseline, fx, fy, cx, cy, thr_mesh, d_depth, d_v));
+    else TRY(recon_depth_backproject(ctx, d_disp, nullptr, d_bgr, (size_t)w * 3, w, h, focal, baseline, fx, fy, cx, cy, d_depth, d_v));
     if (depth) TRY(down2d(ctx, depth, (size_t)w * 4, d_depth, (size_t)w * 4, (size_t)w * 4, h));
     if (vertices) SR_CUDA(ctx, cudaMemcpyAsync(vertices, d_v, n * sizeof(sr_vertex), cudaMemcpyDeviceToHost, ctx->stream));
     if (n_faces) {
-        TRY(recon_mesh_faces(ctx, d_v, w, h, thr_mesh, d_t, n_faces));
+        TRY(recon_mesh_faces(ctx, (w < 2 || h < 2) ? d_v : nullptr, w, h, thr_mesh, d_t, n_faces));
         if (tri && *n_faces) SR_CUDA(ctx, cudaMemcpyAsync(tri, d_t, (size_t)*n_faces * 12, cudaMemcpyDeviceToHost, ctx->stream));
     }
     return sr_ctx_sync(ctx);
@@ -148,7 +150,7 @@ int sr_pair_reconstruct(sr_ctx* ctx, sr_pair* pair, int quantize_u8, int ksize, 
     if (!d) return SR_E_CUDA;
     TRY(recon_quantize(ctx, pair->out, d, n, quantize_u8));   // main.cpp:41-50 (8-bit hand-off) or plain cast
     return reconstruct_device(ctx, d, pair->rawR, w, h, ksize, thr_front, thr_back, focal, baseline, fx, fy, cx, cy, thr_mesh,
-                              disp_filtered, depth, vertices, tri, n_faces);
+                              disp_filtered, depth, vertices, tri, n_faces, quantize_u8 != 0);
 }
 
 // WriteMesh (reconstruction.cpp:72-149): validity + face order on the GPU, COFF text on the host.

@@ -88,7 +88,17 @@ __global__ void blur_exact_check_kernel(const float* __restrict__ src, size_t n,
         q = min(q, __shfl_xor_sync(0xffffffffu, q, off));
         bad |= __shfl_xor_sync(0xffffffffu, bad, off);
     }
-    if ((threadIdx.x & 31) == 0) { atomicMax(flag, E); atomicMin(flag + 1, q); if (bad) atomicOr(flag + 2, 1); }
+    // one set of atomics per CTA (blockDim.x <= 1024)
+    __shared__ int sE[32], sq[32], sbad[32];
+    const int warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+    if ((threadIdx.x & 31) == 0) { sE[warp] = E; sq[warp] = q; sbad[warp] = bad; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 1; i < nwarp; i++) { E = max(E, sE[i]); q = min(q, sq[i]); bad |= sbad[i]; }
+        if (E > -1000) atomicMax(flag, E);
+        if (q < 1000) atomicMin(flag + 1, q);
+        if (bad) atomicOr(flag + 2, 1);
+    }
 }
 // logn = ceil(log2 N) of the comment above (host: blur_logn)
 __device__ __forceinline__ bool blur_is_exact(const int* flag, int logn) {
@@ -227,7 +237,7 @@ __global__ void blur_cols_seq_kernel(const double* __restrict__ rows, int w, int
     }
 }
 
-int recon_box_blur(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, int k) {
+int recon_box_blur(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, int k, int known_u8) {
     double* rows = (double*)sr_scratch(ctx, 1, (size_t)w * h * sizeof(double));
     if (!rows) return SR_E_CUDA;
     static const char* slow_env = getenv("SR_BLUR_SEQUENTIAL");   // test hook: force the recurrence kernels
@@ -246,12 +256,15 @@ int recon_box_blur(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, 
     if (!buf) return SR_E_CUDA;
     double* pe = (double*)buf; double* seg = pe + (size_t)he * w; int* flag = (int*)(seg + (size_t)BLUR_NSEG * w);
     static const int flag_init[4] = {-1000, 1000, 0, 0};
-    SR_CUDA(ctx, cudaMemcpyAsync(flag, flag_init, sizeof flag_init, cudaMemcpyHostToDevice, ctx->stream));
+    static const int flag_u8[4] = {8, 0, 0, 0};              // integers 0..255: below 2^8, multiples of 2^0
+    SR_CUDA(ctx, cudaMemcpyAsync(flag, known_u8 ? flag_u8 : flag_init, sizeof flag_init, cudaMemcpyHostToDevice, ctx->stream));
     size_t n = (size_t)w * h;
     const int logn = blur_logn(w, h, k);
-    const size_t nvec = ((uintptr_t)d_src & 15) ? 0 : n / 4;
-    blur_exact_check_kernel<<<148 * 8, 256, 0, ctx->stream>>>(d_src, n, nvec, flag);
-    SR_LAUNCHED(ctx);
+    if (!known_u8) {   // the 8-bit hand-off (quantize_kernel's output) needs no look at the data
+        const size_t nvec = ((uintptr_t)d_src & 15) ? 0 : n / 4;
+        blur_exact_check_kernel<<<148 * 8, 256, 0, ctx->stream>>>(d_src, n, nvec, flag);
+        SR_LAUNCHED(ctx);
+    }
     static bool configured = false;
     if (!configured) {
         SR_CUDA(ctx, cudaFuncSetAttribute(blur_rows_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -292,10 +305,10 @@ __global__ void outlier_replace_kernel(float* __restrict__ disp, const float* __
     }
 }
 
-int recon_remove_outliers(sr_ctx* ctx, float* d_disp, int w, int h, int k, float thr_front, float thr_back) {
+int recon_remove_outliers(sr_ctx* ctx, float* d_disp, int w, int h, int k, float thr_front, float thr_back, int known_u8) {
     float* blurred = (float*)sr_scratch(ctx, 2, (size_t)w * h * sizeof(float));
     if (!blurred) return SR_E_CUDA;
-    int rc = recon_box_blur(ctx, d_disp, blurred, w, h, k);
+    int rc = recon_box_blur(ctx, d_disp, blurred, w, h, k, known_u8);
     if (rc != SR_OK) return rc;
     size_t n = (size_t)w * h;
     const int vec = (((uintptr_t)d_disp | (uintptr_t)blurred) & 15) == 0;
@@ -378,23 +391,30 @@ __device__ __forceinline__ bool tri_valid(const float4& a, const float4& b, cons
 }
 
 #define FACE_THREADS 256
+// Positions are read from the Vertex array (one 32-byte sector per vertex, 16 bytes of it used).  Recomputing them
+// from the depth map inside the fused pipeline was measured and dropped: 33 MB instead of 271 MB of DRAM traffic per
+// 4K map, but eight IEEE divisions per cell made the kernel ALU-bound (104 us against 64 us).
+struct PosFromVertices {
+    const sr_vertex* v;
+    __device__ __forceinline__ float4 operator()(unsigned x, unsigned y, int w) const {
+        return *reinterpret_cast<const float4*>(v + (size_t)y * w + x);
+    }
+};
 // flags of cell `cell`: bit0 = upper-left triangle valid, bit1 = lower-right valid
-__device__ __forceinline__ uint32_t cell_flags(const sr_vertex* __restrict__ v, int w, int h, unsigned cell, float thr) {
+template <class Pos>
+__device__ __forceinline__ uint32_t cell_flags(const Pos& pos, int w, unsigned cell, float thr) {
     unsigned cw = (unsigned)(w - 1);
     unsigned y = cell / cw, x = cell - y * cw;
-    const float4 pa = *reinterpret_cast<const float4*>(v + (size_t)y * w + x);
-    const float4 pb = *reinterpret_cast<const float4*>(v + (size_t)(y + 1) * w + x);
-    const float4 pc = *reinterpret_cast<const float4*>(v + (size_t)y * w + x + 1);
-    const float4 pd = *reinterpret_cast<const float4*>(v + (size_t)(y + 1) * w + x + 1);
+    const float4 pa = pos(x, y, w), pb = pos(x, y + 1, w), pc = pos(x + 1, y, w), pd = pos(x + 1, y + 1, w);
     return (tri_valid(pa, pb, pc, thr) ? 1u : 0u) | (tri_valid(pb, pd, pc, thr) ? 2u : 0u);
 }
 
-__global__ void __launch_bounds__(FACE_THREADS) face_count_kernel(const sr_vertex* __restrict__ v, int w, int h, float thr,
-                                                                  unsigned ncells, uint8_t* __restrict__ flags,
-                                                                  uint32_t* __restrict__ block_total) {
+template <class Pos>
+__global__ void __launch_bounds__(FACE_THREADS) face_count_kernel(Pos pos, int w, float thr, unsigned ncells,
+                                                                  uint8_t* __restrict__ flags, uint32_t* __restrict__ block_total) {
     __shared__ uint32_t wsum[FACE_THREADS / 32];
     unsigned cell = blockIdx.x * FACE_THREADS + threadIdx.x;
-    uint32_t f = cell < ncells ? cell_flags(v, w, h, cell, thr) : 0u;
+    uint32_t f = cell < ncells ? cell_flags(pos, w, cell, thr) : 0u;
     if (cell < ncells) flags[cell] = (uint8_t)f;
     uint32_t n = __popc(f);
     for (int o = 16; o; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
@@ -404,6 +424,88 @@ __global__ void __launch_bounds__(FACE_THREADS) face_count_kernel(const sr_verte
         uint32_t t = 0;
         for (int i = 0; i < FACE_THREADS / 32; i++) t += wsum[i];
         block_total[blockIdx.x] = t;
+    }
+}
+
+// ---- fused: disparity -> depth -> vertex -> face validity (main.cpp:56-65 in one pass) --------------------
+// depth_backproject_kernel plus the validity flags of WriteMesh, so that the 32-byte vertices are written once and
+// never read back (face_count_kernel reads 271 MB of them per 4K map).  A CTA owns 127 columns x 16 rows of
+// vertices and marches down its rows: every thread keeps its previous position in registers, the right-hand
+// neighbour's comes through shared memory (double-buffered: one barrier per row); the 128th column and the 17th row
+// are halo (computed, not stored).  The next row's disparity and colour are loaded before the barrier of the current
+// one.  Positions are the values the plain kernel stores (same expressions, no FMA), so the flags equal
+// cell_flags() on the stored vertices.
+#define DBF_T 128
+#define DBF_ROWS 16
+__global__ void __launch_bounds__(DBF_T) depth_backproject_faces_kernel(
+    const float* __restrict__ disp, const uint8_t* __restrict__ bgr, size_t bgr_pitch, int w, int h, float focal,
+    float baseline, float fx, float fy, float cx, float cy, float thr, float* __restrict__ depth_out,
+    sr_vertex* __restrict__ vert, uint8_t* __restrict__ flags) {
+    __shared__ float4 spos[2][DBF_T];
+    const int t = threadIdx.x;
+    const int x = blockIdx.x * (DBF_T - 1) + t;
+    const int y0 = blockIdx.y * DBF_ROWS;
+    const bool incol = x < w;
+    const bool own = incol && t < DBF_T - 1;
+    float dn = 0.f;
+    uint32_t cn = 0;
+    if (incol) {
+        dn = disp[(size_t)y0 * w + x];
+        const uint8_t* p = bgr + (size_t)y0 * bgr_pitch + 3 * (size_t)x;
+        cn = (uint32_t)p[2] | ((uint32_t)p[1] << 8) | ((uint32_t)p[0] << 16) | 0xFF000000u;
+    }
+    float4 prev = make_float4(0.f, 0.f, 0.f, 0.f), prev_right = prev;
+    for (int r = 0; r <= DBF_ROWS; r++) {
+        const int y = y0 + r;
+        if (y >= h) break;                                   // uniform over the CTA
+        const float d = dn;
+        const uint32_t colour = cn;
+        if (incol && r < DBF_ROWS && y + 1 < h) {            // prefetch the next row
+            dn = disp[(size_t)(y + 1) * w + x];
+            const uint8_t* p = bgr + (size_t)(y + 1) * bgr_pitch + 3 * (size_t)x;
+            cn = (uint32_t)p[2] | ((uint32_t)p[1] << 8) | ((uint32_t)p[0] << 16) | 0xFF000000u;
+        }
+        float4 cur = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        if (incol) {
+            const float depth = d == 0.0f ? -INFINITY : focal * baseline / d;
+            uint32_t rgba = 0;
+            if (depth != -INFINITY) {
+                float xc = ((float)x * depth - cx * depth) / fx;
+                float yc = ((float)y * depth - cy * depth) / fy;
+                cur = make_float4(xc, yc, depth, 1.0f);
+                rgba = colour;
+            }
+            if (own && r < DBF_ROWS) {
+                const size_t i = (size_t)y * w + x;
+                depth_out[i] = depth;
+                float4* o = reinterpret_cast<float4*>(vert + i);
+                o[0] = cur;
+                o[1] = make_float4(__uint_as_float(rgba), 0.f, 0.f, 0.f);
+            }
+        }
+        spos[r & 1][t] = cur;
+        __syncthreads();
+        const float4 cur_right = t < DBF_T - 1 ? spos[r & 1][t + 1] : cur;
+        if (r > 0 && own && x < w - 1)                       // cell (x, y - 1): a = prev, b = cur, c = prev_right, d = cur_right
+            flags[(size_t)(y - 1) * (w - 1) + x] =
+                (uint8_t)((tri_valid(prev, cur, prev_right, thr) ? 1u : 0u) | (tri_valid(cur, cur_right, prev_right, thr) ? 2u : 0u));
+        prev = cur;
+        prev_right = cur_right;
+    }
+}
+// per-block face totals from flags that the fused kernel wrote (what face_count_kernel produces beside its flags)
+__global__ void __launch_bounds__(FACE_THREADS) face_blocktotal_kernel(const uint8_t* __restrict__ flags, unsigned ncells,
+                                                                       uint32_t* __restrict__ block_total) {
+    __shared__ uint32_t wsum[FACE_THREADS / 32];
+    unsigned cell = blockIdx.x * FACE_THREADS + threadIdx.x;
+    uint32_t n = cell < ncells ? __popc((uint32_t)flags[cell]) : 0u;
+    for (int o = 16; o; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t tt = 0;
+        for (int i = 0; i < FACE_THREADS / 32; i++) tt += wsum[i];
+        block_total[blockIdx.x] = tt;
     }
 }
 
@@ -454,10 +556,12 @@ __global__ void __launch_bounds__(1024) face_scan_kernel(uint32_t* __restrict__ 
     if (threadIdx.x == 0) block_total[nblocks] = carry;
 }
 
+// The CTA's faces are contiguous in the list: staged in shared memory, then stored with coalesced 4-byte words.
 __global__ void __launch_bounds__(FACE_THREADS) face_scatter_kernel(int w, unsigned ncells, const uint8_t* __restrict__ flags,
                                                                     const uint32_t* __restrict__ block_off,
                                                                     uint32_t* __restrict__ tri) {
     __shared__ uint32_t wsum[FACE_THREADS / 32];
+    __shared__ uint32_t stage[FACE_THREADS * 6];
     unsigned cell = blockIdx.x * FACE_THREADS + threadIdx.x;
     uint32_t f = cell < ncells ? flags[cell] : 0u;
     uint32_t n = __popc(f), inc = n;
@@ -467,25 +571,41 @@ __global__ void __launch_bounds__(FACE_THREADS) face_scatter_kernel(int w, unsig
     }
     if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
     __syncthreads();
-    uint32_t off = block_off[blockIdx.x] + inc - n;
-    for (int i = 0; i < (int)(threadIdx.x >> 5); i++) off += wsum[i];
-    if (!f) return;
-    unsigned cw = (unsigned)(w - 1);
-    unsigned y = cell / cw, x = cell - y * cw;
-    uint32_t a = y * w + x, b = (y + 1) * w + x, c = y * w + x + 1, d = (y + 1) * w + x + 1;
-    if (f & 1u) { tri[3 * (size_t)off] = a; tri[3 * (size_t)off + 1] = b; tri[3 * (size_t)off + 2] = c; off++; }
-    if (f & 2u) { tri[3 * (size_t)off] = b; tri[3 * (size_t)off + 1] = d; tri[3 * (size_t)off + 2] = c; }
+    uint32_t off = inc - n, total = 0;                       // offset inside the CTA, faces of the CTA
+    for (int i = 0; i < FACE_THREADS / 32; i++) {
+        if (i < (int)(threadIdx.x >> 5)) off += wsum[i];
+        total += wsum[i];
+    }
+    if (f) {
+        unsigned cw = (unsigned)(w - 1);
+        unsigned y = cell / cw, x = cell - y * cw;
+        uint32_t a = y * w + x, b = (y + 1) * w + x, c = y * w + x + 1, d = (y + 1) * w + x + 1;
+        uint32_t* st = stage + 3 * off;
+        if (f & 1u) { st[0] = a; st[1] = b; st[2] = c; st += 3; }
+        if (f & 2u) { st[0] = b; st[1] = d; st[2] = c; }
+    }
+    __syncthreads();
+    uint32_t* o = tri + 3 * (size_t)block_off[blockIdx.x];
+    for (unsigned i = threadIdx.x; i < 3 * total; i += FACE_THREADS) o[i] = stage[i];
 }
 
+// flags (one byte per cell) + block totals (+ grand total) in scratch slot 3
+static uint8_t* face_buffers(sr_ctx* ctx, unsigned ncells, unsigned nblocks, uint32_t** block_total) {
+    uint8_t* flags = (uint8_t*)sr_scratch(ctx, 3, (size_t)ncells + ((size_t)nblocks + 1) * 4 + 32);
+    if (flags) *block_total = (uint32_t*)(flags + (((size_t)ncells + 15) & ~(size_t)15));
+    return flags;
+}
+// d_vert != NULL: validity from the vertices; NULL: the flags are already in place (recon_depth_backproject_faces)
 int recon_mesh_faces(sr_ctx* ctx, const sr_vertex* d_vert, int w, int h, float thr, uint32_t* d_tri, uint32_t* n_faces) {
     *n_faces = 0;
     if (w < 2 || h < 2) return SR_OK;
     unsigned ncells = (unsigned)(w - 1) * (unsigned)(h - 1);
     unsigned nblocks = (ncells + FACE_THREADS - 1) / FACE_THREADS;
-    uint8_t* flags = (uint8_t*)sr_scratch(ctx, 3, (size_t)ncells + ((size_t)nblocks + 1) * 4 + 32);
+    uint32_t* block_total = nullptr;
+    uint8_t* flags = face_buffers(ctx, ncells, nblocks, &block_total);
     if (!flags) return SR_E_CUDA;
-    uint32_t* block_total = (uint32_t*)(flags + (((size_t)ncells + 15) & ~(size_t)15));
-    face_count_kernel<<<nblocks, FACE_THREADS, 0, ctx->stream>>>(d_vert, w, h, thr, ncells, flags, block_total);
+    if (d_vert) face_count_kernel<PosFromVertices><<<nblocks, FACE_THREADS, 0, ctx->stream>>>(PosFromVertices{d_vert}, w, thr, ncells, flags, block_total);
+    else face_blocktotal_kernel<<<nblocks, FACE_THREADS, 0, ctx->stream>>>(flags, ncells, block_total);
     SR_LAUNCHED(ctx);
     face_scan_kernel<<<1, 1024, 0, ctx->stream>>>(block_total, nblocks);
     SR_LAUNCHED(ctx);
@@ -495,6 +615,22 @@ int recon_mesh_faces(sr_ctx* ctx, const sr_vertex* d_vert, int w, int h, float t
     }
     SR_CUDA(ctx, cudaMemcpyAsync(n_faces, block_total + nblocks, 4, cudaMemcpyDeviceToHost, ctx->stream));
     SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SR_OK;
+}
+int recon_depth_backproject_faces(sr_ctx* ctx, const float* d_disp, const uint8_t* d_bgr, size_t bgr_pitch, int w, int h,
+                                  float focal, float baseline, float fx, float fy, float cx, float cy, float thr,
+                                  float* d_depth_out, sr_vertex* d_vert) {
+    if (w < 2 || h < 2)
+        return recon_depth_backproject(ctx, d_disp, nullptr, d_bgr, bgr_pitch, w, h, focal, baseline, fx, fy, cx, cy, d_depth_out, d_vert);
+    unsigned ncells = (unsigned)(w - 1) * (unsigned)(h - 1);
+    unsigned nblocks = (ncells + FACE_THREADS - 1) / FACE_THREADS;
+    uint32_t* block_total = nullptr;
+    uint8_t* flags = face_buffers(ctx, ncells, nblocks, &block_total);
+    if (!flags) return SR_E_CUDA;
+    dim3 grid(cdiv(w, DBF_T - 1), cdiv(h, DBF_ROWS));
+    depth_backproject_faces_kernel<<<grid, DBF_T, 0, ctx->stream>>>(d_disp, d_bgr, bgr_pitch, w, h, focal, baseline, fx, fy, cx, cy,
+                                                                    thr, d_depth_out, d_vert, flags);
+    SR_LAUNCHED(ctx);
     return SR_OK;
 }
 

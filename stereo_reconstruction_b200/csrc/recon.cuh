@@ -1,12 +1,19 @@
 // recon.cuh -- device-buffer launchers of the Reconstruction kernels (recon.cu).
 #pragma once
 #include "sr_internal.cuh"
-int recon_box_blur(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, int k);
-int recon_remove_outliers(sr_ctx* ctx, float* d_disp, int w, int h, int k, float thr_front, float thr_back);
+// known_u8 != 0: the caller guarantees integer values 0..255 (the 8-bit hand-off), the exactness check is skipped
+int recon_box_blur(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, int k, int known_u8 = 0);
+int recon_remove_outliers(sr_ctx* ctx, float* d_disp, int w, int h, int k, float thr_front, float thr_back, int known_u8 = 0);
 int recon_scale(sr_ctx* ctx, float* d_disp, size_t n, float f);
 int recon_depth_backproject(sr_ctx* ctx, const float* d_disp, const float* d_depth_in, const uint8_t* d_bgr, size_t bgr_pitch,
                             int w, int h, float focal, float baseline, float fx, float fy, float cx, float cy,
                             float* d_depth_out, sr_vertex* d_vert);
-// face list in the reference's order; d_tri holds up to 6*(w-1)*(h-1) indices; *n_faces on host (synchronises)
+// depth + vertices + the face-validity flags of WriteMesh in one pass (the vertices are not read back); follow with
+// recon_mesh_faces(ctx, NULL, ...) for the face list
+int recon_depth_backproject_faces(sr_ctx* ctx, const float* d_disp, const uint8_t* d_bgr, size_t bgr_pitch, int w, int h,
+                                  float focal, float baseline, float fx, float fy, float cx, float cy, float thr,
+                                  float* d_depth_out, sr_vertex* d_vert);
+// face list in the reference's order; d_tri holds up to 6*(w-1)*(h-1) indices; *n_faces on host (synchronises).
+// d_vert == NULL: the validity flags were left by recon_depth_backproject_faces on the same w x h map.
 int recon_mesh_faces(sr_ctx* ctx, const sr_vertex* d_vert, int w, int h, float thr, uint32_t* d_tri, uint32_t* n_faces);
 int recon_quantize(sr_ctx* ctx, const double* d_disp, float* d_out, size_t n, int quantize_u8);

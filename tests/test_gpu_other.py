@@ -319,3 +319,8 @@ def test_mesh_faces_large_map(sr, ctx, orc):
         np.testing.assert_array_equal(R.meshFaces(v, w, h, thr, ctx=ctx), orc.mesh_faces(want_v, w, h, thr))
     d = disp.copy(); R.removeDisparityOutliers(d, 75, 1.5, 0.8, ctx=ctx)
     np.testing.assert_array_equal(d, orc.remove_outliers(disp, 75, 1.5, 0.8))
+    # the fused pipeline (vertices and validity flags from one pass) on the same map
+    got = R.reconstructFused(bgr, disp, K, K[0, 0], 1.0, kernelSize=0, thrMesh=1e9, ctx=ctx)
+    assert got["vertices"].tobytes() == want_v.tobytes()
+    np.testing.assert_array_equal(got["depth"], depth)
+    np.testing.assert_array_equal(got["faces"], orc.mesh_faces(want_v, w, h, 1e9))

@@ -57,6 +57,8 @@ def algorithmic_bytes(kernel, faces, pack_rows):
         "blur_cols_out_kernel": N * (2 * 8 + 4),             # two prefix rows in, float out
         "outlier_replace_kernel": N * (4 + 4 + 4),           # disp + blurred in, disp out (upper bound: all replaced)
         "depth_backproject_kernel": N * (4 + 3 + 4 + 32),
+        "depth_backproject_faces_kernel": N * (4 + 3 + 4 + 32) + CELLS,   # + one flag byte per cell
+        "face_blocktotal_kernel": CELLS,
         "face_count_kernel": N * 32 + CELLS,                 # every vertex once (L1/L2 serve the other three reads), flags out
         "face_scatter_kernel": CELLS + faces * 12,
     }
