@@ -442,6 +442,7 @@ __global__ void __launch_bounds__(DBF_T) depth_backproject_faces_kernel(
     float baseline, float fx, float fy, float cx, float cy, float thr, float* __restrict__ depth_out,
     sr_vertex* __restrict__ vert, uint8_t* __restrict__ flags) {
     __shared__ float4 spos[2][DBF_T];
+    __shared__ float svert[2][DBF_T];
     const int t = threadIdx.x;
     const int x = blockIdx.x * (DBF_T - 1) + t;
     const int y0 = blockIdx.y * DBF_ROWS;
@@ -455,6 +456,7 @@ __global__ void __launch_bounds__(DBF_T) depth_backproject_faces_kernel(
         cn = (uint32_t)p[2] | ((uint32_t)p[1] << 8) | ((uint32_t)p[0] << 16) | 0xFF000000u;
     }
     float4 prev = make_float4(0.f, 0.f, 0.f, 0.f), prev_right = prev;
+    float top = 0.f;                                         // |pos(x,y-1) - pos(x+1,y-1)|
     for (int r = 0; r <= DBF_ROWS; r++) {
         const int y = y0 + r;
         if (y >= h) break;                                   // uniform over the CTA
@@ -483,30 +485,55 @@ __global__ void __launch_bounds__(DBF_T) depth_backproject_faces_kernel(
                 o[1] = make_float4(__uint_as_float(rgba), 0.f, 0.f, 0.f);
             }
         }
+        // Edge lengths are symmetric bit for bit ((a-b)^2 == (b-a)^2), so each is computed once: the vertical edge
+        // of this column here (the left-hand neighbour reads it as its cell's right side), the horizontal edge of
+        // this row (top side of the cell below, bottom side of the cell above) and the diagonal.
+        const float vert_edge = edge_len(prev, cur);
         spos[r & 1][t] = cur;
+        svert[r & 1][t] = vert_edge;
         __syncthreads();
         const float4 cur_right = t < DBF_T - 1 ? spos[r & 1][t + 1] : cur;
-        if (r > 0 && own && x < w - 1)                       // cell (x, y - 1): a = prev, b = cur, c = prev_right, d = cur_right
-            flags[(size_t)(y - 1) * (w - 1) + x] =
-                (uint8_t)((tri_valid(prev, cur, prev_right, thr) ? 1u : 0u) | (tri_valid(cur, cur_right, prev_right, thr) ? 2u : 0u));
+        const float vert_right = t < DBF_T - 1 ? svert[r & 1][t + 1] : 0.f;
+        const float bottom = edge_len(cur, cur_right);
+        if (r > 0 && own && x < w - 1) {
+            // cell (x, y - 1): a = prev, b = cur, c = prev_right, d = cur_right (reconstruction.cpp:92-113);
+            // triangle (a,b,c): edges ab, ac, bc; triangle (b,d,c): edges bd, bc, dc (:46-69)
+            const float diag = edge_len(cur, prev_right);
+            const bool t1 = !(prev.x == -INFINITY || cur.x == -INFINITY || prev_right.x == -INFINITY) &&
+                            !(vert_edge > thr || top > thr || diag > thr);
+            const bool t2 = !(cur.x == -INFINITY || cur_right.x == -INFINITY || prev_right.x == -INFINITY) &&
+                            !(bottom > thr || diag > thr || vert_right > thr);
+            flags[(size_t)(y - 1) * (w - 1) + x] = (uint8_t)((t1 ? 1u : 0u) | (t2 ? 2u : 0u));
+        }
         prev = cur;
         prev_right = cur_right;
+        top = bottom;
     }
 }
-// per-block face totals from flags that the fused kernel wrote (what face_count_kernel produces beside its flags)
-__global__ void __launch_bounds__(FACE_THREADS) face_blocktotal_kernel(const uint8_t* __restrict__ flags, unsigned ncells,
-                                                                       uint32_t* __restrict__ block_total) {
-    __shared__ uint32_t wsum[FACE_THREADS / 32];
-    unsigned cell = blockIdx.x * FACE_THREADS + threadIdx.x;
-    uint32_t n = cell < ncells ? __popc((uint32_t)flags[cell]) : 0u;
-    for (int o = 16; o; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
-    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = n;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t tt = 0;
-        for (int i = 0; i < FACE_THREADS / 32; i++) tt += wsum[i];
-        block_total[blockIdx.x] = tt;
+// per-block face totals from flags that the fused kernel wrote (what face_count_kernel produces beside its flags):
+// 16 flag bytes per thread (one 16-byte load), 16 consecutive lanes make up one block of FACE_THREADS cells
+__global__ void __launch_bounds__(256) face_blocktotal_kernel(const uint8_t* __restrict__ flags, unsigned ncells, unsigned nblocks,
+                                                              uint32_t* __restrict__ block_total) {
+    static_assert(FACE_THREADS == 256, "16 lanes x 16 cells per block total");
+    const unsigned g = blockIdx.x * 256 + threadIdx.x;      // group of 16 cells
+    const size_t c0 = (size_t)g * 16;
+    uint32_t n = 0;
+    if (c0 < ncells) {
+        uint4 v = *reinterpret_cast<const uint4*>(flags + c0);   // the buffer is padded to a multiple of 16 bytes
+        if (c0 + 16 > ncells) {                                  // ragged tail: only the first ncells - c0 bytes are flags
+            uint32_t wv[4] = {v.x, v.y, v.z, v.w};
+            const int keep = (int)(ncells - c0);
+            for (int i = 0; i < 4; i++) {
+                int kb = keep - 4 * i;
+                wv[i] &= kb >= 4 ? 0xFFFFFFFFu : (kb <= 0 ? 0u : ((1u << (8 * kb)) - 1u));
+            }
+            v = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        }
+        n = __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);   // flag bytes are 0..3: one bit per face
     }
+    for (int o = 8; o; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o, 16);
+    const unsigned blk = g >> 4;
+    if ((threadIdx.x & 15) == 0 && blk < nblocks) block_total[blk] = n;
 }
 
 // single-CTA exclusive scan of the block totals (in place), four per thread and 4096 per sweep (16-byte loads: the
@@ -605,7 +632,7 @@ int recon_mesh_faces(sr_ctx* ctx, const sr_vertex* d_vert, int w, int h, float t
     uint8_t* flags = face_buffers(ctx, ncells, nblocks, &block_total);
     if (!flags) return SR_E_CUDA;
     if (d_vert) face_count_kernel<PosFromVertices><<<nblocks, FACE_THREADS, 0, ctx->stream>>>(PosFromVertices{d_vert}, w, thr, ncells, flags, block_total);
-    else face_blocktotal_kernel<<<nblocks, FACE_THREADS, 0, ctx->stream>>>(flags, ncells, block_total);
+    else face_blocktotal_kernel<<<cdiv((int)nblocks, 16), 256, 0, ctx->stream>>>(flags, ncells, nblocks, block_total);
     SR_LAUNCHED(ctx);
     face_scan_kernel<<<1, 1024, 0, ctx->stream>>>(block_total, nblocks);
     SR_LAUNCHED(ctx);
