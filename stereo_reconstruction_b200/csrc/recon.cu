@@ -118,7 +118,7 @@ static int blur_logn(int w, int h, int k) {
 // One CTA per row: the reflect-101 extended row is staged in shared memory with coalesced loads, turned into
 // inclusive prefix sums there (per-thread chunks of odd length: conflict-free 64-bit accesses, then a scan of
 // the chunk totals), and rowsum[x] = PE[x + k - 1] - PE[x - 1].
-#define BLUR_T 256
+#define BLUR_T 512
 __global__ void __launch_bounds__(BLUR_T) blur_rows_fast_kernel(const float* __restrict__ src, int w, int h, int k, int logn,
                                                                 double* __restrict__ rows, const int* __restrict__ flag) {
     extern __shared__ double pe[];               // w + k - 1 prefix values

@@ -73,6 +73,50 @@ __global__ void resolve_plain_kernel(SearchGeom g, int from_direct, int have_c0,
     out[i] = v;
 }
 
+// The same for the tile kernel's key planes, two pixels per thread (8-byte loads of the packed pixels, the key
+// plane(s) and the u32 d = 0 plane, one 16-byte store): twice the bytes in flight per thread.  Needs an even
+// width and even pitches (checked by the launcher); per pixel the logic is load_rec(from_direct = 0) +
+// resolve_plain_kernel, line for line.
+__global__ void resolve_plain2_kernel(SearchGeom g, int have_c0 /* 0 or 2 */, Planes pl, const uint32_t* __restrict__ c0u,
+                                      const uint32_t* __restrict__ Rp, int pitchR, double* __restrict__ out) {
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const int y = g.row0 + blockIdx.y;
+    if (x >= g.w2 || y >= g.row1) return;
+    const size_t i = (size_t)y * g.w2 + x;
+    const bool yin = y < g.height;
+    const uint2 px2 = yin ? __ldg(reinterpret_cast<const uint2*>(Rp + (size_t)y * pitchR + x)) : make_uint2(0u, 0u);
+    uint32_t bc[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};
+    int bd[2] = {0, 0};
+    for (int p = 0; p < pl.npass; p++) {
+        const uint2 k2 = __ldg(reinterpret_cast<const uint2*>(pl.planes + (size_t)p * pl.stride + i));
+        const uint32_t k[2] = {k2.x, k2.y};
+#pragma unroll
+        for (int e = 0; e < 2; e++)
+            if (k[e] != 0xFFFFFFFFu && (k[e] >> pl.shift) < bc[e]) {
+                bc[e] = k[e] >> pl.shift;
+                bd[e] = pl.dbase + 64 * p + (int)(k[e] & ((1u << pl.shift) - 1u));
+            }
+    }
+    const uint2 c02 = have_c0 == 2 ? __ldg(reinterpret_cast<const uint2*>(c0u + i)) : make_uint2(0u, 0u);
+    const uint32_t px[2] = {px2.x, px2.y}, c0raw[2] = {c02.x, c02.y};
+    double v[2];
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+        const int xe = x + e;
+        const bool skip = !yin || (px[e] & 0xFFFFFFu) == 0;
+        const int l = min(xe, g.half), rr = min(g.w2 - xe - 1, g.half), u = min(y, g.half), dn = min(g.h2 - y - 1, g.half);
+        const int n = (l + rr) * (u + dn);
+        const unsigned long long cr = bc[e] == 0xFFFFFFFFu ? SR_NONE64 : (unsigned long long)bc[e];
+        const unsigned long long c0 = (have_c0 == 2 && !skip && xe + rr < g.w1) ? (unsigned long long)c0raw[e] : SR_NONE64;
+        if (skip) v[e] = 0.0;
+        else if (n == 0) v[e] = (double)(0 - xe);
+        else if (c0 != SR_NONE64 && (cr == SR_NONE64 || c0 <= cr)) v[e] = 0.0;
+        else if (cr != SR_NONE64) v[e] = (double)bd[e];
+        else v[e] = (double)(0 - xe);
+    }
+    *reinterpret_cast<double2*>(out + i) = make_double2(v[0], v[1]);
+}
+
 // Phase A of the smoothing pass: bit planes a0,a1,a2 (ballot words) and the alternative value.
 __global__ void smooth_prepare_kernel(SearchGeom g, int from_direct, int have_c0, double s, Planes best,
                                       const unsigned long long* __restrict__ c0, const unsigned long long* __restrict__ cr,
@@ -268,6 +312,13 @@ int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, dou
     Planes pl{pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase, pair->key_shift};
     dim3 grid(cdiv(g.w2, 128), rows);
     bool plain = smooth == 1.0 || !have_c0;
+    if (plain && !from_direct && have_c0 != 1 && (g.w2 & 1) == 0 && (pl.stride & 1) == 0 && (pair->R.pitch & 1) == 0 &&
+        (((uintptr_t)pl.planes | (uintptr_t)pair->R.px | (uintptr_t)pair->c0) & 7) == 0 && ((uintptr_t)pair->out & 15) == 0) {
+        resolve_plain2_kernel<<<dim3(cdiv(g.w2, 256), rows), 128, 0, ctx->stream>>>(g, have_c0, pl, (const uint32_t*)pair->c0,
+                                                                                   pair->R.px, pair->R.pitch, pair->out);
+        SR_LAUNCHED(ctx);
+        return SR_OK;
+    }
     if (plain) {
         resolve_plain_kernel<<<grid, 128, 0, ctx->stream>>>(g, from_direct, have_c0, pl, pair->c0, pair->cr, pair->dr,
                                                             pair->nwin, pair->R.px, pair->R.pitch, pair->out);

@@ -48,7 +48,8 @@ def hbm_peak():
 def algorithmic_bytes(kernel, faces, pack_rows):
     table = {
         "pack_bgr_kernel": (pack_rows * W if pack_rows else 2 * N) * (3 + 4),   # one launch packs both images
-        "resolve_plain_kernel": N * (4 + 8),                 # merged key plane in, CV_64F out
+        "resolve_plain_kernel": N * (4 + 4 + 8),             # merged key plane + packed pixel in, CV_64F out
+        "resolve_plain2_kernel": N * (4 + 4 + 8),
         "quantize_kernel": N * (8 + 4),                      # CV_64F in, float out
         "blur_exact_check_kernel": N * 4,
         "blur_rows_fast_kernel": N * (4 + 8),                # float in, fp64 row sums out
