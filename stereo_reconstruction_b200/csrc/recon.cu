@@ -265,10 +265,10 @@ int recon_box_blur(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, 
         blur_exact_check_kernel<<<148 * 8, 256, 0, ctx->stream>>>(d_src, n, nvec, flag);
         SR_LAUNCHED(ctx);
     }
-    static bool configured = false;
-    if (!configured) {
+    static DeviceOnce configured;
+    if (configured.need(ctx->device)) {
         SR_CUDA(ctx, cudaFuncSetAttribute(blur_rows_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = true;
+        configured.done(ctx->device);
     }
     blur_rows_fast_kernel<<<h, BLUR_T, smem, ctx->stream>>>(d_src, w, h, k, logn, rows, flag);
     SR_LAUNCHED(ctx);

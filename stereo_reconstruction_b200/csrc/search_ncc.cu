@@ -271,10 +271,10 @@ __global__ void __launch_bounds__(NW * 32, 1) search_ncc_kernel(NccArgs a) {
 template <int H2>
 int launch_ncc(sr_ctx* ctx, const NccArgs& a, int ntx, int nbands) {
     size_t smem = ((size_t)(H2 + PF + 1) * SLOT_U4 + (size_t)NT * TSLOT_U4 + 2 * NW * KEY_U4) * sizeof(uint4);
-    static bool configured = false;
-    if (!configured) {
+    static DeviceOnce configured;
+    if (configured.need(ctx->device)) {
         SR_CUDA(ctx, cudaFuncSetAttribute(search_ncc_kernel<H2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        configured.done(ctx->device);
     }
     SR_CUDA(ctx, cudaEventRecord(ctx->kev0, ctx->stream));
     search_ncc_kernel<H2><<<dim3(ntx, nbands, a.npass), NW * 32, smem, ctx->stream>>>(a);

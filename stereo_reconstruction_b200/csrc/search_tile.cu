@@ -342,10 +342,10 @@ template <int H2, int COST>
 int launch(sr_ctx* ctx, const TileArgs& a, int nwork) {
     constexpr int NW = 16;
     size_t smem = ((size_t)(H2 + PF + 1) * SLOT_U4 + 2 * NW * KEY_U4) * sizeof(uint4);
-    static bool configured = false;
-    if (!configured) {
+    static DeviceOnce configured;
+    if (configured.need(ctx->device)) {
         SR_CUDA(ctx, cudaFuncSetAttribute(search_tile_kernel<H2, COST, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        configured.done(ctx->device);
     }
     SR_CUDA(ctx, cudaEventRecord(ctx->kev0, ctx->stream));
     search_tile_kernel<H2, COST, NW><<<nwork, NW * 32, smem, ctx->stream>>>(a);

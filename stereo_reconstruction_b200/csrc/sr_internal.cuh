@@ -1,5 +1,6 @@
 // sr_internal.cuh -- shared declarations of libsr_b200.so (sm_100a only).
 #pragma once
+#include <atomic>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
@@ -26,6 +27,14 @@ struct TileWork {
 };
 
 struct sr_stage_pool;   // host threads for pageable <-> pinned staging copies (host_stage.cu)
+
+// cudaFuncSetAttribute applies to the current device only: one flag per device for each kernel instantiation that
+// raises its dynamic shared-memory limit (a process may hold contexts on several GPUs; setting twice is harmless).
+struct DeviceOnce {
+    std::atomic<uint64_t> mask{0};
+    bool need(int dev) const { return ((mask.load(std::memory_order_acquire) >> (dev & 63)) & 1ull) == 0; }
+    void done(int dev) { mask.fetch_or(1ull << (dev & 63), std::memory_order_release); }
+};
 
 struct sr_ctx {
     int device = 0;
