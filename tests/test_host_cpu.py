@@ -38,3 +38,22 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert "sr_oracle" not in txt and "import orc" not in txt and "from oracle" not in txt, f
+
+
+def test_recon_roofline_summary_of_committed_launch_list():
+    """tools/recon_roofline.py --summarise on the committed ncu launch list: every HBM-bound kernel of the 4K pipeline is
+    there with its algorithmic bytes and a fraction of the HBM peak (no GPU needed: parsing only)."""
+    import json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "tools", "recon_roofline.py"), "--summarise",
+                          os.path.join(root, "profiles", "r01_launches_recon_4k.csv"), "--peak", "6553"],
+                         check=True, capture_output=True, text=True, env=dict(os.environ, SR_FACES="16026827")).stdout
+    rows = {j["kernel"]: j for j in map(json.loads, out.splitlines())}
+    n = 3840 * 2160
+    assert rows["quantize_kernel"]["algorithmic_bytes"] == n * 12
+    assert rows["depth_backproject_faces_kernel"]["algorithmic_bytes"] == n * 43 + 3839 * 2159
+    for k in ("quantize_kernel", "blur_rows_fast_kernel", "blur_cols_seg_kernel", "blur_cols_prefix_kernel", "blur_cols_out_kernel",
+              "outlier_replace_kernel", "depth_backproject_faces_kernel", "resolve_plain2_kernel", "face_scatter_kernel"):
+        r = rows[k]
+        assert r["us"] > 0 and r["dram_bytes"] > 0 and 0.1 < r["frac_of_hbm_peak"] < 1.5, (k, r)
+        assert abs(r["algorithmic_GBps"] / (r["algorithmic_bytes"] / r["us"] / 1e3) - 1.0) < 1e-3     # us is printed rounded
