@@ -14,6 +14,8 @@ gathered to rank 0 over NCCL ("scaling": "strong").
 Prints ONE JSON line on rank 0.  `value` = effective evaluations (reference semantics: candidates
 before the break rule) of the whole pair / device time per step with inputs resident in HBM;
 `e2e` = the same through the public host-pointer API (pinned host buffers, H2D + D2H inside).
+At N=1 the line also carries `roofline_recon`: the HBM-bound Reconstruction kernels (main.cpp:41-65) on the same
+pair, timed after every other timed region (secondary; SR_BENCH_NO_RECON=1 skips it).
 """
 import argparse
 import json
@@ -161,6 +163,41 @@ def run_reference(args, rank, world):
             "e2e": {"value": val, "unit": "MDE/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def recon_roofline(ctx, pair, w, h, iters=5):
+    """HBM-bound part of the path: main.cpp:41-65 on the search result resident in HBM --
+    8-bit hand-off -> removeDisparityOutliers(500) -> depth -> vertices -> face count (sr_pair_reconstruct, outputs
+    NULL: nothing leaves HBM but n_faces).  CUDA events on the context stream, L2 flushed between iterations.
+    Algorithmic bytes per pixel after SURVEY.md 8d: hand-off 8+4, a6 4+4, a8 4+4, a9 3+4+32, a10 validity 32."""
+    import ctypes as C
+    f, null, nf = C.c_float, C.c_void_p(None), C.c_uint32(0)
+    focal = 3000.0
+
+    def pipeline():
+        ctx.check(ctx._l.sr_pair_reconstruct(ctx.h, pair.h, 1, 500, f(1.5), f(0.8), f(focal), f(1.0), f(focal), f(focal),
+                                             f(w / 2), f(h / 2), f(1.0), null, null, null, null, C.byref(nf)))
+    for _ in range(2):
+        pipeline()
+    ts = []
+    for _ in range(iters):
+        ctx.l2_flush()
+        ctx.timer_start()
+        pipeline()
+        ts.append(ctx.timer_stop())
+    ms = float(np.median(ts))
+    peak, src = 6551.7, "fallback of B200_PROFILING.md"
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+        src = "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:
+        pass
+    alg = w * h * 99
+    return {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+            "frac": alg / (ms * 1e-3) / 1e9 / peak, "ms": ms, "algorithmic_bytes": alg, "algorithmic_bytes_per_pixel": 99,
+            "implementation_bytes_per_pixel": 125, "faces": int(nf.value), "peak_source": src,
+            "what": "sr_pair_reconstruct on the resident search result: u8 hand-off, outliers k=500, depth, vertices, "
+                    "face count (main.cpp:41-65); per-kernel figures in DESIGN.md 4.2c / profiles/r01_recon_4k_hbm.jsonl"}
 
 
 def cpu_baseline(args, L, R, w, h, D, block, cost):
@@ -375,6 +412,12 @@ def main():
         }
         if world > 1:
             line["gathered_map_equals_single_gpu"] = gather_ok
+        if world == 1 and not os.environ.get("SR_BENCH_NO_RECON"):
+            # secondary, after every timed region: the HBM-bound Reconstruction kernels on the same pair
+            try:
+                line["roofline_recon"] = recon_roofline(ctx, pair, w, h)
+            except Exception as e:   # never at the expense of the headline line
+                line["roofline_recon"] = {"error": str(e)}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, L, R, w, h, D, block, cost)
         print(json.dumps(line), flush=True)
