@@ -61,3 +61,64 @@ def test_warp_nearest(orc):
 def test_quantize(orc):
     (name, z), = golden_cases("quantize")
     np.testing.assert_array_equal(orc.quantize_u8(z["vals"]), z["out"])
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_right_fast_equals_literal_on_random_pairs(orc, seed):
+    """The box-sum + OpenMP port that bench.py times as cpu_baseline / --impl reference equals the literal restatement
+    of BlockSearch.cpp:88-179 (itself pinned by the cv2 goldens above) on random pairs: few grey levels (ties: the
+    first minimum must win), black pixels (skipped), unequal image sizes, even / odd blocks, minDisparity, smoothFactor
+    below / at / above 1, row sub-ranges and thread counts."""
+    rng = np.random.default_rng(1000 + seed)
+    h2, w2 = int(rng.integers(9, 30)), int(rng.integers(20, 60))
+    h1, w1 = h2 + int(rng.integers(0, 4)), w2 + int(rng.integers(-6, 10))
+    levels = int(rng.choice([2, 4, 256]))
+    R = (rng.integers(0, levels, (h2, w2, 3)) * (255 // (levels - 1))).astype(np.uint8)
+    L = (rng.integers(0, levels, (h1, w1, 3)) * (255 // (levels - 1))).astype(np.uint8)
+    R[rng.random((h2, w2)) < 0.05] = 0
+    block = int(rng.choice([3, 4, 7, 9, 17]))
+    min_d = int(rng.choice([0, 0, 2]))
+    max_d = min_d + int(rng.integers(1, 24))
+    smooth = float(rng.choice([1.0, 0.9, 1.3]))
+    want = orc.block_search_right(L, R, block, min_d, max_d, smooth)
+    np.testing.assert_array_equal(orc.block_search_right_fast(L, R, block, min_d, max_d, smooth), want)
+    np.testing.assert_array_equal(orc.block_search_right_fast(L, R, block, min_d, max_d, smooth, nthreads=3), want)
+    if smooth == 1.0:                                   # a row range is independent of the rows above it only without the bias
+        r0, r1 = h2 // 3, h2 - 2
+        got = orc.block_search_right_fast(L, R, block, min_d, max_d, smooth, rows=(r0, r1))
+        np.testing.assert_array_equal(got[r0:r1], want[r0:r1])
+
+
+def test_box_blur_oracle_against_numpy_recurrence(orc):
+    """A second, independent restatement of cv::blur's RowSum<float,double> / ColumnSum<double,float> recurrences
+    (reconstruction.cpp:8) in plain Python on a small map with a wide dynamic range, where the order of the additions
+    is visible in the result: the C oracle must follow the same order bit for bit."""
+    rng = np.random.default_rng(5)
+    h, w, k = 13, 17, 5
+    src = (rng.standard_normal((h, w)) * 10.0 ** rng.integers(-6, 7, (h, w))).astype(np.float32)
+    a = k // 2
+
+    def r101(p, n):
+        while p < 0 or p >= n:
+            p = -p if p < 0 else 2 * (n - 1) - p
+        return p
+    rows = np.zeros((h, w), np.float64)
+    for y in range(h):
+        acc = 0.0
+        for i in range(k):
+            acc += float(src[y, r101(i - a, w)])
+        rows[y, 0] = acc
+        for x in range(1, w):
+            acc += float(src[y, r101(x + k - 1 - a, w)]) - float(src[y, r101(x - 1 - a, w)])
+            rows[y, x] = acc
+    want = np.zeros((h, w), np.float32)
+    scale = 1.0 / (float(k) * float(k))
+    for x in range(w):
+        s = 0.0
+        for i in range(k - 1):
+            s += rows[r101(i - a, h), x]
+        for y in range(h):
+            s0 = s + rows[r101(y - a + k - 1, h), x]
+            want[y, x] = np.float32(s0 * scale)
+            s = s0 - rows[r101(y - a, h), x]
+    assert orc.box_blur(src, k).tobytes() == want.tobytes()
