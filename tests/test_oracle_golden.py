@@ -122,3 +122,107 @@ def test_box_blur_oracle_against_numpy_recurrence(orc):
             want[y, x] = np.float32(s0 * scale)
             s = s0 - rows[r101(y - a, h), x]
     assert orc.box_blur(src, k).tobytes() == want.tobytes()
+
+
+def _np_search_right(L, R, block, min_d, max_d, sad):
+    """SURVEY.md 8c in plain numpy: the reference's window geometry, candidate order, break rule and first minimum
+    (BlockSearch.cpp:105-172) on integer SAD / SSD costs, plus the sub-pixel parabola in fp32."""
+    h2, w2, _ = R.shape
+    h1, w1, _ = L.shape
+    half = (block - 1) // 2
+    disp = np.zeros((h2, w2), np.int32)
+    sub = np.zeros((h2, w2), np.float32)
+    f = np.float32
+    for y in range(min(h1, h2)):
+        for x in range(w2):
+            if not R[y, x].any():
+                continue
+            l, r, u, dn = min(x, half), min(w2 - x - 1, half), min(y, half), min(h2 - y - 1, half)
+            b = R[y - u:y + dn, x - l:x + r].astype(np.int64)
+            costs = []
+            for d in range(min_d, max_d):
+                if x + d + r >= w1:
+                    break
+                a = L[y - u:y + dn, x + d - l:x + d + r].astype(np.int64)
+                costs.append(int(np.abs(a - b).sum() if sad else ((a - b) ** 2).sum()))
+            if not costs:
+                continue
+            bi = int(np.argmin(costs))                      # first minimum
+            disp[y, x] = min_d + bi
+            s = f(min_d + bi)
+            if 1 <= bi < len(costs) - 1:
+                cm, c0, cp = f(costs[bi - 1]), f(costs[bi]), f(costs[bi + 1])
+                den = (cm - f(2.0) * c0) + cp
+                if den > 0:
+                    s = s + (cm - cp) / (f(2.0) * den)
+            sub[y, x] = s
+    return disp, sub
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_extension_oracle_against_numpy_and_reference_path(orc, seed):
+    """The extension oracle (SAD / SSD integer costs, sub-pixel; no reference counterpart) against an
+    independent numpy restatement, and its SSD disparities against the reference-pinned Right search with
+    smoothFactor 1 (same geometry, break rule and tie-breaking: the extensions share the pinned machinery)."""
+    rng = np.random.default_rng(2000 + seed)
+    h, w2 = int(rng.integers(8, 14)), int(rng.integers(16, 30))
+    w1 = w2 + int(rng.integers(-3, 6))
+    levels = int(rng.choice([3, 256]))
+    R = (rng.integers(0, levels, (h, w2, 3)) * (255 // (levels - 1))).astype(np.uint8)
+    L = (rng.integers(0, levels, (h, w1, 3)) * (255 // (levels - 1))).astype(np.uint8)
+    R[rng.random((h, w2)) < 0.05] = 0
+    block = int(rng.choice([3, 5, 8, 9]))
+    min_d = int(rng.choice([0, 1]))
+    max_d = min_d + int(rng.integers(2, 12))
+    for cost in (orc.COST_SSD_L2, orc.COST_SAD):
+        d, _, sp = orc.search_ext(L, R, block, min_d, max_d, cost, want_subpix=True)
+        want_d, want_sp = _np_search_right(L, R, block, min_d, max_d, sad=cost == orc.COST_SAD)
+        np.testing.assert_array_equal(d, want_d)
+        assert sp.tobytes() == want_sp.tobytes()
+    ref = orc.block_search_right(L, R, block, min_d, max_d, 1.0)
+    d, _, _ = orc.search_ext(L, R, block, min_d, max_d, orc.COST_SSD_L2)
+    has = ref >= 0                                          # the reference stores -x where no candidate survives
+    np.testing.assert_array_equal(d[has], ref[has].astype(np.int32))
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_extension_oracle_ncc_against_numpy(orc, seed):
+    """NCC extension cost (exact integer moments, then one correctly rounded fp32 operation
+    per step) restated independently in numpy float32; first candidate with the strictly smallest cost wins, flat
+    windows cost +inf."""
+    rng = np.random.default_rng(3000 + seed)
+    h, w2 = int(rng.integers(8, 12)), int(rng.integers(16, 26))
+    w1 = w2 + int(rng.integers(0, 5))
+    levels = int(rng.choice([2, 256]))
+    R = (rng.integers(0, levels, (h, w2, 3)) * (255 // (levels - 1))).astype(np.uint8)
+    L = (rng.integers(0, levels, (h, w1, 3)) * (255 // (levels - 1))).astype(np.uint8)
+    if levels == 2:
+        R[2:6, 3:9] = 255                                   # flat windows: zero variance
+    block, min_d, max_d = int(rng.choice([5, 7])), 0, int(rng.integers(3, 10))
+    half = (block - 1) // 2
+    f = np.float32
+    want = np.zeros((h, w2), np.int32)
+    for y in range(h):
+        for x in range(w2):
+            if not R[y, x].any():
+                continue
+            l, r, u, dn = min(x, half), min(w2 - x - 1, half), min(y, half), min(h - y - 1, half)
+            b = R[y - u:y + dn, x - l:x + r].astype(np.int64)
+            n = b.size
+            best, bi = f(np.inf), -1
+            for k, d in enumerate(range(min_d, max_d)):
+                if x + d + r >= w1:
+                    break
+                a = L[y - u:y + dn, x + d - l:x + d + r].astype(np.int64)
+                sl, sr, sll, srr, slr = int(a.sum()), int(b.sum()), int((a * a).sum()), int((b * b).sum()), int((a * b).sum())
+                num, vl, vr = n * slr - sl * sr, n * sll - sl * sl, n * srr - sr * sr
+                if n == 0 or vl <= 0 or vr <= 0:
+                    c = f(np.inf)
+                else:
+                    rl, rr = f(1.0) / np.sqrt(f(vl)), f(1.0) / np.sqrt(f(vr))
+                    c = -((f(num) * rl) * rr)
+                if c < best:
+                    best, bi = c, k
+            want[y, x] = min_d + bi if bi >= 0 else 0
+    got, _, _ = orc.search_ext(L, R, block, min_d, max_d, orc.COST_NCC)
+    np.testing.assert_array_equal(got, want)
