@@ -226,3 +226,39 @@ def test_extension_oracle_ncc_against_numpy(orc, seed):
             want[y, x] = min_d + bi if bi >= 0 else 0
     got, _, _ = orc.search_ext(L, R, block, min_d, max_d, orc.COST_NCC)
     np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_extension_oracle_left_referenced_and_lr_check_against_numpy(orc, seed):
+    """Left-referenced search ("same geometry mirrored, d >= 0") and the left-right consistency rule
+    (D_R valid iff x + D_R < w1 and |D_L(y, x + D_R) - D_R| <= 1, else 0) restated in numpy."""
+    rng = np.random.default_rng(4000 + seed)
+    h, w = int(rng.integers(8, 12)), int(rng.integers(18, 28))
+    levels = int(rng.choice([3, 256]))
+    R = (rng.integers(1, levels + 1, (h, w, 3)) * (255 // levels)).astype(np.uint8)      # no black pixels
+    L = (rng.integers(1, levels + 1, (h, w, 3)) * (255 // levels)).astype(np.uint8)
+    block, min_d, max_d = int(rng.choice([5, 7])), 0, int(rng.integers(3, 9))
+    half = (block - 1) // 2
+    want_l = np.zeros((h, w), np.int32)
+    for y in range(h):
+        for x in range(w):
+            l, r, u, dn = min(x, half), min(w - x - 1, half), min(y, half), min(h - y - 1, half)
+            a = L[y - u:y + dn, x - l:x + r].astype(np.int64)
+            costs = []
+            for d in range(min_d, max_d):
+                cx = x - d                                   # partner column in the right image
+                if cx - l < 0:
+                    break
+                b = R[y - u:y + dn, cx - l:cx + r].astype(np.int64)
+                costs.append(int(np.abs(a - b).sum()))
+            want_l[y, x] = min_d + int(np.argmin(costs)) if costs else 0
+    dl, _, _ = orc.search_ext(L, R, block, min_d, max_d, orc.COST_SAD, left_ref=True)
+    np.testing.assert_array_equal(dl, want_l)
+    dr, _, _ = orc.search_ext(L, R, block, min_d, max_d, orc.COST_SAD)
+    want = np.zeros_like(dr)
+    for y in range(h):
+        for x in range(w):
+            d = int(dr[y, x])
+            if x + d < w and abs(int(dl[y, x + d]) - d) <= 1:
+                want[y, x] = d
+    np.testing.assert_array_equal(orc.lr_check(dr, dl), want)
