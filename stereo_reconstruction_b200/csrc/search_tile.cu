@@ -38,10 +38,6 @@ constexpr int LPOS = LCH + LCH / 4;
 constexpr int SLOT_U4 = RPOS + LPOS;  // uint4 per ring slot
 constexpr int KEY_U4 = 160;           // uint4 per warp key row (128 chunks padded)
 constexpr int PF = 2;                 // rows prefetched ahead
-#ifndef SR_TILE_FMA_FROM
-#define SR_TILE_FMA_FROM 4             // disparity pairs >= this index slide on the FMA pipe (4 = none)
-#endif
-constexpr int FMA_FROM = SR_TILE_FMA_FROM;
 
 __device__ __forceinline__ int padpos(int c) { return c + (c >> 2); }
 
@@ -74,12 +70,29 @@ __device__ __forceinline__ uint4 lds128(uint32_t saddr) {
     return v;
 }
 
+// col - (pointwise cost): the row leaving the window.  Both integer pipes issue 64 lanes/clk/SM (ALU: VABSDIFF4,
+// IADD3, VIMNMX3; FMA: IDP.4A, IMAD), so the subtraction goes to the FMA pipe, which the rest of the loop leaves
+// idle: SAD = VABSDIFF4 (ALU) + IDP.4A.U8.S8 with the byte multipliers -1 (FMA) instead of VABSDIFF4 + IADD
+// (ALU + ALU); SSD = VABSDIFF4 + IDP.4A + (FSUB ? IMAD by -1 : IADD).  km1 = 0xFFFFFFFF is a kernel argument so that
+// the IMAD is not strength-reduced to an ALU subtract.
+template <int COST, bool FSUB>
+__device__ __forceinline__ uint32_t pcost_sub(uint32_t l, uint32_t r, uint32_t acc, uint32_t km1) {
+    uint32_t ad = __vabsdiffu4(l, r);
+    if (COST == SR_COST_SAD) {
+        int o;
+        asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(o) : "r"(ad), "r"(0xFFFFFFFFu), "r"((int)acc));
+        return (uint32_t)o;
+    }
+    uint32_t sq = __dp4a(ad, ad, 0u);
+    return FSUB ? sq * km1 + acc : acc - sq;
+}
+
 // vertical update of the 64 column sums with one staged image row (ADD: row enters the window).
 // slot: shared address of the ring slot (warp-uniform); rb: this lane's byte offset inside the right
 // segment; lb[i]: byte offsets (lane base + warp-uniform chunk) of the 5 left chunks.
-template <int COST, bool ADD>
+template <int COST, bool ADD, bool FSUB>
 __device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], uint32_t slot, uint32_t lane_b,
-                                                const uint32_t (&uo)[5], uint32_t colmask) {
+                                                const uint32_t (&uo)[5], uint32_t colmask, uint32_t km1) {
     // all nine LDS.128 of the row first (36 registers: the WTA's key / halo registers are dead here), then the
     // 64 pointwise updates: the load latency is paid once per phase instead of once per 16-column group
     uint4 lv[5], rv[4];
@@ -96,7 +109,7 @@ __device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], uint32_
 #pragma unroll
             for (int t = 0; t < DT; t++) {
                 if (ADD) col[4 * k + jj][t] = pcost_add<COST>(l7[jj + t], r4[jj], col[4 * k + jj][t]);
-                else col[4 * k + jj][t] -= pcost_add<COST>(l7[jj + t], r4[jj], 0u);
+                else col[4 * k + jj][t] = pcost_sub<COST, FSUB>(l7[jj + t], r4[jj], col[4 * k + jj][t], km1);
             }
     }
     if (colmask != 0xFFFFu) {
@@ -121,20 +134,28 @@ struct TileArgs {
     int npass;
     int row0, row1;      // output rows (already clipped to min(h1,h2))
     const int4* work;    // work items {tile, first row, end row, pass}, one per CTA, in schedule order
-    uint32_t k64;        // key = S*k64 + d_key as one IMAD (FMA pipe); 64 with one plane per pass, 2^shift when merged
-    int merged;          // 1: one plane for all passes, key = cost << shift | (d - dbase), folded in with RED.MIN
-    uint32_t kp1, km1;   // == 1, == 0xFFFFFFFF (-1): IMAD-based sliding sums
+    uint32_t k64, nk64;  // == 64, == -64: in-kernel key = S*64 + d_local (d_local = candidate index within the pass);
+                         // kernel arguments so that the multiplications stay IMADs on the FMA pipe
+    int merged;          // 1: one plane for all passes: the key reduction rewrites the winner as
+    int shift;           //    cost << shift | (pass*64 + d_local) and folds it in with RED.MIN
+    uint32_t km1;        // == 0xFFFFFFFF (-1): IMAD-based subtract
     int red_mode;        // 1: half of the warps merge the previous row's keys at the end of the iteration
+    uint32_t zmask;      // bit w: warp w slides its window sums on the FMA pipe (window_wta ZMODE)
+    uint32_t fmask;      // bit w: warp w subtracts the leaving row's SSD cost with an IMAD (pcost_sub FSUB)
 };
 
 // horizontal window sums + in-thread WTA for one output row.  Disparities are processed in pairs so
-// that the two keys fold into one 3-input min (VIMNMX3).  The sliding update S += in - out of the
-// second pair runs as two IMADs (FMA pipe: multipliers kp1 = 1, km1 = -1 are kernel arguments so that
-// they are not strength-reduced) to balance the two integer pipes.  MASKED: candidates outside
-// [dlo, dlim(x)) are discarded (tiles that touch the break rule or the range ends).
-template <int H2, bool MASKED>
+// that the two keys fold into one 3-input min (VIMNMX3).  Two instruction mixes, chosen per warp so that the two
+// integer pipes (64 lanes/clk/SM each) fill evenly:
+//   ZMODE = false: S += in - out as one IADD3 (ALU), key = S*64 + d_local as one IMAD (FMA);
+//   ZMODE = true:  the window sum is kept as the key itself, K = 64*S + d_local, and slides with two IMADs
+//                  (K += in*64; K += out*(-64); FMA pipe) -- no ALU instruction but the min.
+// With the leaving-row subtract on the FMA pipe (pcost_sub) a SAD evaluation is 3.5 ALU + 2 FMA instructions
+// without ZMODE and 2.5 + 3 with it; one warp in four without ZMODE balances the pipes at 2.75 each.
+// MASKED: candidates outside [dlo, dlim(x)) are discarded (tiles that touch the break rule or the range ends).
+template <int H2, bool MASKED, bool ZMODE>
 __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32_t (&keys)[XT], uint32_t k64,
-                                           uint32_t kp1, uint32_t km1, uint32_t dl0, int d0, int x0, const TileArgs& a) {
+                                           uint32_t nk64, uint32_t dl0, int d0, int x0, const TileArgs& a) {
     constexpr int HALO = H2 - 1;
 #pragma unroll
     for (int tp = 0; tp < DT; tp += 2) {
@@ -150,9 +171,12 @@ __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32
 #pragma unroll
         for (int i = 0; i < H2; i++) { S0 += w0[i]; S1 += w1[i]; }
         const uint32_t dla = dl0 + tp, dlb = dl0 + tp + 1;
+        if (ZMODE) { S0 = S0 * k64 + dla; S1 = S1 * k64 + dlb; }
 #pragma unroll
         for (int j = 0; j < XT; j++) {
-            uint32_t ka = S0 * k64 + dla, kb = S1 * k64 + dlb;
+            uint32_t ka, kb;
+            if (ZMODE) { ka = S0; kb = S1; }
+            else { ka = S0 * k64 + dla; kb = S1 * k64 + dlb; }
             if (MASKED) {
                 int x = x0 + j;
                 int lim = min(a.dhi, a.w1 - x - min(a.w2 - x - 1, a.half));
@@ -161,9 +185,9 @@ __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32
             }
             keys[j] = min(min(keys[j], ka), kb);
             if (j + 1 < XT) {
-                if (tp >= FMA_FROM) {
-                    S0 = w0[j + H2] * kp1 + S0; S0 = w0[j] * km1 + S0;
-                    S1 = w1[j + H2] * kp1 + S1; S1 = w1[j] * km1 + S1;
+                if (ZMODE) {
+                    S0 = w0[j + H2] * k64 + S0; S0 = w0[j] * nk64 + S0;
+                    S1 = w1[j + H2] * k64 + S1; S1 = w1[j] * nk64 + S1;
                 } else {
                     S0 += w0[j + H2] - w0[j];
                     S1 += w1[j + H2] - w1[j];
@@ -200,11 +224,13 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int yb0 = wk.y, yb1 = wk.z;
     if (yb0 >= yb1) return;
     const int cb = CB + XT * lane;                             // this thread's own columns [cb, cb+16)
-    const uint32_t k64 = a.k64;
+    const uint32_t k64 = a.k64, nk64 = a.nk64, km1 = a.km1;
     const int pass = wk.w;
     const int dcta = a.dbase + pass * (DT * NW);               // first disparity of the pass (multiple of 4)
     const int d0 = dcta + DT * warp;                            // this warp's 4 disparities
-    const uint32_t dkey0 = (uint32_t)(DT * warp + (a.merged ? pass * (DT * NW) : 0));   // candidate index in the key
+    const uint32_t dkey0 = (uint32_t)(DT * warp);               // candidate index within the pass: the key's low 6 bits
+    const bool zmode = (a.zmask >> warp) & 1u;
+    const bool fsub = (a.fmask >> warp) & 1u;
     const bool late_sub = (warp >> 2) & 1;
     const bool red_late = a.red_mode && ((warp >> 3) & 1);   // spreads the LDS burst of the key merge over the iteration
 
@@ -274,6 +300,8 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const uint32_t red_b = keys_base + 4u * (20 * rgrp + (lane & 15));
     uint32_t* pl = a.planes + (a.merged ? (size_t)0 : (size_t)pass * a.plane_stride) + (size_t)yb0 * a.w2 + xq;
     const bool merged = a.merged != 0;
+    const int mshift = a.shift - 6;
+    const uint32_t mpass = (uint32_t)pass * (DT * NW);
     auto reduce_row = [&](uint32_t buf) {
         if (red_on) {
             uint32_t kk[NW];
@@ -284,7 +312,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
             for (int w = 0; w < NW; w++) k = min(k, kk[w]);
             // merged: the key carries the global candidate index, so the first minimum over all passes is one
             // fire-and-forget RED.MIN in L2 (the plane is preset to "none")
-            if (merged) { if (k != 0xFFFFFFFFu) atomicMin(pl, k); }
+            if (merged) { if (k != 0xFFFFFFFFu) atomicMin(pl, ((k & ~63u) << mshift) + (mpass + (k & 63u))); }
             else *pl = k;
         }
         pl += a.w2;
@@ -311,20 +339,25 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
             // Phase staggering: the warps of one scheduler alternate between "subtract now" and
             // "subtract at the start of the next iteration", so that ALU-only phases (pointwise
             // costs) of some warps overlap the FMA-heavy window/WTA phase of the others.
-            if (late_sub && y - 1 >= yb0 && row_ok(y - 1 - h) && colmask != 0)
-                vertical_update<COST, false>(col, smem_base + s_prev, lane_b, uo, colmask);
-            if (row_ok(y + h - 1) && colmask != 0) vertical_update<COST, true>(col, smem_base + s_in, lane_b, uo, colmask);
+            if (late_sub && y - 1 >= yb0 && row_ok(y - 1 - h) && colmask != 0) {
+                if (COST == SR_COST_SSD_L2 && fsub) vertical_update<COST, false, true>(col, smem_base + s_prev, lane_b, uo, colmask, km1);
+                else vertical_update<COST, false, false>(col, smem_base + s_prev, lane_b, uo, colmask, km1);
+            }
+            if (row_ok(y + h - 1) && colmask != 0) vertical_update<COST, true, false>(col, smem_base + s_in, lane_b, uo, colmask, km1);
             if (y >= yb0) {
                 uint32_t keys[XT];
 #pragma unroll
                 for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
-                if (needmask) window_wta<H2, true>(col, keys, k64, a.kp1, a.km1, dkey0, d0, cb + h, a);
-                else window_wta<H2, false>(col, keys, k64, a.kp1, a.km1, dkey0, d0, cb + h, a);
+                if (needmask) window_wta<H2, true, false>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
+                else if (zmode) window_wta<H2, false, true>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
+                else window_wta<H2, false, false>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
 #pragma unroll
                 for (int k = 0; k < 4; k++)
                     sts128(key_st + buf + 16 * k, keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
-                if (!late_sub && y + 1 < yb1 && row_ok(y - h) && colmask != 0)
-                    vertical_update<COST, false>(col, smem_base + s_out, lane_b, uo, colmask);
+                if (!late_sub && y + 1 < yb1 && row_ok(y - h) && colmask != 0) {
+                    if (COST == SR_COST_SSD_L2 && fsub) vertical_update<COST, false, true>(col, smem_base + s_out, lane_b, uo, colmask, km1);
+                    else vertical_update<COST, false, false>(col, smem_base + s_out, lane_b, uo, colmask, km1);
+                }
             }
         } else if (y >= yb0) {
 #pragma unroll
@@ -452,7 +485,12 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     a.w1 = g.w1; a.h1 = g.h1; a.w2 = g.w2; a.h2 = g.h2; a.half = g.half;
     a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
     a.npass = (g.dhi - a.dbase + 63) / 64;
-    a.row0 = g.row0; a.row1 = r1; a.k64 = 64; a.merged = 0; a.kp1 = 1u; a.km1 = 0xFFFFFFFFu;
+    a.row0 = g.row0; a.row1 = r1; a.k64 = 64u; a.nk64 = (uint32_t)-64; a.merged = 0; a.shift = 6; a.km1 = 0xFFFFFFFFu;
+    // per-warp instruction mixes (window_wta, pcost_sub); SR_TILE_ZMASK / SR_TILE_FMASK override for tuning
+    static const char* zm_env = getenv("SR_TILE_ZMASK");
+    static const char* fm_env = getenv("SR_TILE_FMASK");
+    a.zmask = zm_env ? (uint32_t)strtoul(zm_env, nullptr, 0) : (cost == SR_COST_SAD ? 0xEEEEu : 0x0000u);
+    a.fmask = fm_env ? (uint32_t)strtoul(fm_env, nullptr, 0) : 0xEEEEu;
     static const char* rm_env = getenv("SR_TILE_REDMODE");
     a.red_mode = rm_env ? atoi(rm_env) : 1;
     int ntx = (g.w2 + XT - g.half + TILE_OUT - 1) / TILE_OUT;
@@ -472,7 +510,7 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     static const char* mg_env = getenv("SR_TILE_MERGE");    // tuning / test override
     a.merged = a.npass > 1 && ((cmax + 1) << shift) < 0xFFFFFFFFull && !(mg_env && atoi(mg_env) == 0);
     if (!a.merged) shift = 6;
-    a.k64 = 1u << shift;
+    a.shift = shift;
     pair->npass = a.merged ? 1 : a.npass; pair->plane_dbase = a.dbase; pair->key_shift = shift;
     pair->planes = (uint32_t*)sr_scratch(ctx, 0, (size_t)pair->npass * pair->npx_cap * sizeof(uint32_t));
     if (!pair->planes) return SR_E_CUDA;
