@@ -206,6 +206,16 @@ int sr_pair_reconstruct(sr_ctx* ctx, sr_pair* pair, int quantize_u8,
                         int ksize, float thr_front, float thr_back, float focal, float baseline,
                         float fx, float fy, float cx, float cy, float thr_mesh,
                         float* disp_filtered, float* depth, sr_vertex* vertices, uint32_t* tri, uint32_t* n_faces);
+/* The same with the inverse warp of ImageRectifier::computeDisparityMapRight in between (rectification.cpp:82-87 ->
+ * main.cpp:41-65): search result (rectified frame, in HBM) -> cv::warpPerspective(disp, M, Size(dw, dh),
+ * INTER_NEAREST) with M = H_.inv() as the reference passes it -> [u8 hand-off] -> outliers -> depth -> vertices ->
+ * faces, all in HBM.  `color` is the un-rectified right image (dw x dh BGR, main.cpp:61 imageRight) whose pixels
+ * colour the vertices; NULL uses the pair's own right image (then dw x dh must be its size).  disp_warped (optional,
+ * CV_64F dw x dh, tight) receives the warped map, i.e. what computeDisparityMapRight returns. */
+int sr_pair_reconstruct_warp(sr_ctx* ctx, sr_pair* pair, const double M[9], int dw, int dh, const sr_image* color,
+                             int quantize_u8, int ksize, float thr_front, float thr_back, float focal, float baseline,
+                             float fx, float fy, float cx, float cy, float thr_mesh, double* disp_warped,
+                             float* disp_filtered, float* depth, sr_vertex* vertices, uint32_t* tri, uint32_t* n_faces);
 /* WriteMesh(vertices, w, h, filename, thr), reconstruction.cpp:72-149: validity on the GPU,
  * COFF text on the host.  Returns SR_E_IO where the reference returns false. */
 int sr_write_mesh(sr_ctx* ctx, const sr_vertex* v, int w, int h, const char* filename, float thr);
@@ -218,9 +228,22 @@ int sr_warp_nearest_f64(sr_ctx* ctx, const double* src, int sw, int sh, double* 
 typedef struct { int n, bad, invalid; double serr; float bad_pct, invalid_pct, total_bad_pct, avg_err; } sr_eval;
 int sr_evaldisp(sr_ctx* ctx, const float* disp, const float* gt, const uint8_t* mask, int w, int h,
                 float badthresh, float maxdisp, int rounddisp, sr_eval* out);
+/* computeAverageDisparity(disparityMap), utils.cpp:8-20: one float accumulator over the non-infinite pixels in raster
+ * order, divided by their count -- the order of the additions is reproduced, so the result is bit-identical.
+ * valid (optional) receives the count. */
+int sr_average_disparity(sr_ctx* ctx, const float* disp, int w, int h, size_t pitch, float* avg, int* valid);
 /* Middlebury PFM / ASCII PLY writers (host). */
 int sr_write_pfm(const char* path, const float* data, int w, int h);
 int sr_write_ply(const char* path, const sr_vertex* v, int w, int h);
+/* Middlebury PFM reader with the semantics of the SDK call in DataLoader::loadDisparityMatrices
+ * (data_loader.cpp:110-125): rows returned top to bottom, the scale's sign selects the byte order and its magnitude is
+ * not applied, unknown pixels stay +inf.  sr_pfm_info gives the size to allocate. */
+int sr_pfm_info(const char* path, int* w, int* h);
+int sr_read_pfm(const char* path, float* out, int w, int h);
+/* calib.txt: cam0 / cam1 (row-major 3x3) parsed like DataLoader::readCameraMatrices (data_loader.cpp:141-164); the
+ * key=value lines (ndisp is the maxDisparity of BASELINE.json configs 1-2) into `calib` when not NULL. */
+typedef struct { double doffs, baseline, dyavg, dymax; int width, height, ndisp, isint, vmin, vmax; } sr_calib;
+int sr_read_calib(const char* path, float cam0[9], float cam1[9], sr_calib* calib);
 
 /* ---- multi-GPU (config 4) ------------------------------------------------------------------ */
 /* Balanced band of output rows for `rank` of `nranks`.  Ranks run sr_search_run on their band and

@@ -207,6 +207,21 @@ def search_ext(left, right, block, min_disp, max_disp, cost, left_ref=False, wan
     return disp, ci, sp
 
 
+def search_ext_fast(left, right, block, min_disp, max_disp, cost, left_ref=False, want_cost=False, want_subpix=False, nthreads=0):
+    """search_ext for SSD / SAD through sliding box sums + OpenMP: same results, whole pairs in seconds."""
+    L, lp, w1, h1, p1 = _img(left)
+    R, rp, w2, h2, p2 = _img(right)
+    shape = (h1, w1) if left_ref else (h2, w2)
+    disp = np.zeros(shape, np.int32)
+    ci = np.zeros(shape, np.int64) if want_cost else None
+    sp = np.zeros(shape, np.float32) if want_subpix else None
+    _chk(lib().orc_search_ext_fast(lp, w1, h1, p1, rp, w2, h2, p2, int(block), int(min_disp), int(max_disp), int(cost),
+                                   int(bool(left_ref)), disp.ctypes.data_as(C.c_void_p),
+                                   ci.ctypes.data_as(C.c_void_p) if want_cost else None,
+                                   sp.ctypes.data_as(C.c_void_p) if want_subpix else None, int(nthreads)), "search_ext_fast")
+    return disp, ci, sp
+
+
 def lr_check(disp_r, disp_l):
     dr = np.ascontiguousarray(disp_r, np.int32)
     dl = np.ascontiguousarray(disp_l, np.int32)

@@ -78,6 +78,7 @@ int ref_block_search_right_rows(const uint8_t* left, int w1, int h1, size_t pitc
     int nt = nthreads > 0 ? nthreads : ref_max_threads();
     if (nt > row1 - row0) nt = row1 - row0;
     int rc = REF_OK, used = 1;
+    CoutCapture cap;   // "max block size" once per band (BlockSearch.cpp:177)
 #pragma omp parallel num_threads(nt)
     {
 #ifdef _OPENMP

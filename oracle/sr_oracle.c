@@ -484,18 +484,28 @@ static int invert3(const double m[9], double o[9]) {
     o[6] = c2*id; o[7] = (m[1]*m[6] - m[0]*m[7])*id; o[8] = (m[0]*m[4] - m[1]*m[3])*id;
     return 1;
 }
-/* cv::warpPerspective nearest: dst(x,y) = src(round(X/W), round(Y/W)) with [X Y W] = M^-1 [x y 1];
- * OpenCV evaluates in double, W==0 -> 0, saturate_cast<int>(rint), constant border 0.
- * NOTE: OpenCV inverts M with its own cv::invert (LU); inputs here are checked against
- * cv2.warpPerspective in tests/golden. */
+/* cv::warpPerspective nearest (modules/imgproc/src/imgwarp.cpp, WarpPerspectiveInvoker): dst(x,y) =
+ * src(round(X/W), round(Y/W)) with [X Y W] = M^-1 [x y 1] in double, W==0 -> 0, saturate_cast<int> (rint, half to
+ * even), constant border 0.  OpenCV walks the destination in blocks of bw0 x bh0 pixels (bh0 = min(16, dh),
+ * bw0 = min(1024 / bh0, dw), i.e. 64 columns for any map of 16 rows or more) and evaluates a pixel as
+ * ((M0*bx + M1*y + M2) + M0*x1) * (1 / ((M6*bx + M7*y + M8) + M6*x1)) with bx the block's first column and x1 the
+ * offset inside it -- not as M0*x + M1*y + M2.  The two differ in the last bit, which decides the source pixel when
+ * the landing point is k + 0.5 (golden case warp_strong_perspective: one such pixel).  cv::invert of a 3x3 uses the
+ * cofactor formula below (modules/core/src/lapack.cpp), bit for bit.  Checked against cv2.warpPerspective on the
+ * tests/golden warp_* cases. */
 int orc_warp_nearest_f64(const double* src, int sw, int sh, double* dst, int dw, int dh, const double M[9]) {
     double m[9];
     if (!invert3(M, m)) memset(m, 0, sizeof m);
+    int bh0 = dh < 16 ? dh : 16;
+    int bw0 = 1024 / bh0 < dw ? 1024 / bh0 : dw;
     for (int y = 0; y < dh; y++)
         for (int x = 0; x < dw; x++) {
-            double X = m[0]*x + m[1]*y + m[2], Y = m[3]*x + m[4]*y + m[5], W = m[6]*x + m[7]*y + m[8];
+            int bx = x - x % bw0, x1 = x - bx;
+            double X0 = m[0]*bx + m[1]*y + m[2], Y0 = m[3]*bx + m[4]*y + m[5], W0 = m[6]*bx + m[7]*y + m[8];
+            double W = W0 + m[6]*x1;
             W = W != 0 ? 1.0 / W : 0;
-            double fx = fmax(-2147483648.0, fmin(2147483647.0, X * W)), fy = fmax(-2147483648.0, fmin(2147483647.0, Y * W));
+            double fx = fmax(-2147483648.0, fmin(2147483647.0, (X0 + m[0]*x1) * W));
+            double fy = fmax(-2147483648.0, fmin(2147483647.0, (Y0 + m[3]*x1) * W));
             long ix = lrint(fx), iy = lrint(fy);
             dst[(size_t)y * dw + x] = (ix >= 0 && ix < sw && iy >= 0 && iy < sh) ? src[(size_t)iy * sw + ix] : 0.0;
         }
@@ -606,6 +616,110 @@ int orc_search_ext(const uint8_t* left, int w1, int h1, size_t pitch1,
             }
         free(cst); free(csti);
     }
+    return ORC_OK;
+}
+
+/* The same search as orc_search_ext for the integer costs (SSD, SAD), with vertical sliding column sums + prefix sums
+ * per row and OpenMP over row chunks, so that whole MiddEval3 pairs finish in seconds (the literal version above is
+ * O(window) per candidate).  Same definition, candidate order, break rule, first-minimum rule and parabola; held equal
+ * to orc_search_ext on random pairs and real crops by tests/test_oracle_golden.py. */
+int orc_search_ext_fast(const uint8_t* left, int w1, int h1, size_t pitch1,
+                        const uint8_t* right, int w2, int h2, size_t pitch2,
+                        int block, int min_disp, int max_disp, int cost, int left_ref,
+                        int32_t* disp, int64_t* cost_i, float* subpix, int nthreads) {
+    if (!left || !right || !disp || block < 1 || min_disp < 0) return ORC_E_BADARG;
+    if (cost != ORC_COST_SSD_L2 && cost != ORC_COST_SAD) return ORC_E_BADARG;
+    int half = (block - 1) / 2;
+    const uint8_t* ref = left_ref ? left : right; const uint8_t* oth = left_ref ? right : left;
+    int wr = left_ref ? w1 : w2, hr = left_ref ? h1 : h2, wo = left_ref ? w2 : w1, ho = left_ref ? h2 : h1;
+    size_t pr_ = left_ref ? pitch1 : pitch2, po = left_ref ? pitch2 : pitch1;
+    int height = imin(hr, ho);
+    if (!right_rows_fit(ho, hr, half)) return ORC_E_SHAPE;
+    int sgn = left_ref ? -1 : 1;
+    size_t npx = (size_t)wr * hr;
+    const int64_t NONE = -1, INF = INT64_MAX;
+    int64_t* best = (int64_t*)malloc(npx * 8); int64_t* prev = (int64_t*)malloc(npx * 8);
+    int64_t* cm = (int64_t*)malloc(npx * 8); int64_t* cp = (int64_t*)malloc(npx * 8);
+    if (!best || !prev || !cm || !cp) { free(best); free(prev); free(cm); free(cp); return ORC_E_BADARG; }
+    for (size_t i = 0; i < npx; i++) { best[i] = NONE; prev[i] = NONE; cm[i] = NONE; cp[i] = NONE; disp[i] = 0; }
+    const int CH = 16;
+    int nchunks = (height + CH - 1) / CH;
+#ifdef _OPENMP
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#else
+    nthreads = 1;
+#endif
+#pragma omp parallel num_threads(nthreads)
+    {
+        int64_t* col = (int64_t*)malloc(sizeof(int64_t) * (size_t)(wr + 1));
+        int64_t* pre = (int64_t*)malloc(sizeof(int64_t) * (size_t)(wr + 1));
+#pragma omp for schedule(dynamic, 1)
+        for (int ch = 0; ch < nchunks; ch++) {
+            int ya = ch * CH, yb = imin(ya + CH, height);
+            for (int d = min_disp; d < max_disp; d++) {
+                /* reference columns c whose partner c + sgn*d exists; the window never reaches column wr-1 */
+                int clo = left_ref ? d : 0, chi = imin(wr - 1, left_ref ? wo + d : wo - d);
+                if (chi <= clo) { if (left_ref) continue; else break; }
+                for (int y = ya; y < yb; y++) {
+                    int u = imin(y, half), dn = imin(hr - y - 1, half);
+                    int ra = y - u, rb = y + dn;
+                    int rfirst, rlast, sub_a = 0, sub_b = 0;
+                    if (y == ya) { for (int c = clo; c < chi; c++) col[c] = 0; rfirst = ra; rlast = rb; }
+                    else {
+                        int pu = imin(y - 1, half), pdn = imin(hr - y, half);
+                        sub_a = y - 1 - pu; sub_b = ra; rfirst = y - 1 + pdn; rlast = rb;
+                    }
+                    for (int pass = 0; pass < 2; pass++) {
+                        int r0 = pass ? rfirst : sub_a, r1 = pass ? rlast : sub_b;
+                        for (int r = r0; r < r1; r++) {
+                            const uint8_t* pa = px(ref, pr_, r, 0); const uint8_t* pb = px(oth, po, r, sgn * d);
+                            for (int c = clo; c < chi; c++) {
+                                int a = pa[3*c] - pb[3*c], b = pa[3*c+1] - pb[3*c+1], e = pa[3*c+2] - pb[3*c+2];
+                                int64_t v = cost == ORC_COST_SAD ? abs(a) + abs(b) + abs(e) : a*a + b*b + e*e;
+                                col[c] += pass ? v : -v;
+                            }
+                        }
+                    }
+                    pre[clo] = 0;
+                    for (int c = clo; c < chi; c++) pre[c + 1] = pre[c] + col[c];
+                    for (int x = 0; x < wr; x++) {
+                        size_t i = (size_t)y * wr + x;
+                        int l = imin(x, half), r = imin(wr - x - 1, half);
+                        int cx = x + sgn * d;
+                        int64_t c;
+                        if (left_ref) {
+                            if (cx - l < 0) continue;                 /* break: no candidate from here on for this pixel */
+                            c = cx + r > wo ? INF : pre[x + r] - pre[x - l];
+                        } else {
+                            if (cx + r >= wo) break;                  /* monotone in x for a fixed d */
+                            c = pre[x + r] - pre[x - l];
+                        }
+                        if (is_black(px(ref, pr_, y, x))) continue;
+                        /* parabola neighbours: cost right after the current winner */
+                        if (best[i] != NONE && disp[i] == d - 1 && cp[i] == NONE) cp[i] = c;
+                        if (c != INF && (best[i] == NONE || c < best[i])) { best[i] = c; disp[i] = d; cm[i] = prev[i]; cp[i] = NONE; }
+                        prev[i] = c;
+                    }
+                }
+            }
+        }
+        free(col); free(pre);
+    }
+    for (size_t i = 0; i < npx; i++) {
+        int has = best[i] != NONE;
+        if (!has) disp[i] = 0;
+        if (cost_i) cost_i[i] = has ? best[i] : -1;
+        if (subpix) {
+            float dsub = has ? (float)disp[i] : 0.0f;
+            if (has && cm[i] != NONE && cp[i] != NONE && cm[i] != INF && cp[i] != INF) {
+                float a = (float)(double)cm[i], c0 = (float)(double)best[i], b = (float)(double)cp[i];
+                float den = (a - 2.0f * c0) + b;
+                if (den > 0.0f) dsub = dsub + (a - b) / (2.0f * den);
+            }
+            subpix[i] = dsub;
+        }
+    }
+    free(best); free(prev); free(cm); free(cp);
     return ORC_OK;
 }
 

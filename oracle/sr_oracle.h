@@ -119,6 +119,12 @@ int orc_search_ext(const uint8_t* left, int w1, int h1, size_t pitch1,
                    int block, int min_disp, int max_disp, int cost, int left_ref,
                    int32_t* disp, int64_t* cost_i, float* subpix);
 
+/* orc_search_ext for SSD / SAD through sliding box sums + OpenMP (whole MiddEval3 pairs in seconds); same results. */
+int orc_search_ext_fast(const uint8_t* left, int w1, int h1, size_t pitch1,
+                        const uint8_t* right, int w2, int h2, size_t pitch2,
+                        int block, int min_disp, int max_disp, int cost, int left_ref,
+                        int32_t* disp, int64_t* cost_i, float* subpix, int nthreads);
+
 /* LR check: disp_r (h2*w2) invalidated (set to 0) where inconsistent with disp_l (h1*w1). */
 int orc_lr_check(const int32_t* disp_r, int w2, int h2, const int32_t* disp_l, int w1, int h1,
                  int32_t* out);

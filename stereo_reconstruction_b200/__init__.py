@@ -7,4 +7,4 @@ by tests and bench.py; nothing in this package imports the CPU oracle.
 """
 from . import capi  # noqa: F401
 from .window_search import BlockSearch, LinearSearch  # noqa: F401
-from . import reconstruction, sharding, synth  # noqa: F401
+from . import reconstruction, sharding, synth, data_loader  # noqa: F401

@@ -53,7 +53,8 @@ SYMBOLS = [
     "sr_search_effective_evals", "sr_remove_outliers", "sr_box_blur", "sr_scale", "sr_disparity_to_depth",
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
     "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
-    "sr_search_kernel_ms", "sr_int_peak",
+    "sr_search_kernel_ms", "sr_int_peak", "sr_pair_reconstruct_warp", "sr_average_disparity", "sr_pfm_info", "sr_read_pfm",
+    "sr_read_calib",
 ]
 
 _lib = None

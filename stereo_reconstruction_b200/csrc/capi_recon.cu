@@ -153,6 +153,33 @@ int sr_pair_reconstruct(sr_ctx* ctx, sr_pair* pair, int quantize_u8, int ksize, 
                               disp_filtered, depth, vertices, tri, n_faces, quantize_u8 != 0);
 }
 
+int sr_pair_reconstruct_warp(sr_ctx* ctx, sr_pair* pair, const double M[9], int dw, int dh, const sr_image* color, int quantize_u8,
+                             int ksize, float thr_front, float thr_back, float focal, float baseline, float fx, float fy, float cx,
+                             float cy, float thr_mesh, double* disp_warped, float* disp_filtered, float* depth,
+                             sr_vertex* vertices, uint32_t* tri, uint32_t* n_faces) {
+    NEED(ctx, ctx && pair && M && pair->ow > 0 && pair->oh > 0 && dw > 0 && dh > 0, "sr_pair_reconstruct_warp: bad argument / no search result");
+    NEED(ctx, pair->ow == pair->w2 && pair->oh == pair->h2, "sr_pair_reconstruct_warp: needs a right-referenced result");
+    NEED(ctx, color ? (color->bgr && color->w == dw && color->h == dh && color->pitch >= (size_t)dw * 3) : (dw == pair->w2 && dh == pair->h2),
+         "sr_pair_reconstruct_warp: the colour image must have the warped map's size");
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)dw * dh;
+    double* dwarp = (double*)sr_scratch(ctx, SL_B, n * 8);
+    float* d = (float*)sr_scratch(ctx, SL_DISP, n * 4);
+    if (!dwarp || !d) return SR_E_CUDA;
+    const uint8_t* d_bgr = pair->rawR;
+    if (color) {
+        uint8_t* b = (uint8_t*)sr_scratch(ctx, SL_BGR, n * 3);
+        if (!b) return SR_E_CUDA;
+        TRY(up2d(ctx, b, (size_t)dw * 3, color->bgr, color->pitch, (size_t)dw * 3, dh));
+        d_bgr = b;
+    }
+    TRY(sr_launch_warp_nearest(ctx, pair->out, pair->ow, pair->oh, dwarp, dw, dh, M));   // rectification.cpp:82-87
+    if (disp_warped) SR_CUDA(ctx, cudaMemcpyAsync(disp_warped, dwarp, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    TRY(recon_quantize(ctx, dwarp, d, n, quantize_u8));                                   // main.cpp:41-50
+    return reconstruct_device(ctx, d, d_bgr, dw, dh, ksize, thr_front, thr_back, focal, baseline, fx, fy, cx, cy, thr_mesh,
+                              disp_filtered, depth, vertices, tri, n_faces, quantize_u8 != 0);
+}
+
 // WriteMesh (reconstruction.cpp:72-149): validity + face order on the GPU, COFF text on the host.
 int sr_write_mesh(sr_ctx* ctx, const sr_vertex* v, int w, int h, const char* filename, float thr) {
     NEED(ctx, ctx && v && filename && w > 0 && h > 0, "sr_write_mesh: bad argument");

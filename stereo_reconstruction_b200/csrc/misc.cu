@@ -3,19 +3,24 @@
 #include <cmath>
 #include "sr_internal.cuh"
 
-// cv::warpPerspective(src, dst, M, size, INTER_NEAREST), constant-0 border: dst(x,y) =
-// src(rint(X/W), rint(Y/W)) with [X Y W] = M^-1 [x y 1], evaluated in double like OpenCV.
+// cv::warpPerspective(src, dst, M, size, INTER_NEAREST), constant-0 border: dst(x,y) = src(rint(X/W), rint(Y/W)) with
+// [X Y W] = M^-1 [x y 1], evaluated in double in OpenCV's order: the destination is walked in blocks of bw0 columns
+// (64 for maps of 16 rows or more) and a pixel is ((M0*bx + M1*y + M2) + M0*x1) * (1 / ((M6*bx + M7*y + M8) + M6*x1)),
+// bx = first column of the block, x1 = offset inside it (WarpPerspectiveInvoker) -- the last bit matters where the
+// landing point is k + 0.5.
 __global__ void warp_nearest_kernel(const double* __restrict__ src, int sw, int sh, double* __restrict__ dst, int dw, int dh,
-                                    double m0, double m1, double m2, double m3, double m4, double m5, double m6, double m7,
-                                    double m8) {
+                                    int bw0, double m0, double m1, double m2, double m3, double m4, double m5, double m6,
+                                    double m7, double m8) {
     int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
     if (x >= dw) return;
-    double X = __dadd_rn(__dadd_rn(__dmul_rn(m0, x), __dmul_rn(m1, y)), m2);
-    double Y = __dadd_rn(__dadd_rn(__dmul_rn(m3, x), __dmul_rn(m4, y)), m5);
-    double W = __dadd_rn(__dadd_rn(__dmul_rn(m6, x), __dmul_rn(m7, y)), m8);
+    const int bx = x - x % bw0, x1 = x - bx;
+    double X0 = __dadd_rn(__dadd_rn(__dmul_rn(m0, bx), __dmul_rn(m1, y)), m2);
+    double Y0 = __dadd_rn(__dadd_rn(__dmul_rn(m3, bx), __dmul_rn(m4, y)), m5);
+    double W0 = __dadd_rn(__dadd_rn(__dmul_rn(m6, bx), __dmul_rn(m7, y)), m8);
+    double W = __dadd_rn(W0, __dmul_rn(m6, x1));
     W = W != 0 ? __ddiv_rn(1.0, W) : 0;
-    double fx = fmax(-2147483648.0, fmin(2147483647.0, __dmul_rn(X, W)));
-    double fy = fmax(-2147483648.0, fmin(2147483647.0, __dmul_rn(Y, W)));
+    double fx = fmax(-2147483648.0, fmin(2147483647.0, __dmul_rn(__dadd_rn(X0, __dmul_rn(m0, x1)), W)));
+    double fy = fmax(-2147483648.0, fmin(2147483647.0, __dmul_rn(__dadd_rn(Y0, __dmul_rn(m3, x1)), W)));
     long long ix = __double2ll_rn(fx), iy = __double2ll_rn(fy);
     dst[(size_t)y * dw + x] = (ix >= 0 && ix < sw && iy >= 0 && iy < sh) ? src[(size_t)iy * sw + ix] : 0.0;
 }
@@ -61,19 +66,29 @@ __global__ void evaldisp_kernel(const float* __restrict__ disp, const float* __r
     }
 }
 
+// device buffers; M is the matrix PASSED to warpPerspective (inverted here like OpenCV does, cofactor formula of
+// cv::invert for 3x3); asynchronous on the context stream
+int sr_launch_warp_nearest(sr_ctx* ctx, const double* d_src, int sw, int sh, double* d_dst, int dw, int dh, const double M[9]) {
+    double m[9];
+    if (!invert3(M, m)) for (double& v : m) v = 0;
+    const int bh0 = dh < 16 ? dh : 16;
+    const int bw0 = 1024 / bh0 < dw ? 1024 / bh0 : dw;
+    warp_nearest_kernel<<<dim3(cdiv(dw, 128), dh), 128, 0, ctx->stream>>>(d_src, sw, sh, d_dst, dw, dh, bw0, m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], m[8]);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
 extern "C" {
 
 int sr_warp_nearest_f64(sr_ctx* ctx, const double* src, int sw, int sh, double* dst, int dw, int dh, const double M[9]) {
     if (!ctx || !src || !dst || !M || sw <= 0 || sh <= 0 || dw <= 0 || dh <= 0) return sr_fail(ctx, SR_E_BADARG, "sr_warp_nearest_f64: bad argument");
     SR_CUDA(ctx, cudaSetDevice(ctx->device));
-    double m[9];
-    if (!invert3(M, m)) for (double& v : m) v = 0;
     double* ds = (double*)sr_scratch(ctx, 11, (size_t)sw * sh * 8);
     double* dd = (double*)sr_scratch(ctx, 12, (size_t)dw * dh * 8);
     if (!ds || !dd) return SR_E_CUDA;
     SR_CUDA(ctx, cudaMemcpyAsync(ds, src, (size_t)sw * sh * 8, cudaMemcpyHostToDevice, ctx->stream));
-    warp_nearest_kernel<<<dim3(cdiv(dw, 128), dh), 128, 0, ctx->stream>>>(ds, sw, sh, dd, dw, dh, m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], m[8]);
-    SR_LAUNCHED(ctx);
+    int rc = sr_launch_warp_nearest(ctx, ds, sw, sh, dd, dw, dh, M);
+    if (rc != SR_OK) return rc;
     SR_CUDA(ctx, cudaMemcpyAsync(dst, dd, (size_t)dw * dh * 8, cudaMemcpyDeviceToHost, ctx->stream));
     return sr_ctx_sync(ctx);
 }

@@ -165,6 +165,8 @@ int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, dou
                             int have_c0);
 int sr_launch_search_left(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, double smooth);
 int sr_launch_search_linear(sr_ctx* ctx, sr_pair* pair, double smooth);
+// cv::warpPerspective(..., INTER_NEAREST) on device buffers (misc.cu); M as passed to warpPerspective
+int sr_launch_warp_nearest(sr_ctx* ctx, const double* d_src, int sw, int sh, double* d_dst, int dw, int dh, const double M[9]);
 int sr_launch_count_evals(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g);
 // NCC through sliding sums: interior pixels -> per-pass (score, d) planes (search_ncc.cu)
 int sr_launch_search_ncc(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, float** pscore, int** pdisp, void** tab);

@@ -155,6 +155,44 @@ def pairReconstruct(pair, intrinsics, focalLength, baseline=1.0, quantize_u8=Tru
     return {"disp": disp_f, "depth": depth, "vertices": vert, "faces": tri[:nf.value].copy()}
 
 
+def pairReconstructWarp(pair, M, dsize, colorImage, intrinsics, focalLength, baseline=1.0, quantize_u8=True, kernelSize=500,
+                        thrFront=1.5, thrBack=0.8, thrMesh=1.0):
+    """rectification.cpp:82-87 -> main.cpp:41-65 with the disparity map never leaving HBM (sr_pair_reconstruct_warp):
+    search result in the rectified frame -> cv::warpPerspective(disp, M = H_.inv(), dsize, INTER_NEAREST) -> (8-bit
+    hand-off) -> outliers -> depth -> vertices (coloured from colorImage, the un-rectified right image) -> faces.
+    Returns dict(warped, disp, depth, vertices, faces)."""
+    c = pair.ctx
+    dw, dh = dsize
+    fx, fy, cx, cy = _intrinsics(intrinsics)
+    m = np.ascontiguousarray(M, dtype=np.float64).reshape(9)
+    warped = np.empty((dh, dw), np.float64)
+    disp_f = np.empty((dh, dw), np.float32); depth = np.empty((dh, dw), np.float32)
+    vert = np.zeros(dw * dh, dtype=capi.VERTEX_DTYPE)
+    tri = np.zeros((max((dw - 1) * (dh - 1), 1) * 2, 3), np.uint32)
+    nf = C.c_uint32(0)
+    if colorImage is not None:
+        img, si = capi.image(colorImage)
+        col = C.byref(si)
+    else:
+        col = None
+    c.check(c._l.sr_pair_reconstruct_warp(c.h, pair.h, C.c_void_p(m.ctypes.data), int(dw), int(dh), col, int(bool(quantize_u8)),
+                                          int(kernelSize), C.c_float(thrFront), C.c_float(thrBack), C.c_float(focalLength),
+                                          C.c_float(baseline), C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy),
+                                          C.c_float(thrMesh), C.c_void_p(warped.ctypes.data), C.c_void_p(disp_f.ctypes.data),
+                                          C.c_void_p(depth.ctypes.data), C.c_void_p(vert.ctypes.data), C.c_void_p(tri.ctypes.data),
+                                          C.byref(nf)))
+    return {"warped": warped, "disp": disp_f, "depth": depth, "vertices": vert, "faces": tri[:nf.value].copy()}
+
+
+def computeAverageDisparity(disparityMap, *, ctx=None, return_count=False):
+    """utils.cpp:8-20: the float sum of the non-infinite pixels in raster order / their count (bit-identical)."""
+    c = _ctx(ctx)
+    d = np.ascontiguousarray(disparityMap, dtype=np.float32)
+    avg = C.c_float(0); cnt = C.c_int(0)
+    c.check(c._l.sr_average_disparity(c.h, C.c_void_p(d.ctypes.data), d.shape[1], d.shape[0], C.c_size_t(d.strides[0]), C.byref(avg), C.byref(cnt)))
+    return (np.float32(avg.value), cnt.value) if return_count else np.float32(avg.value)
+
+
 def warpPerspectiveNearest(src, M, dsize, *, ctx=None):
     """cv::warpPerspective(src, dst, M, dsize, INTER_NEAREST) on CV_64F (rectification.cpp:82-87)."""
     c = _ctx(ctx)

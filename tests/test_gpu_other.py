@@ -169,10 +169,60 @@ def test_pair_reconstruct_device_resident(sr, ctx, orc):
     np.testing.assert_array_equal(got["faces"], orc.mesh_faces(v, 400, 90, 2.0))
 
 
-def test_warp_and_quantize_golden(sr, ctx, orc):
-    (name, z), = golden_cases("warp")
-    out = sr.reconstruction.warpPerspectiveNearest(z["src"], z["M"], (int(z["dw"]), int(z["dh"])), ctx=ctx)
-    np.testing.assert_array_equal(out, z["out"])
+@pytest.mark.parametrize("name,z", golden_cases("warp"), ids=lambda v: v if isinstance(v, str) else "")
+def test_warp_golden(sr, ctx, orc, name, z):
+    """cv2.warpPerspective(INTER_NEAREST) goldens incl. half-pixel landings, strong perspective, (near-)singular M."""
+    out = sr.reconstruction.warpPerspectiveNearest(np.asarray(z["src"], np.float64), z["M"], (int(z["dw"]), int(z["dh"])), ctx=ctx)
+    np.testing.assert_array_equal(out, np.asarray(z["out"], np.float64))
+
+
+def test_average_disparity(sr, ctx, orc):
+    """computeAverageDisparity (utils.cpp:8-20): one float accumulator in raster order -- bit-identical, not 'close'."""
+    rng = np.random.default_rng(11)
+    for shape in ((37, 53), (750, 900), (1, 1)):
+        d = (rng.random(shape) * 200).astype(np.float32)
+        d[rng.random(shape) < 0.1] = np.inf
+        d[rng.random(shape) < 0.02] = -np.inf
+        got, cnt = sr.reconstruction.computeAverageDisparity(d, ctx=ctx, return_count=True)
+        want = np.float32(orc.average_disparity(d))
+        assert cnt == int(np.isfinite(d).sum())
+        assert got.tobytes() == want.tobytes(), (got, want)
+
+
+def test_pipeline_with_inverse_warp(sr, ctx, orc):
+    """rectification.cpp:78-88 -> main.cpp:41-65 without the disparity map leaving HBM (sr_pair_reconstruct_warp):
+    search on the rectified pair -> warpPerspective(H_.inv(), INTER_NEAREST) into the original right image's frame ->
+    8-bit hand-off -> removeDisparityOutliers -> depth -> vertices (coloured from the un-rectified image) -> faces."""
+    capi = sr.capi
+    w, h, D = 420, 300, 40
+    L, R = orc.synth_pair(0xB200, 3, w, h, 0, D)
+    dw, dh = 400, 310
+    color = np.random.default_rng(5).integers(0, 256, (dh, dw, 3), dtype=np.uint8)
+    Hinv = np.array([[1.0021, 0.0153, -6.7], [-0.0112, 0.9987, 4.3], [1.3e-5, -2.1e-6, 1.0]])
+    pair = capi.Pair(ctx, w, h, w, h)
+    pair.upload(L, R)
+    p = capi.search_params(block=17, min_disp=0, max_disp=D, smooth=0.9)
+    pair.run(p)
+    K = np.array([[1733.74, 0, 792.27], [0, 1733.68, 541.89], [0, 0, 1]], np.float32)
+    got = sr.reconstruction.pairReconstructWarp(pair, Hinv, (dw, dh), color, K, float(K[0, 0]), 1.0, quantize_u8=True, kernelSize=50)
+    disp = orc.block_search_right_fast(L, R, 17, 0, D, 0.9)
+    warped = orc.warp_nearest_f64(disp, Hinv, (dw, dh))
+    np.testing.assert_array_equal(got["warped"], warped)
+    d8 = orc.quantize_u8(warped)
+    filt = orc.remove_outliers(d8, 50, 1.5, 0.8)
+    np.testing.assert_array_equal(got["disp"], filt)
+    depth = orc.disparity_to_depth(filt, float(K[0, 0]), 1.0)
+    np.testing.assert_array_equal(got["depth"], depth)
+    verts = orc.backproject(color, depth, float(K[0, 0]), float(K[1, 1]), float(K[0, 2]), float(K[1, 2]))
+    assert got["vertices"].tobytes() == verts.tobytes()
+    np.testing.assert_array_equal(got["faces"], orc.mesh_faces(verts, dw, dh, 1.0))
+    # colour image omitted: the warped map must have the pair's size and takes the pair's right image
+    got2 = sr.reconstruction.pairReconstructWarp(pair, np.eye(3), (w, h), None, K, float(K[0, 0]), 1.0, quantize_u8=True, kernelSize=50)
+    same = sr.reconstruction.pairReconstruct(pair, K, float(K[0, 0]), 1.0, quantize_u8=True, kernelSize=50)
+    for k in ("disp", "depth", "faces"):
+        np.testing.assert_array_equal(got2[k], same[k])
+    assert got2["vertices"].tobytes() == same["vertices"].tobytes()
+    pair.close()
 
 
 def test_evaldisp(sr, ctx, orc):

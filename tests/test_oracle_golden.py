@@ -52,10 +52,41 @@ def test_outliers_full(orc):
     assert int((d != disp).sum()) == int(z["changed"])
 
 
-def test_warp_nearest(orc):
-    (name, z), = golden_cases("warp")
-    out = orc.warp_nearest_f64(z["src"], z["M"], (int(z["dw"]), int(z["dh"])))
-    np.testing.assert_array_equal(out, z["out"])
+@pytest.mark.parametrize("name,z", golden_cases("warp"), ids=lambda v: v if isinstance(v, str) else "")
+def test_warp_nearest(orc, name, z):
+    """cv2.warpPerspective(INTER_NEAREST) goldens (rectification.cpp:82-87): half-pixel landings, strong perspective,
+    (near-)singular matrices, maps narrower / lower than OpenCV's 64 x 16 evaluation block."""
+    out = orc.warp_nearest_f64(np.asarray(z["src"], np.float64), z["M"], (int(z["dw"]), int(z["dh"])))
+    np.testing.assert_array_equal(out, np.asarray(z["out"], np.float64))
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_search_ext_fast_equals_literal(orc, seed):
+    """The box-sum version of the extension search (used as the oracle on whole MiddEval3 pairs) equals the literal
+    O(window) definition: both directions, SSD / SAD, winner, winner cost and parabola, ties, black pixels, unequal
+    widths, minDisparity, thread counts."""
+    rng = np.random.default_rng(7000 + seed)
+    h2, w2 = int(rng.integers(6, 22)), int(rng.integers(12, 50))
+    h1, w1 = h2 + int(rng.integers(0, 3)), w2 + int(rng.integers(-6, 8))
+    lv = int(rng.choice([2, 4, 256]))
+    R = (rng.integers(0, lv, (h2, w2, 3)) * (255 // (lv - 1))).astype(np.uint8)
+    L = (rng.integers(0, lv, (h1, w1, 3)) * (255 // (lv - 1))).astype(np.uint8)
+    R[rng.random((h2, w2)) < 0.05] = 0
+    L[rng.random((h1, w1)) < 0.05] = 0
+    block = int(rng.choice([3, 4, 7, 9, 17]))
+    mn = int(rng.choice([0, 0, 2]))
+    mx = mn + int(rng.integers(1, 24))
+    for cost in (orc.COST_SSD_L2, orc.COST_SAD):
+        for lr in (False, True):
+            try:
+                want = orc.search_ext(L, R, block, mn, mx, cost, lr, True, True)
+            except orc.OracleError:
+                with pytest.raises(orc.OracleError):
+                    orc.search_ext_fast(L, R, block, mn, mx, cost, lr, True, True)
+                continue
+            got = orc.search_ext_fast(L, R, block, mn, mx, cost, lr, True, True, nthreads=1 + seed % 3)
+            for a, b in zip(got, want):
+                np.testing.assert_array_equal(a, b)
 
 
 def test_quantize(orc):
