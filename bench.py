@@ -42,7 +42,32 @@ WORKLOADS = {
 OPS_PER_EVAL = {"ssd": 8, "sad": 7}
 # dram__bytes_read.sum + dram__bytes_write.sum of the search kernel from the committed ncu capture
 # (profiles/), per launch, keyed by workload; None = not captured for this workload
-NCU_TRAFFIC = {"4k512": 105726720 + 14286080}   # profiles/r01_tile_sad_4k512_ncu_full.csv (read + write bytes)
+NCU_TRAFFIC = {"4k512": 106000128 + 14022400}   # profiles/r02_tile_sad_4k512_ncu_full.csv (read + write bytes, N=1 launch)
+
+
+def host_threads():
+    """All host threads this process may use.  torch.distributed.run exports OMP_NUM_THREADS=1 when it starts more than
+    one rank: the CPU arms pass an explicit thread count to the oracle instead of inheriting that."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def config_for(args, world):
+    """`config` of the JSON line -- identical in both arms (--impl b200 / reference) for the same flags."""
+    if args.workload == "batch720":
+        return {"workload": f"batch720: {args.batch_pairs} synthetic 1280x720 pairs per rank and step, 128 disparities, 7x7 SAD + "
+                            "sub-pixel (BASELINE.json configs[4]; the config names 1024 pairs in total)",
+                "sharding": "by pair, p mod N, no collective", "evals": "effective (reference break rule)"}
+    w, h, D, block, cost = WORKLOADS[args.workload]
+    cost = args.cost or cost
+    block = args.block or block
+    return {"workload": f"{args.workload}: synthetic {w}x{h} rectified pair, {D} disparities, {block}x{block} {cost.upper()}, "
+                        "smooth 1.0 (BASELINE.json configs)",
+            "sharding": "single GPU" if world == 1 else "row bands with halo rows, bands gathered to rank 0",
+            "l2": "384 MB written between timed iterations", "evals": "effective (reference break rule)",
+            "nominal_MDE": w * h * D / 1e6}
 
 
 def parse():
@@ -114,52 +139,108 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def _oracle_sample(orc, L, R, block, D, ocost, mid, rows):
+def _oracle_sample(orc, L, R, block, D, ocost, mid, rows, nthreads):
     """Runs the CPU port on `rows` output rows starting at `mid`, on a crop that carries the
     window halo (so the port's per-call setup is proportional to the sample, not the image)."""
     pad = block
     y0 = max(mid - pad, 0)
     y1 = min(mid + rows + pad, L.shape[0])
     t0 = time.perf_counter()
-    orc.block_search_right_fast(L[y0:y1], R[y0:y1], block, 0, D, 1.0, cost=ocost, rows=(mid - y0, mid - y0 + rows))
+    orc.block_search_right_fast(L[y0:y1], R[y0:y1], block, 0, D, 1.0, cost=ocost, rows=(mid - y0, mid - y0 + rows), nthreads=nthreads)
     return time.perf_counter() - t0
 
 
+def _ref_sample(ref, L, R, block, D, mid, rows, nthreads):
+    """The reference's own BlockSearch.cpp (oracle/_ref, compiled unchanged) on `rows` output rows: the rows are cut into
+    one band per thread, each band is a BlockSearch of its own on a crop with halo rows.  -> (seconds, threads used)"""
+    pad = block
+    y0 = max(mid - pad, 0)
+    y1 = min(mid + rows + pad, L.shape[0])
+    t0 = time.perf_counter()
+    _, used = ref.block_search_right_rows(L[y0:y1], R[y0:y1], block, 0, D, (mid - y0, mid - y0 + rows), nthreads)
+    return time.perf_counter() - t0, used
+
+
+def _ref_available():
+    try:
+        from oracle import ref
+        if ref.available():
+            ref.lib()
+            return ref
+    except Exception as e:   # a missing .so on a box without the reference tree: fall back to the port, say so
+        print(f"[bench] oracle/_ref unavailable ({e}); timing the oracle port", file=sys.stderr, flush=True)
+    return None
+
+
+def port_baseline(orc, L, R, w, h, D, block, cost, seconds, nthreads):
+    """Optimised CPU port (box sums + OpenMP, bit-identical to the reference) on a bounded row sample."""
+    from stereo_reconstruction_b200 import synth
+    ocost = orc.COST_SAD if cost == "sad" else orc.COST_SSD_L2
+    mid = block
+    unit = 16 * nthreads                                          # the port parallelises over 16-row chunks
+    cal = min(unit, h - 2 * block)
+    _oracle_sample(orc, L, R, block, D, ocost, mid, 2, nthreads)
+    per_row = _oracle_sample(orc, L, R, block, D, ocost, mid, cal, nthreads) / cal
+    rows = int(seconds / max(per_row, 1e-6))
+    rows = max(min(cal, h - 2 * block), min(h - 2 * block, (rows // unit) * unit))
+    sec = _oracle_sample(orc, L, R, block, D, ocost, mid, rows, nthreads)
+    ev = synth.effective_evals(w, w, rows, block, 0, D)
+    return {"value": ev / sec / 1e6, "unit": "MDE/s", "cores": nthreads, "kind": "port",
+            "sample": f"rows {mid}..{mid + rows} of the same pair ({rows}/{h} rows, {sec:.2f} s), {cost.upper()} {block}x{block}: box-sum + "
+                      f"OpenMP port of BlockSearch::computeDisparityMapRight (bit-identical to the reference), {nthreads} threads"}
+
+
 def run_reference(args, rank, world):
-    """The reference's own CPU algorithm for the path (oracle/: box-sum + OpenMP restatement of
-    BlockSearch::computeDisparityMapRight, bit-identical to the literal loop) on all host cores.
-    The reference binary itself cannot be built here (OpenCV C++/Eigen/Ceres absent), see DESIGN.md."""
+    """The reference's own CPU implementation of the path on the box's host cores: oracle/_ref = the reference's
+    BlockSearch.cpp compiled UNCHANGED (header stand-ins for OpenCV/Eigen, oracle/Makefile), one BlockSearch per row band,
+    bands on all host threads (the reference itself has no threads).  Its only cost is SSD-L2 (BlockSearch.cpp:156-158),
+    so that is what is timed, on the workload's shape, window and disparity range.  Falls back to the oracle port when the
+    prebuilt library is missing.  Rank 0 only; the other ranks exit without work."""
     if rank != 0:
         return
+    nthreads = host_threads()
+    os.environ["OMP_NUM_THREADS"] = str(nthreads)                 # before the OpenMP runtimes load (torchrun exports 1)
     from oracle import orc
     from stereo_reconstruction_b200 import synth
-    w, h, D, block, cost = WORKLOADS[args.workload]
+    w, h, D, block, cost = WORKLOADS["720p128" if args.workload == "batch720" else args.workload]
     cost = args.cost or cost
     block = args.block or block
     L, R = orc.synth_pair(0xB200, 0, w, h, 0, D)
-    ocost = orc.COST_SAD if cost == "sad" else orc.COST_SSD_L2
-    cores = os.cpu_count() or 1
     mid = block
-    unit = 16 * cores                                            # the port parallelises over 16-row chunks
-    cal = min(unit, h - 2 * block)
-    _oracle_sample(orc, L, R, block, D, ocost, mid, 2)
-    per_row = _oracle_sample(orc, L, R, block, D, ocost, mid, cal) / cal
-    budget = 150.0 / max(args.steps + args.warmup, 1)            # whole run within a few minutes
-    rows = int(min(3.0, budget) / max(per_row, 1e-6))
-    rows = max(min(cal, h - 2 * block), min(h - 2 * block, (rows // unit) * unit))
-    for _ in range(args.warmup):
-        _oracle_sample(orc, L, R, block, D, ocost, mid, rows)
-    ts = [_oracle_sample(orc, L, R, block, D, ocost, mid, rows) for _ in range(args.steps)]
+    budget = min(3.0, 150.0 / max(args.steps + args.warmup, 1))   # seconds per step: the whole run ends within a few minutes
+    ref = _ref_available()
+    if ref is not None:
+        sec1, used = _ref_sample(ref, L, R, block, D, mid, nthreads, nthreads)          # one row per thread
+        rows = max(nthreads, min(h - 2 * block, int(budget / max(sec1, 1e-6)) * nthreads))
+        for _ in range(args.warmup):
+            _ref_sample(ref, L, R, block, D, mid, rows, nthreads)
+        ts = [_ref_sample(ref, L, R, block, D, mid, rows, nthreads)[0] for _ in range(args.steps)]
+        kind, what = "reference", (f"oracle/_ref (the reference's BlockSearch.cpp compiled unchanged), SSD-L2 {block}x{block} "
+                                   f"(the reference's only cost), one BlockSearch per row band on {used} threads")
+    else:
+        ocost = orc.COST_SAD if cost == "sad" else orc.COST_SSD_L2
+        unit = 16 * nthreads
+        cal = min(unit, h - 2 * block)
+        _oracle_sample(orc, L, R, block, D, ocost, mid, 2, nthreads)
+        per_row = _oracle_sample(orc, L, R, block, D, ocost, mid, cal, nthreads) / cal
+        rows = int(budget / max(per_row, 1e-6))
+        rows = max(min(cal, h - 2 * block), min(h - 2 * block, (rows // unit) * unit))
+        for _ in range(args.warmup):
+            _oracle_sample(orc, L, R, block, D, ocost, mid, rows, nthreads)
+        ts = [_oracle_sample(orc, L, R, block, D, ocost, mid, rows, nthreads) for _ in range(args.steps)]
+        used, kind = nthreads, "port"
+        what = f"box-sum + OpenMP port of BlockSearch::computeDisparityMapRight, {cost.upper()} {block}x{block}, {nthreads} threads"
     ev = synth.effective_evals(w, w, rows, block, 0, D)
     sec = float(np.mean(ts))
     val = ev / sec / 1e6
-    sample = f"{rows} of {h} rows of the {w}x{h} pair per step (rows {mid}..{mid + rows}), {cost.upper()} {block}x{block}, D={D}"
+    sample = f"{rows} of {h} rows of the {w}x{h} pair per step (rows {mid}..{mid + rows}), D={D}; {what}"
+    cpu = {"value": val, "unit": "MDE/s", "cores": used, "kind": kind, "sample": sample}
+    if kind == "reference":   # the optimised port beside it (the number round 1 reported as the reference arm)
+        cpu["port"] = port_baseline(orc, L, R, w, h, D, block, cost, min(4.0, budget * 2), nthreads)
     line = {"impl": "reference", "metric": "disparity_evals_per_s", "value": val, "unit": "MDE/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: synthetic {w}x{h} pair, {D} disparities, {block}x{block} {cost.upper()}",
-                       "sample": sample},
-            "cpu_baseline": {"value": val, "unit": "MDE/s", "cores": cores, "kind": "port", "sample": sample},
+            "scaling": "weak" if args.workload == "batch720" else "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
+            "config": config_for(args, world), "cpu_baseline": cpu,
             "e2e": {"value": val, "unit": "MDE/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -201,25 +282,32 @@ def recon_roofline(ctx, pair, w, h, iters=5):
 
 
 def cpu_baseline(args, L, R, w, h, D, block, cost):
+    """The CPU reference beside the GPU number, on rank 0 at N=1, bounded to about --cpu-seconds of CPU work in total:
+    (reference) oracle/_ref = the reference's own code on all host threads, SSD-L2; (literal_1_thread) the same on one
+    thread, as the reference actually runs; (port) the optimised box-sum port with the workload's cost."""
     from oracle import orc
     from stereo_reconstruction_b200 import synth
-    ocost = orc.COST_SAD if cost == "sad" else orc.COST_SSD_L2
+    nthreads = host_threads()
     mid = block
-    unit = 16 * (os.cpu_count() or 1)                            # the port parallelises over 16-row chunks
-    cal = min(unit, h - 2 * block)
-    _oracle_sample(orc, L, R, block, D, ocost, mid, 2)
-    per_row = _oracle_sample(orc, L, R, block, D, ocost, mid, cal) / cal
-    rows = int(args.cpu_seconds / max(per_row, 1e-6))
-    rows = max(min(cal, h - 2 * block), min(h - 2 * block, (rows // unit) * unit))
-    sec = _oracle_sample(orc, L, R, block, D, ocost, mid, rows)
-    reps = 1
-    while sec * reps < 0.8 * args.cpu_seconds and reps < 64:      # small workloads: repeat the sample
-        sec = (sec * reps + _oracle_sample(orc, L, R, block, D, ocost, mid, rows)) / (reps + 1)
-        reps += 1
-    ev = synth.effective_evals(w, w, rows, block, 0, D)
-    return {"value": ev / sec / 1e6, "unit": "MDE/s", "cores": os.cpu_count() or 1, "kind": "port",
-            "sample": f"rows {mid}..{mid + rows} of the same pair ({rows}/{h} rows, {reps} x {sec:.2f} s), box-sum + OpenMP port of "
-                      f"BlockSearch::computeDisparityMapRight, all host threads"}
+    out = None
+    ref = _ref_available()
+    if ref is not None:
+        sec1, used = _ref_sample(ref, L, R, block, D, mid, nthreads, nthreads)
+        rows = max(nthreads, min(h - 2 * block, int(0.4 * args.cpu_seconds / max(sec1, 1e-6)) * nthreads))
+        sec, used = _ref_sample(ref, L, R, block, D, mid, rows, nthreads)
+        ev = synth.effective_evals(w, w, rows, block, 0, D)
+        out = {"value": ev / sec / 1e6, "unit": "MDE/s", "cores": used, "kind": "reference",
+               "sample": f"rows {mid}..{mid + rows} of the same pair ({rows}/{h} rows, {sec:.2f} s): oracle/_ref = the reference's "
+                         f"BlockSearch.cpp compiled unchanged, SSD-L2 {block}x{block} (its only cost), one BlockSearch per row band on {used} threads"}
+        rows1 = max(1, rows // max(used, 1) // 2)
+        sec_1, _ = _ref_sample(ref, L, R, block, D, mid, rows1, 1)
+        out["literal_1_thread"] = {"value": synth.effective_evals(w, w, rows1, block, 0, D) / sec_1 / 1e6, "unit": "MDE/s", "cores": 1,
+                                   "sample": f"{rows1} rows, {sec_1:.2f} s, extrapolates to {sec_1 / rows1 * h:.0f} s for the pair"}
+    port = port_baseline(orc, L, R, w, h, D, block, cost, 0.4 * args.cpu_seconds, nthreads)
+    if out is None:
+        return port
+    out["port"] = port
+    return out
 
 
 def main():
@@ -380,7 +468,7 @@ def main():
             in_bytes = 2 * w * (r1 - r0) * 3 + w * (r1 - r0) * 8   # algorithmic: BGR in (both images) + CV_64F out
             roofline = {"bound": "alu", "achieved": achieved, "peak": peak_dual / 1e12, "unit": "Tint-op/s",
                         "frac": achieved / (peak_dual / 1e12),
-                        "traffic": NCU_TRAFFIC.get(args.workload),
+                        "traffic": NCU_TRAFFIC.get(args.workload) if world == 1 else None,   # captured for the whole-pair launch only
                         "kernel": "search_tile_kernel", "kernel_ms": k_ms, "ops_per_eval": ops,
                         "evals_per_launch": band_evals, "kernel_MDE_per_s": band_evals / (k_ms * 1e-3) / 1e6,
                         "peak_source": "measured live: VABSDIFF4+IDP.4A dual-pipe issue (sr_int_peak)",
@@ -391,13 +479,11 @@ def main():
             "metric": "disparity_evals_per_s", "value": total_evals / (ms_per_step * 1e-3) / 1e6, "unit": "MDE/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: synthetic {w}x{h} rectified pair, {D} disparities, {block}x{block} "
-                                   f"{cost.upper()}, smooth 1.0 (BASELINE.json configs)",
-                       "sharding": ("single GPU" if world == 1 else
-                                    "row bands; gather = int16 stores into rank 0's HBM over NVLink (peer memory), widened by rank 0 as the flags arrive" if peer is not None else
-                                    "row bands + NCCL gather to rank 0 (int16 wire format, widened on rank 0)"),
-                       "l2": "384 MB written between timed iterations", "evals": "effective (reference break rule)",
-                       "nominal_MDE": w * h * D / 1e6, "effective_MDE": total_evals / 1e6},
+            "config": config_for(args, world),
+            "gather": (None if world == 1 else
+                       "int16 stores into rank 0's HBM over NVLink (peer memory), widened by rank 0 as the flags arrive" if peer is not None else
+                       "NCCL point-to-point to rank 0 (int16 wire format, widened on rank 0)"),
+            "effective_MDE": total_evals / 1e6,
             "pairs_per_s": 1e3 / ms_per_step,
             "nominal_value": w * h * D / (ms_per_step * 1e-3) / 1e6,
             "e2e": {"value": total_evals / e2e_s / 1e6, "unit": "MDE/s", "ms_per_step": e2e_s * 1e3,
@@ -494,10 +580,7 @@ def run_batch(args, rank, world, local_rank):
         line = {"metric": "disparity_evals_per_s", "value": total_pairs * evals / dev_s / 1e6, "unit": "MDE/s", "n_gpus": world,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": dev_s * 1e3 / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
-                "config": {"workload": f"batch720: {n} synthetic 1280x720 pairs per rank and step, 128 disparities, 7x7 SAD + sub-pixel "
-                                       "(BASELINE.json configs[4]; the config names 1024 pairs in total)",
-                           "sharding": "by pair, p mod N, no collective", "l2": "inputs (5.5 MB/pair, ring of 8) exceed nothing: L2 not flushed, "
-                           "the search is compute-bound", "evals": "effective (reference break rule)"},
+                "config": config_for(args, world),
                 "pairs_per_s": total_pairs / dev_s,
                 "e2e": {"value": total_pairs * evals / e2e_s / 1e6, "unit": "MDE/s", "pairs_per_s": total_pairs / e2e_s,
                         "h2d_bytes_per_step": int(n * 2 * w * h * 3), "d2h_bytes_per_step": int(n * w * h * 8),

@@ -45,7 +45,11 @@ def test_config4_4k512_sad(sr, ctx, orc):
         pair.run(p)
         full = pair.download(p)
         assert ctx.last_kernel == "tile"
-        _check_right_rows(orc, L, R, block, D, cost, full)
+        # the WHOLE map against the oracle port (1-3 s on the box's host cores), not a row sample
+        want = orc.block_search_right_fast(L, R, block, 0, D, 1.0, cost=cost)
+        bad = int((full != want).sum())
+        print(f"4K/512 cost {cost}: {bad} mismatching pixels of {full.size}")
+        assert bad == 0
         assert full.min() >= 0 and full.max() < D
         if cost != capi.COST_SAD:
             continue
@@ -109,12 +113,16 @@ def test_config5_batch_720p_subpixel(sr, ctx, orc):
     p = capi.search_params(block=block, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD, subpixel=True)
     capi.block_search_batch(ctx, [a for a, _ in pairs], [b for _, b in pairs], p, outs)
     half = (block - 1) // 2
-    for i in (0, n - 1):
+    for i in range(n):
+        L, R = pairs[i]
+        _, _, sp = orc.search_ext_fast(L, R, block, 0, D, orc.COST_SAD, want_subpix=True)   # whole maps
+        assert np.abs(outs[i] - sp).max() <= 1e-3                                # north_star tolerance
+        np.testing.assert_array_equal(outs[i], sp.astype(np.float64))            # and in fact bit-exact
+    # the literal O(window) definition on row samples of one pair (ties the fast oracle to it at this size too)
+    for i in (0,):
         L, R = pairs[i]
         for c0, c1, r0, r1 in _row_samples(h, 6, block):
             _, _, sp = orc.search_ext(L[c0:c1], R[c0:c1], block, 0, D, orc.COST_SAD, want_subpix=True)
             a = r0 if c0 == 0 else max(r0, c0 + half + 1)
             b = r1 if c1 == h else min(r1, c1 - half - 1)
-            got = outs[i][a:b]
-            assert np.abs(got - sp[a - c0:b - c0]).max() <= 1e-3                 # north_star tolerance
-            np.testing.assert_array_equal(got, sp[a - c0:b - c0].astype(np.float64))   # and in fact bit-exact
+            np.testing.assert_array_equal(outs[i][a:b], sp[a - c0:b - c0].astype(np.float64))
