@@ -37,8 +37,12 @@
 #define CV_32FC1 CV_MAKETYPE(CV_32F, 1)
 #define CV_64FC1 CV_MAKETYPE(CV_64F, 1)
 
+#define CV_Assert(expr) do { if (!(expr)) throw cv::Exception(std::string("(-215:Assertion failed) ") + #expr); } while (0)
+#define CV_Error(code, msg) throw cv::Exception(std::string(msg))
+
 namespace cv {
 typedef unsigned char uchar;
+namespace Error { enum Code { StsBadSize = -201, StsBadArg = -5, StsAssert = -215 }; }
 
 class Exception : public std::exception {
 public:
@@ -107,10 +111,11 @@ public:
     size_t elemSize() const { return esz(type_); }
     Size size() const { return Size(cols, rows); }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
+    bool isContinuous() const { return rows <= 1 || step == (size_t)cols * elemSize(); }
     template <typename T> T& at(int y, int x) { return *reinterpret_cast<T*>(data + (size_t)y * step + (size_t)x * sizeof(T)); }
     template <typename T> const T& at(int y, int x) const { return *reinterpret_cast<const T*>(data + (size_t)y * step + (size_t)x * sizeof(T)); }
-    template <typename T> T* ptr(int y) { return reinterpret_cast<T*>(data + (size_t)y * step); }
-    template <typename T> const T* ptr(int y) const { return reinterpret_cast<const T*>(data + (size_t)y * step); }
+    template <typename T> T* ptr(int y = 0) { return reinterpret_cast<T*>(data + (size_t)y * step); }
+    template <typename T> const T* ptr(int y = 0) const { return reinterpret_cast<const T*>(data + (size_t)y * step); }
     Mat operator()(const Rect& r) const {
         if (!(0 <= r.x && 0 <= r.width && r.x + r.width <= cols && 0 <= r.y && 0 <= r.height && r.y + r.height <= rows))
             throw Exception("(-215:Assertion failed) 0 <= roi.x && 0 <= roi.width && roi.x + roi.width <= m.cols && "

@@ -6,7 +6,8 @@
 #include <string>
 #include <vector>
 #include <opencv2/core.hpp>
-#include "../../Eigen.h"          // the reference's own header: Vector4f, Vector4uc, Matrix3f, MINF
+#include <cmath>
+#include "../Eigen.h"             // the reference's own src/Eigen.h: Vector4f, Vector4uc, Matrix3f, MINF
 #include "../sr_shim_common.h"
 
 struct Vertex {
@@ -17,13 +18,14 @@ struct Vertex {
 static_assert(sizeof(Vertex) == sizeof(sr_vertex), "Vertex layout differs from sr_vertex");
 
 inline bool CheckTriangularValidity(Vertex* vertices, unsigned int one, unsigned int two, unsigned int three, float threshold) {
-    // reconstruction.cpp:46-69 through a 2x2 grid: cell (a,b,c) = (0,2,1); vertex 3 invalid
-    sr_vertex v[4];
-    v[0] = *reinterpret_cast<sr_vertex*>(vertices + one); v[2] = *reinterpret_cast<sr_vertex*>(vertices + two);
-    v[1] = *reinterpret_cast<sr_vertex*>(vertices + three); v[3] = v[0]; v[3].pos[0] = MINF;
-    uint32_t tri[12], n = 0;
-    sr_shim::check(sr_mesh_faces(sr_shim::ctx(), v, 2, 2, threshold, tri, &n));
-    return n == 1;
+    // reconstruction.cpp:46-69 -- nine subtractions and three square roots: computed here, a GPU round trip per triangle
+    // would cost more than the whole mesh (WriteMesh / sr_mesh_faces evaluate all cells on the device in one pass)
+    const Vector4f &a = vertices[one].position, &b = vertices[two].position, &c = vertices[three].position;
+    if (a.x() == MINF || b.x() == MINF || c.x() == MINF) return false;
+    auto len = [](const Vector4f& p, const Vector4f& q) {
+        return sqrtf(powf(p.x() - q.x(), 2) + powf(p.y() - q.y(), 2) + powf(p.z() - q.z(), 2));
+    };
+    return !(len(a, b) > threshold || len(a, c) > threshold || len(b, c) > threshold);
 }
 
 inline bool WriteMesh(Vertex* vertices, unsigned int width, unsigned int height, const std::string& filename, float edgeThreshold) {

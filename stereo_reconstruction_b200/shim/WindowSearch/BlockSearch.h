@@ -28,7 +28,7 @@ private:
         sr_image l = sr_shim::image(leftImage_), r = sr_shim::image(rightImage_);
         int maxBlock = blockSize_;
         sr_shim::check(sr_block_search(sr_shim::ctx(), &l, &r, &p, out.ptr<double>(), out.step, &maxBlock));
-        if (variant == SR_VARIANT_RIGHT) std::cout << "max block size: " << maxBlock << std::endl;   // :177
+        if (variant == SR_VARIANT_RIGHT) std::cout << "max block size: " << maxBlock << "\n";   // :177
         return out;
     }
     cv::Mat leftImage_;   // shallow copies, never written (BlockSearch.h:40-41)

@@ -9,7 +9,8 @@ class LinearSearch {
 public:
     LinearSearch(cv::Mat& leftImage, cv::Mat& rightImage) : leftImage_(leftImage), rightImage_(rightImage) {}
     cv::Mat computeDisparityMap(double smoothFactor) {
-        std::cout << leftImage_.rows << std::endl << rightImage_.rows << std::endl;              // LinearSearch.cpp:16-17
+        std::cout << "h1:" << leftImage_.rows << "\n";                                           // LinearSearch.cpp:16-17
+        std::cout << "h2:" << rightImage_.rows << "\n";
         sr_search_params p{SR_VARIANT_LINEAR, 1, 0, 200, smoothFactor, 0, 19.0, SR_COST_SSD_L2, 0, 0};
         cv::Mat out(rightImage_.rows, rightImage_.cols, CV_64F);
         sr_image l = sr_shim::image(leftImage_), r = sr_shim::image(rightImage_);

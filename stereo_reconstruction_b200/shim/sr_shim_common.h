@@ -5,7 +5,7 @@
 #include <stdexcept>
 #include <string>
 #include <opencv2/core.hpp>
-#include "../../include/sr_capi.h"
+#include "sr_capi.h"   // copied next to this file by INTEGRATION.md 2 (in this repository: -I include)
 
 namespace sr_shim {
 inline sr_ctx* ctx() {
