@@ -379,9 +379,34 @@ def main():
             dist.barrier()
 
     def step_resident():
-        pair.run(params, r0, r1)
-        if world > 1:
-            gather()
+        if peer is not None:
+            peer.run_and_gather(params)      # ranks > 0: the resolve pass stores the int16 wire format into rank 0's window
+        else:
+            pair.run(params, r0, r1)
+            if world > 1:
+                gather()
+
+    # end to end at N > 1: the CV_64F result lives in ONE host buffer shared by the ranks (POSIX shared memory, pinned in
+    # every process): each rank uploads its band's rows (+ halo), searches and downloads its band straight into its rows
+    # of that buffer -- N PCIe links instead of rank 0's one, no device-side gather on this route
+    shm = out_shm = None
+    if world > 1:
+        from multiprocessing import shared_memory
+        name = f"sr_bench_out_{os.environ.get('MASTER_PORT', '0')}"
+        if rank == 0:
+            try:
+                old = shared_memory.SharedMemory(name=name); old.close(); old.unlink()
+            except FileNotFoundError:
+                pass
+            shm = shared_memory.SharedMemory(name=name, create=True, size=h * w * 8)
+        dist.barrier()
+        if rank != 0:
+            shm = shared_memory.SharedMemory(name=name)
+        out_shm = np.ndarray((h, w), np.float64, buffer=shm.buf)
+        capi.host_register(out_shm)
+
+    def step_e2e_shared():
+        pair.search_band(Lp, Rp, params, r0, r1, out=out_shm)         # sr_pair_search_band: H2D (band + halo) + kernels + D2H of the band
 
     def step_e2e():
         if world == 1:
@@ -434,6 +459,21 @@ def main():
         step_e2e()
         e2e_t.append(time.perf_counter() - t0)
     barrier()
+    e2e_shared_s = None
+    if world > 1:
+        for _ in range(2):
+            step_e2e_shared()
+        barrier()
+        ts = []
+        for _ in range(max(3, min(args.steps, 10))):
+            dist.barrier()
+            t0 = time.perf_counter()
+            step_e2e_shared()
+            ts.append(time.perf_counter() - t0)
+        barrier()
+        tt = torch.tensor([float(np.mean(ts))], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_shared_s = float(tt.item())
     clocks = sampler.stop() if sampler else None
     # the same call with pageable buffers (what a cv::Mat holds): staged through pinned memory by host threads
     pageable_ms = None
@@ -455,10 +495,12 @@ def main():
     if rank == 0:
         res = pair.download(params)
         checksum = float(res.sum())
-        gather_ok = None
+        gather_ok = shared_ok = None
         if world > 1:
             pair.run(params)                 # the whole pair on this GPU: the gathered bands must reproduce it
-            gather_ok = bool(np.array_equal(res, pair.download(params)))
+            single = pair.download(params)
+            gather_ok = bool(np.array_equal(res, single))
+            shared_ok = bool(np.array_equal(out_shm, single))
         band_evals = synth.effective_evals(w, w, r1 - r0, block, 0, D)
         k_ms = float(np.mean(kern_ms)) if kern_ms else None
         ops = OPS_PER_EVAL[cost]
@@ -486,10 +528,17 @@ def main():
             "effective_MDE": total_evals / 1e6,
             "pairs_per_s": 1e3 / ms_per_step,
             "nominal_value": w * h * D / (ms_per_step * 1e-3) / 1e6,
-            "e2e": {"value": total_evals / e2e_s / 1e6, "unit": "MDE/s", "ms_per_step": e2e_s * 1e3,
-                    "h2d_bytes_per_step": int(h2d_rows * w * 3 * 2), "d2h_bytes_per_step": int(w * h * 8),
-                    "pageable_ms_per_step": pageable_ms,
-                    "api": "sr_block_search (pinned host buffers; pageable_ms_per_step = same call on pageable buffers)" if world == 1 else "sr_pair_search_band (band rows + halo H2D, chunked) + band gather + sr_search_download of the gathered bands"},
+            "e2e": ({"value": total_evals / e2e_s / 1e6, "unit": "MDE/s", "ms_per_step": e2e_s * 1e3,
+                     "h2d_bytes_per_step": int(h2d_rows * w * 3 * 2), "d2h_bytes_per_step": int(w * h * 8),
+                     "pageable_ms_per_step": pageable_ms,
+                     "api": "sr_block_search (pinned host buffers; pageable_ms_per_step = same call on pageable buffers)"} if world == 1 else
+                    {"value": total_evals / e2e_shared_s / 1e6, "unit": "MDE/s", "ms_per_step": e2e_shared_s * 1e3,
+                     "h2d_bytes_per_step": int(h2d_rows * w * 3 * 2), "d2h_bytes_per_step": int(w * h * 8),
+                     "api": "sr_pair_search_band on every rank: H2D of the band's image rows + halo, band search, D2H of the band into its rows "
+                            "of ONE result buffer in POSIX shared memory pinned by every process (N PCIe links, no device-side gather)",
+                     "result_equals_single_gpu": shared_ok,
+                     "via_rank0": {"value": total_evals / e2e_s / 1e6, "ms_per_step": e2e_s * 1e3,
+                                   "api": "sr_pair_search_band + band gather into rank 0's HBM + sr_search_download on rank 0 (one PCIe link carries the 66 MB)"}}),
             "gpu_launches": int(launches),
             "kernel_family": ctx.last_kernel,
             "clocks": clocks,
@@ -510,6 +559,13 @@ def main():
     barrier()
     capi.free_pinned(lp_h); capi.free_pinned(rp_h); capi.free_pinned(out_h)
     if world > 1:
+        pair.peer_status()                   # a failed step of the gather protocol is an error on every rank
+        capi.host_unregister(out_shm)
+        del out_shm
+        dist.barrier()
+        shm.close()
+        if rank == 0:
+            shm.unlink()
         dist.destroy_process_group()
 
 

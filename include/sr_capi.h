@@ -154,8 +154,8 @@ void* sr_search_result16_dev(sr_ctx* ctx, sr_pair* pair);
  * stores them into the root's HBM and publishes the step in the root's flag word of rank r; the root calls
  * sr_search_collect_bands after its own band search -- one kernel widens every other rank's rows (bands of
  * sr_band_rows(h, r, nranks)) into its CV_64F result as their flags arrive and acknowledges the step, which
- * lets the pushers overwrite the window.  All asynchronous on the context stream; a band that does not arrive
- * within ~1 s sets the pair's status (reported by sr_search_download) instead of hanging the GPU.
+ * lets the pushers overwrite the window.  All asynchronous on the context stream; a band that does not arrive in
+ * time sets the pair's sticky status (see sr_search_run_push) instead of hanging the GPU.
  * sr_pair_peer_attach_local attaches to a root pair of the same process (single-GPU tests of the protocol). */
 #define SR_PEER_HANDLE_BYTES 64
 int sr_pair_peer_export(sr_ctx* ctx, sr_pair* pair, void* handle);
@@ -163,6 +163,15 @@ int sr_pair_peer_attach(sr_ctx* ctx, sr_pair* pair, const void* handle);
 int sr_pair_peer_attach_local(sr_ctx* ctx, sr_pair* pair, sr_pair* root);
 int sr_pair_peer_detach(sr_ctx* ctx, sr_pair* pair);
 int sr_search_push_band(sr_ctx* ctx, sr_pair* pair, int row0, int row1, int rank, unsigned seq);
+/* The band search of a rank > 0 with the gather fused into it: sr_search_run on rows [row0,row1) whose resolve pass
+ * writes the int16 wire format straight into the root's window and publishes step `seq` -- the CV_64F band is never
+ * formed and no push kernel runs (falls back to sr_search_run + sr_search_push_band where the fused pass does not
+ * apply).  Every export / attach starts a new generation of the protocol (steps restart at 1).  A band or an
+ * acknowledgement that does not arrive within SR_PEER_TIMEOUT_MS (default 10000) is never published / acknowledged;
+ * the failure is sticky and reported by every later sr_search_run_push / sr_search_push_band /
+ * sr_search_collect_bands / sr_search_download / sr_ctx_sync / sr_pair_peer_status on that rank. */
+int sr_search_run_push(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1, int rank, unsigned seq);
+int sr_pair_peer_status(sr_ctx* ctx, sr_pair* pair);
 int sr_search_collect_bands(sr_ctx* ctx, sr_pair* pair, int nranks, unsigned seq);
 int sr_search_max_block(sr_ctx* ctx, sr_pair* pair, int* max_block);
 /* The left-referenced integer disparity map (w1 x h1, int32) that the last run with lr_check = 1

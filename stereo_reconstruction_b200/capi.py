@@ -54,7 +54,7 @@ SYMBOLS = [
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
     "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
     "sr_search_kernel_ms", "sr_int_peak", "sr_pair_reconstruct_warp", "sr_average_disparity", "sr_pfm_info", "sr_read_pfm",
-    "sr_read_calib",
+    "sr_read_calib", "sr_search_run_push", "sr_pair_peer_status",
 ]
 
 _lib = None
@@ -277,6 +277,14 @@ class Pair:
 
     def push_band(self, row0, row1, rank, seq):
         self.ctx.check(self.ctx._l.sr_search_push_band(self.ctx.h, self.h, int(row0), int(row1), int(rank), C.c_uint(int(seq))))
+
+    def run_push(self, params, row0, row1, rank, seq):
+        """sr_search_run_push: band search whose resolve pass stores the int16 wire format into the root's window."""
+        self.ctx.check(self.ctx._l.sr_search_run_push(self.ctx.h, self.h, C.byref(params), int(row0), int(row1), int(rank), C.c_uint(int(seq))))
+
+    def peer_status(self):
+        """Synchronises and raises if a step of the gather protocol failed on this rank (sticky)."""
+        self.ctx.check(self.ctx._l.sr_pair_peer_status(self.ctx.h, self.h))
 
     def collect_bands(self, nranks, seq):
         self.ctx.check(self.ctx._l.sr_search_collect_bands(self.ctx.h, self.h, int(nranks), C.c_uint(int(seq))))

@@ -371,6 +371,24 @@ int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row
     return SR_OK;
 }
 
+// Band search of a rank > 0 of a row-band sharded pair with the gather fused into it: sr_search_run on rows
+// [row0,row1) whose resolve pass writes the int16 wire format straight into the root's gather window and publishes step
+// `seq` (no CV_64F band, no separate push kernel).  Where the fused pass does not apply (odd width, direct kernels,
+// smoothing rule) it is sr_search_run followed by sr_search_push_band -- same protocol, same result on the root.
+int sr_search_run_push(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1, int rank, unsigned seq) {
+    if (!ctx || !pair || !p) return sr_fail(ctx, SR_E_BADARG, "sr_search_run_push: NULL argument");
+    if (pair->peer_mode != 2 && pair->peer_mode != 3) return sr_fail(ctx, SR_E_BADARG, "sr_search_run_push: not attached to a root window");
+    if (rank < 1 || rank >= 32 || seq == 0) return sr_fail(ctx, SR_E_BADARG, "sr_search_run_push: rank 1..31, step >= 1");
+    int st = sr_peer_check(ctx, pair);
+    if (st != SR_OK) return st;
+    pair->wire_rank = rank; pair->wire_seq = seq; pair->wire_done = false;
+    int rc = sr_search_run(ctx, pair, p, row0, row1);
+    bool done = pair->wire_done;
+    pair->wire_rank = 0; pair->wire_seq = 0; pair->wire_done = false;
+    if (rc != SR_OK) return rc;
+    return done ? SR_OK : sr_search_push_band(ctx, pair, row0, row1, rank, seq);
+}
+
 void* sr_search_result_dev(sr_ctx* ctx, sr_pair* pair) { return pair ? (void*)pair->out : nullptr; }
 
 int sr_search_download(sr_ctx* ctx, sr_pair* pair, double* disp_out, size_t out_pitch, int row0, int row1) {
@@ -400,7 +418,7 @@ int sr_search_download(sr_ctx* ctx, sr_pair* pair, double* disp_out, size_t out_
     int status[2];
     SR_CUDA(ctx, cudaMemcpy(status, pair->maxblock, sizeof status, cudaMemcpyDeviceToHost));
     if (status[1] == SR_E_BADARG) return sr_fail(ctx, status[1], "sr_search_pack16: the map holds values that are not integers in int16 range");
-    if (status[1] == SR_E_CUDA) return sr_fail(ctx, status[1], "band gather over peer memory: a rank's band did not arrive (timeout)");
+    { int st = sr_peer_check(ctx, pair); if (st != SR_OK) return st; }   // band gather: sticky protocol status
     if (status[1] != SR_OK) return sr_fail(ctx, status[1], "the grown window runs past the left image (cv::Exception in the reference)");
     return SR_OK;
 }

@@ -262,7 +262,7 @@ int recon_box_blur(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, 
     const int logn = blur_logn(w, h, k);
     if (!known_u8) {   // the 8-bit hand-off (quantize_kernel's output) needs no look at the data
         const size_t nvec = ((uintptr_t)d_src & 15) ? 0 : n / 4;
-        blur_exact_check_kernel<<<148 * 8, 256, 0, ctx->stream>>>(d_src, n, nvec, flag);
+        blur_exact_check_kernel<<<ctx->sms * 8, 256, 0, ctx->stream>>>(d_src, n, nvec, flag);
         SR_LAUNCHED(ctx);
     }
     static DeviceOnce configured;

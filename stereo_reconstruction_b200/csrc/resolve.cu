@@ -117,6 +117,59 @@ __global__ void resolve_plain2_kernel(SearchGeom g, int have_c0 /* 0 or 2 */, Pl
     *reinterpret_cast<double2*>(out + i) = make_double2(v[0], v[1]);
 }
 
+// The same two-pixel resolve with the int16 wire format of the band gather as its output ("fuse by letting
+// the WTA epilogue write straight into the registered send buffer"): ranks > 0 of a row-band sharded pair never form
+// the CV_64F band -- the disparities go as short2 stores into the root's gather window over NVLink, and the last block
+// publishes the step in the root's flag word of this rank (the acknowledgement of the previous step was awaited by a
+// one-thread kernel earlier on the stream, sr_peer_wait_ack).  Values outside int16 (an image wider than 32767 pixels
+// whose "no candidate" value -x does not fit) set the pair's sticky status instead of the flag.
+__global__ void resolve_wire16_kernel(SearchGeom g, Planes pl, const uint32_t* __restrict__ Rp, int pitchR, short* win16,
+                                      volatile unsigned* flags, int rank, unsigned seq, unsigned* counter, int* status) {
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const int y = g.row0 + blockIdx.y;
+    if (x < g.w2 && y < g.row1) {
+        const size_t i = (size_t)y * g.w2 + x;
+        const bool yin = y < g.height;
+        const uint2 px2 = yin ? __ldg(reinterpret_cast<const uint2*>(Rp + (size_t)y * pitchR + x)) : make_uint2(0u, 0u);
+        uint32_t bc[2] = {0xFFFFFFFFu, 0xFFFFFFFFu};
+        int bd[2] = {0, 0};
+        for (int p = 0; p < pl.npass; p++) {
+            const uint2 k2 = __ldg(reinterpret_cast<const uint2*>(pl.planes + (size_t)p * pl.stride + i));
+            const uint32_t k[2] = {k2.x, k2.y};
+#pragma unroll
+            for (int e = 0; e < 2; e++)
+                if (k[e] != 0xFFFFFFFFu && (k[e] >> pl.shift) < bc[e]) {
+                    bc[e] = k[e] >> pl.shift;
+                    bd[e] = pl.dbase + 64 * p + (int)(k[e] & ((1u << pl.shift) - 1u));
+                }
+        }
+        const uint32_t px[2] = {px2.x, px2.y};
+        int v[2];
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            const int xe = x + e;
+            const bool skip = !yin || (px[e] & 0xFFFFFFu) == 0;
+            const int l = min(xe, g.half), rr = min(g.w2 - xe - 1, g.half), u = min(y, g.half), dn = min(g.h2 - y - 1, g.half);
+            const int n = (l + rr) * (u + dn);
+            if (skip) v[e] = 0;
+            else if (n == 0) v[e] = 0 - xe;
+            else if (bc[e] != 0xFFFFFFFFu) v[e] = bd[e];
+            else v[e] = 0 - xe;
+            if (v[e] < -32768 || v[e] > 32767) { *status = SR_E_BADARG; v[e] = 0; }
+        }
+        *reinterpret_cast<short2*>(win16 + i) = make_short2((short)v[0], (short)v[1]);
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (atomicAdd(counter, 1u) == gridDim.x * gridDim.y - 1) {   // last block: every block's stores are fenced
+            *counter = 0;
+            __threadfence_system();
+            if (*(volatile int*)status == SR_OK) flags[rank] = seq;
+        }
+    }
+}
+
 // Phase A of the smoothing pass: bit planes a0,a1,a2 (ballot words) and the alternative value.
 __global__ void smooth_prepare_kernel(SearchGeom g, int from_direct, int have_c0, double s, Planes best,
                                       const unsigned long long* __restrict__ c0, const unsigned long long* __restrict__ cr,
@@ -312,6 +365,18 @@ int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, dou
     Planes pl{pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase, pair->key_shift};
     dim3 grid(cdiv(g.w2, 128), rows);
     bool plain = smooth == 1.0 || !have_c0;
+    pair->wire_done = false;
+    if (pair->wire_seq && plain && !from_direct && have_c0 == 0 && (g.w2 & 1) == 0 && (pl.stride & 1) == 0 && (pair->R.pitch & 1) == 0 &&
+        (((uintptr_t)pl.planes | (uintptr_t)pair->R.px) & 7) == 0 && pair->peer_win && (pair->peer_mode == 2 || pair->peer_mode == 3)) {
+        int rc = sr_peer_wait_ack(ctx, pair, pair->wire_seq);
+        if (rc != SR_OK) return rc;
+        resolve_wire16_kernel<<<dim3(cdiv(g.w2, 256), rows), 128, 0, ctx->stream>>>(g, pl, pair->R.px, pair->R.pitch, sr_peer_window16(pair),
+                                                                                   sr_peer_flags(pair), pair->wire_rank, pair->wire_seq,
+                                                                                   pair->peer_counter, pair->peer_status_d);
+        SR_LAUNCHED(ctx);
+        pair->wire_done = true;
+        return SR_OK;
+    }
     if (plain && !from_direct && have_c0 != 1 && (g.w2 & 1) == 0 && (pl.stride & 1) == 0 && (pair->R.pitch & 1) == 0 &&
         (((uintptr_t)pl.planes | (uintptr_t)pair->R.px | (uintptr_t)pair->c0) & 7) == 0 && ((uintptr_t)pair->out & 15) == 0) {
         resolve_plain2_kernel<<<dim3(cdiv(g.w2, 256), rows), 128, 0, ctx->stream>>>(g, have_c0, pl, (const uint32_t*)pair->c0,

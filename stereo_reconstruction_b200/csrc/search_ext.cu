@@ -354,7 +354,10 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
     int* disp_r = (int*)sr_scratch(ctx, 14, npx * 4 * 2);
     float* subpix = p->subpixel ? (float*)sr_scratch(ctx, 15, npx * 4) : nullptr;
     if (!disp_r || (p->subpixel && !subpix)) return SR_E_CUDA;
-    int* disp_l = p->lr_check ? disp_r + npx : nullptr;
+    // the left-referenced map outlives this call (sr_search_left_disparity): it lives in a buffer of the pair, not in
+    // the context's shared scratch, which the next search on ANY pair of the context may overwrite or regrow
+    if (p->lr_check && !pair->disp_left_own) SR_CUDA(ctx, cudaMalloc((void**)&pair->disp_left_own, npx * sizeof(int)));
+    int* disp_l = p->lr_check ? pair->disp_left_own : nullptr;
     int dhi = p->max_disp, dlo = p->min_disp;
     if (dhi < dlo) dhi = dlo;
     ExtGeom g{w2, h2, w1, h1, h1 < h2 ? h1 : h2, half, dlo, dhi, 0, p->cost, row0};

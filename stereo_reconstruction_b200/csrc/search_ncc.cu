@@ -384,7 +384,7 @@ int sr_launch_search_ncc(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, float*
     const int tile_out = (2 * h - 1 > XT ? 30 : 31) * XT;
     int ntx = cdiv(g.w2 - 2 * h + XT, tile_out);
     int rows = r1 - r0;
-    const int sms = 148;
+    const int sms = ctx->sms;
     int maxnb = rows / (2 * h + 2); if (maxnb < 1) maxnb = 1; if (maxnb > 256) maxnb = 256;
     long bestcost = -1; int nbands = 1; a.band = rows;
     for (int nb = 1; nb <= maxnb; nb++) {

@@ -132,6 +132,7 @@ __global__ void __launch_bounds__(LEFT_WARPS * 32) left_raster_kernel(const uint
             double dup = 0.0;
             if (y - 1 >= h) {
                 if (lane == 0) while (done[y - 1] <= x) { }
+                __threadfence();                                  // acquire side of the writer's store -> fence -> flag
                 __syncwarp();
                 dup = __ldcg(out + o - w1);
             }

@@ -407,51 +407,109 @@ int dispatch_h2(sr_ctx* ctx, const TileArgs& a, int nwork) {
 //  * Bands, then tiles, then passes (heaviest -- masked / ragged -- pass first): the passes of one (tile, band)
 //    run at the same time and share its image rows in L2, so DRAM reads stay near one sweep of the two images
 //    (pass-major order re-reads them once per wave: 295 MB instead of 106 MB on the 4K pair).
-//  * The last `pct` percent of the rows are cut into bands 1/div as tall: the last CTAs to start are short, so
-//    the SMs run dry together at the end of the kernel (4K/512: -6 %).
+//  * The rows are cut into `nb` equal bands followed by a tail of bands 1/div as tall over the last `pct` percent of
+//    the rows: the last CTAs to start are short, so the SMs run dry together at the end of the kernel.  (nb, pct, div)
+//    is chosen by SIMULATING the hardware's list scheduling of that very list on the device's SM count (one CTA per
+//    SM, the next CTA of the list goes to the SM that frees first) with a cost model of one unit per output row, 0.3
+//    per warm-up row, a fixed launch share and 20 % more for passes on the break-rule diagonal; the plan with the
+//    smallest makespan wins.  A 270-row band of the 4K pair at 8 GPUs (62 (tile, pass) columns on 148 SMs) thus
+//    becomes two bands of ~118 rows and a short tail instead of two of 135.
 //  * With the merged key plane, (tile, pass) combinations without a single candidate (break rule at the right
 //    image edge) are left out altogether.
 // Lists are cached per geometry on the context (the row-chunk pipeline repeats the same few shapes).
-int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx, int rows, int band, int nbands,
-                   const int4** work, int* nwork) {
+int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx, int rows, const int4** work, int* nwork) {
     static const char* ord_env = getenv("SR_TILE_ORDER");   // 0: pass-major (development comparison)
     static const char* tl_env = getenv("SR_TILE_TAIL");     // "percent,divisor" tuning override
+    static const char* nb_env = getenv("SR_TILE_NBANDS");   // tuning override
     const int order = ord_env ? atoi(ord_env) : 1;
-    int pct = 10, div = 4;
-    if (tl_env) sscanf(tl_env, "%d,%d", &pct, &div);
-    if (ctx->more_chunks_follow) pct = 0;   // row-chunk pipeline: the next chunk's CTAs fill the end of this launch
+    int f_pct = -1, f_div = -1, f_nb = nb_env ? atoi(nb_env) : 0;
+    if (tl_env) sscanf(tl_env, "%d,%d", &f_pct, &f_div);
+    const int no_tail = ctx->more_chunks_follow ? 1 : 0;   // row-chunk pipeline: the next chunk's CTAs fill the end of this launch
     TileWork key;
-    const int kv[TileWork::NKEY] = {g.w1, g.w2, g.half, a.dlo, a.dhi, a.row0, a.row1, a.merged, order, pct, div, band};
+    const int kv[TileWork::NKEY] = {g.w1, g.w2, g.half, a.dlo, a.dhi, a.row0, a.row1, a.merged, order, f_pct * 64 + f_div, f_nb, no_tail};
     for (int i = 0; i < TileWork::NKEY; i++) key.key[i] = kv[i];
     for (TileWork& t : ctx->tile_work)
         if (!memcmp(t.key, key.key, sizeof key.key)) { t.stamp = ++ctx->tile_work_clock; *work = t.dev; *nwork = t.n; return SR_OK; }
-    // bands
-    std::vector<int2> bands;
-    {
-        int band2 = div > 1 ? band / div : band;
-        if (band2 < 2 * g.half + 2) band2 = 2 * g.half + 2;
-        int rows_tail = order && div > 1 && nbands >= 4 ? rows * pct / 100 : 0;
-        int nb1 = (rows - rows_tail + band - 1) / band;
-        int split = a.row0 + (nb1 * band < rows ? nb1 * band : rows);
-        for (int y = a.row0; y < split; y += band) bands.push_back(make_int2(y, y + band < split ? y + band : split));
-        for (int y = split; y < a.row1; y += band2) bands.push_back(make_int2(y, y + band2 < a.row1 ? y + band2 : a.row1));
+
+    const int warm = 2 * g.half - 1, minband = 2 * g.half + 2;
+    auto dlim_at = [&](int x) {
+        int r = g.w2 - x - 1 < g.half ? g.w2 - x - 1 : g.half;
+        return g.w1 - x - r < a.dhi ? g.w1 - x - r : a.dhi;
+    };
+    auto x_first_of = [&](int tile) { int x = -XT + TILE_OUT * tile + g.half; return x < 0 ? 0 : x; };
+    auto has_candidates = [&](int tile, int pass) { return a.dbase + 64 * pass < dlim_at(x_first_of(tile)); };
+    // (tile, pass) columns in launch order within a band, with their relative cost per row
+    struct Col { int tile, pass; float w; };
+    std::vector<Col> cols;
+    for (int t = 0; t < ntx; t++)
+        for (int p = a.npass - 1; p >= 0; p--) {
+            if (a.merged && !has_candidates(t, p)) continue;   // planes mode: the CTA still writes its "none" keys
+            int x_last = -XT + TILE_OUT * (t + 1) + g.half - 1;
+            if (x_last > g.w2 - 1) x_last = g.w2 - 1;
+            bool masked = a.dbase + 64 * p < a.dlo || a.dbase + 64 * (p + 1) > dlim_at(x_last);
+            cols.push_back({t, p, has_candidates(t, p) ? (masked ? 1.2f : 1.0f) : 0.1f});
+        }
+    auto make_bands = [&](int nb, int pct, int div) {
+        std::vector<int2> bands;
+        int rows_tail = (div > 1 && pct > 0) ? rows * pct / 100 : 0;
+        if (rows_tail < minband) rows_tail = 0;
+        int main_rows = rows - rows_tail;
+        if (nb < 1) nb = 1;
+        int band = (main_rows + nb - 1) / nb;
+        if (band < minband) band = minband;
+        int y = a.row0;
+        for (; y + band <= a.row0 + main_rows; y += band) bands.push_back(make_int2(y, y + band));
+        int band2 = rows_tail ? band / div : band;
+        if (band2 < minband) band2 = minband;
+        for (; y < a.row1; y += band2) bands.push_back(make_int2(y, y + band2 < a.row1 ? y + band2 : a.row1));
+        return bands;
+    };
+    std::vector<double> sm_free((size_t)ctx->sms);
+    auto makespan = [&](const std::vector<int2>& bands) {
+        std::fill(sm_free.begin(), sm_free.end(), 0.0);
+        // a binary heap would do; the lists are a few hundred to a few thousand items and SMs free up in order
+        double end = 0;
+        auto run = [&](const Col& c, int2 b) {
+            size_t k = 0;
+            for (size_t i = 1; i < sm_free.size(); i++) if (sm_free[i] < sm_free[k]) k = i;
+            sm_free[k] += 3.0 + c.w * ((b.y - b.x) + 0.3 * warm);
+            if (sm_free[k] > end) end = sm_free[k];
+        };
+        if (order) { for (int2 b : bands) for (const Col& c : cols) run(c, b); }
+        else { for (int p = a.npass - 1; p >= 0; p--) for (int2 b : bands) for (const Col& c : cols) if (c.pass == p) run(c, b); }
+        return end;
+    };
+    std::vector<int2> best_bands;
+    double best = -1;
+    if (!cols.empty()) {
+        const int maxnb = rows / minband < 1 ? 1 : (rows / minband > 96 ? 96 : rows / minband);
+        static const int pcts[] = {0, 6, 10, 14, 18, 24, 30, 38}, divs[] = {2, 3, 4};
+        for (int nb = (f_nb > 0 ? f_nb : 1); nb <= (f_nb > 0 ? f_nb : maxnb); nb++) {
+            if ((size_t)nb * cols.size() > 6000) break;        // makespan() is O(items x SMs)
+            for (int pct : pcts) {
+                if (f_pct >= 0 && pct != pcts[0]) continue;
+                if (no_tail && pct) continue;
+                for (int div : divs) {
+                    if ((pct == 0 || f_pct >= 0) && div != divs[0]) continue;
+                    std::vector<int2> bands = make_bands(nb, f_pct >= 0 ? (no_tail ? 0 : f_pct) : pct, f_div > 0 ? f_div : div);
+                    double m = makespan(bands);
+                    if (best < 0 || m < best * 0.999) { best = m; best_bands.swap(bands); }
+                }
+            }
+        }
     }
-    auto has_candidates = [&](int tile, int pass) {
-        int x_first = -XT + TILE_OUT * tile + g.half;
-        if (x_first < 0) x_first = 0;
-        int r = g.w2 - x_first - 1 < g.half ? g.w2 - x_first - 1 : g.half;
-        int dlim = g.w1 - x_first - r < a.dhi ? g.w1 - x_first - r : a.dhi;
-        return a.dbase + 64 * pass < dlim;
-    };
     std::vector<int4> items;
-    auto add = [&](int tile, int2 b, int pass) {
-        if (a.merged && !has_candidates(tile, pass)) return;   // planes mode: the CTA still writes its "none" keys
-        items.push_back(make_int4(tile, b.x, b.y, pass));
-    };
     if (order) {
-        for (int2 b : bands) for (int t = 0; t < ntx; t++) for (int p = a.npass - 1; p >= 0; p--) add(t, b, p);
+        for (int2 b : best_bands) for (const Col& c : cols) items.push_back(make_int4(c.tile, b.x, b.y, c.pass));
     } else {
-        for (int p = a.npass - 1; p >= 0; p--) for (int2 b : bands) for (int t = 0; t < ntx; t++) add(t, b, p);
+        for (int p = a.npass - 1; p >= 0; p--) for (int2 b : best_bands) for (const Col& c : cols) if (c.pass == p) items.push_back(make_int4(c.tile, b.x, b.y, c.pass));
+    }
+    static const char* dbg_env = getenv("SR_TILE_PLAN_DEBUG");
+    if (dbg_env) {
+        fprintf(stderr, "[tile plan] rows %d..%d cols %zu bands %zu (first %d, last %d rows) items %zu makespan %.0f ideal %.0f\n", a.row0, a.row1,
+                cols.size(), best_bands.size(), best_bands.empty() ? 0 : best_bands.front().y - best_bands.front().x,
+                best_bands.empty() ? 0 : best_bands.back().y - best_bands.back().x, items.size(), best,
+                cols.size() * (double)rows / ctx->sms);
     }
     key.n = (int)items.size();
     key.dev = nullptr;
@@ -489,8 +547,8 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     // per-warp instruction mixes (window_wta, pcost_sub); SR_TILE_ZMASK / SR_TILE_FMASK override for tuning
     static const char* zm_env = getenv("SR_TILE_ZMASK");
     static const char* fm_env = getenv("SR_TILE_FMASK");
-    a.zmask = zm_env ? (uint32_t)strtoul(zm_env, nullptr, 0) : (cost == SR_COST_SAD ? 0xEEEEu : 0x0000u);
-    a.fmask = fm_env ? (uint32_t)strtoul(fm_env, nullptr, 0) : 0xEEEEu;
+    a.zmask = zm_env ? (uint32_t)strtoul(zm_env, nullptr, 0) : (cost == SR_COST_SAD ? 0xFFF0u : 0x0000u);   // measured: tools/tune_tile.sh
+    a.fmask = fm_env ? (uint32_t)strtoul(fm_env, nullptr, 0) : 0xFFFFu;
     static const char* rm_env = getenv("SR_TILE_REDMODE");
     a.red_mode = rm_env ? atoi(rm_env) : 1;
     int ntx = (g.w2 + XT - g.half + TILE_OUT - 1) / TILE_OUT;
@@ -517,27 +575,8 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     a.planes = pair->planes; a.plane_stride = pair->npx_cap;
     if (a.merged)
         SR_CUDA(ctx, cudaMemsetAsync(pair->planes + (size_t)g.row0 * g.w2, 0xFF, (size_t)(r1 - g.row0) * g.w2 * sizeof(uint32_t), ctx->stream));
-    // bands: CTAs = ntx * npass * nbands, one CTA per SM at a time; minimise waves * (band + warm-up rows)
-    const int sms = 148;
-    int maxnb = rows / (2 * g.half + 2);
-    if (maxnb < 1) maxnb = 1;
-    if (maxnb > 256) maxnb = 256;
-    long bestcost = -1;
-    int nbands = 1, band = rows;
-    static const char* nb_env = getenv("SR_TILE_NBANDS");   // tuning override
-    int nb_lo = 1;
-    if (nb_env && atoi(nb_env) > 0) { nb_lo = atoi(nb_env); if (nb_lo > maxnb) nb_lo = maxnb; maxnb = nb_lo; }
-    for (int nb = nb_lo; nb <= maxnb; nb++) {
-        int bnd = (rows + nb - 1) / nb;
-        int nbe = (rows + bnd - 1) / bnd;
-        long ctas = (long)ntx * a.npass * nbe;
-        // makespan model: CTAs are list-scheduled one per SM; durations vary (masked passes, image edges),
-        // so the tail costs about one CTA duration on top of the average load
-        long c = (long)((double)(ctas + sms) / sms * (bnd + 2 * g.half - 1 + 2) * 16.0);
-        if (bestcost < 0 || c < bestcost) { bestcost = c; nbands = nbe; band = bnd; }
-    }
     int nwork = 0;
-    int rc = tile_work_list(ctx, g, a, ntx, rows, band, nbands, &a.work, &nwork);
+    int rc = tile_work_list(ctx, g, a, ntx, rows, &a.work, &nwork);
     if (rc != SR_OK) return rc;
     if (nwork == 0) return 1;                                // merged plane, no (tile, pass) has a candidate: all "none"
     if (cost == SR_COST_SAD) return dispatch_h2<SR_COST_SAD>(ctx, a, nwork);

@@ -62,6 +62,7 @@ int sr_ctx_create(int device, sr_ctx** out) {
     if ((e = cudaSetDevice(device)) != cudaSuccess) return sr_cuda_check(nullptr, e, "cudaSetDevice");
     sr_ctx* c = new sr_ctx();
     c->device = device;
+    { int n = 0; if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && n > 0) c->sms = n; }
     // the copy streams outrank the compute stream: their small pack kernels must not queue behind the
     // search kernel's CTAs (one per SM) when the pipelines overlap upload, search and download
     int prio_lo = 0, prio_hi = 0;
@@ -125,6 +126,8 @@ void* sr_ctx_stream(sr_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 int sr_ctx_sync(sr_ctx* ctx) {
     if (!ctx) return SR_E_BADARG;
     SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    // a failed step of a band gather (time-out, non-integer map) is reported by every rank at its next synchronisation
+    for (sr_pair* p : ctx->peer_pairs) { int st = sr_peer_check(ctx, p); if (st != SR_OK) return st; }
     return SR_OK;
 }
 int sr_timer_start(sr_ctx* ctx) {
@@ -281,7 +284,9 @@ void sr_pair_destroy(sr_ctx* ctx, sr_pair* p) {
     if (!p) return;
     if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
     sr_pair_peer_detach(ctx, p); cudaFree(p->peer_counter);
-    cudaFree(p->L.base); cudaFree(p->R.base); cudaFree(p->Lm.base); cudaFree(p->Rm.base); cudaFree(p->ncc_tab); cudaFree(p->ncc_tab_m); cudaFree(p->out16); cudaFree(p->rawL); cudaFree(p->rawR);
+    if (p->peer_status_h) cudaFreeHost(p->peer_status_h);
+    if (ctx) for (size_t i = 0; i < ctx->peer_pairs.size(); i++) if (ctx->peer_pairs[i] == p) { ctx->peer_pairs.erase(ctx->peer_pairs.begin() + i); break; }
+    cudaFree(p->L.base); cudaFree(p->R.base); cudaFree(p->Lm.base); cudaFree(p->Rm.base); cudaFree(p->ncc_tab); cudaFree(p->ncc_tab_m); cudaFree(p->out16); cudaFree(p->disp_left_own); cudaFree(p->rawL); cudaFree(p->rawR);
     cudaFree(p->best); cudaFree(p->c0); cudaFree(p->cr); cudaFree(p->dr); cudaFree(p->nwin);
     cudaFree(p->bits); cudaFree(p->alt); cudaFree(p->out); cudaFree(p->outf); cudaFree(p->maxblock);
     delete p;

@@ -38,6 +38,7 @@ struct DeviceOnce {
 
 struct sr_ctx {
     int device = 0;
+    int sms = 148;                 // cudaDevAttrMultiProcessorCount of `device` (B200: 148), set by sr_ctx_create
     cudaStream_t stream = nullptr;
     cudaStream_t aux[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // 0/1: copy streams of the pipelines, 2/3: extra compute streams, 4: pack kernels (high priority)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -50,6 +51,7 @@ struct sr_ctx {
     void* pinned[4] = {nullptr, nullptr, nullptr, nullptr};
     size_t pinned_cap[4] = {0, 0, 0, 0};
     std::vector<sr_pair*> batch_pairs;
+    std::vector<sr_pair*> peer_pairs;  // pairs with a gather window: sr_ctx_sync reports their protocol status
     std::vector<cudaEvent_t> pipe_ev;  // events of the row-chunk pipeline of sr_block_search
     sr_stage_pool* stage_pool = nullptr;
     std::vector<TileWork> tile_work;   // schedules of the tile kernel, by geometry
@@ -99,6 +101,11 @@ struct sr_pair {
     void* peer_win = nullptr;             // gather window over peer memory (capi_peer.cu)
     int peer_mode = 0;                    // 0 none, 1 root (owns the window), 2 attached through CUDA IPC, 3 attached in-process
     unsigned* peer_counter = nullptr;     // last-block counter of the push / collect kernels
+    int* peer_status_h = nullptr;         // sticky status of the gather protocol: one word of mapped pinned host memory that the
+    int* peer_status_d = nullptr;         // kernels write (time-out, non-integer map) and the host reads without a copy
+    int wire_rank = 0;                    // set by sr_search_run_push around the run: the resolve pass writes the int16 wire
+    unsigned wire_seq = 0;                // format straight into the root's window (rank, step) instead of the CV_64F map
+    bool wire_done = false;               // ... and reports here that it did
     int* maxblock = nullptr;              // device scalar
     unsigned long long* evals = nullptr;  // device scalar
     size_t npx_cap = 0;
@@ -106,7 +113,8 @@ struct sr_pair {
     bool evals_valid = false;
     void* ncc_tab = nullptr;              // window-moment tables of the NCC search (search_ncc.cu)
     void* ncc_tab_m = nullptr;            // the same for the mirror-packed pair (left-referenced NCC search)
-    const int* disp_left = nullptr;       // left-referenced map of the last lr_check run (ctx scratch)
+    const int* disp_left = nullptr;       // left-referenced map of the last lr_check run (= disp_left_own, or NULL)
+    int* disp_left_own = nullptr;         // pair-owned buffer: searches on other pairs of the context cannot overwrite it
     SearchGeom last_geom;
 };
 
@@ -167,6 +175,11 @@ int sr_launch_search_left(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, d
 int sr_launch_search_linear(sr_ctx* ctx, sr_pair* pair, double smooth);
 // cv::warpPerspective(..., INTER_NEAREST) on device buffers (misc.cu); M as passed to warpPerspective
 int sr_launch_warp_nearest(sr_ctx* ctx, const double* d_src, int sw, int sh, double* d_dst, int dw, int dh, const double M[9]);
+// band gather over peer memory (capi_peer.cu)
+int sr_peer_check(sr_ctx* ctx, sr_pair* pair);                 // SR_OK, or the sticky protocol error of this pair
+int sr_peer_wait_ack(sr_ctx* ctx, sr_pair* pair, unsigned seq); // stream-ordered: the root has consumed step seq-1
+short* sr_peer_window16(sr_pair* pair);                        // int16 map of the window this pair is attached to / owns
+volatile unsigned* sr_peer_flags(sr_pair* pair);
 int sr_launch_count_evals(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g);
 // NCC through sliding sums: interior pixels -> per-pass (score, d) planes (search_ncc.cu)
 int sr_launch_search_ncc(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, float** pscore, int** pdisp, void** tab);

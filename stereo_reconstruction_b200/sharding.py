@@ -89,6 +89,21 @@ class PeerGather:
             r0, r1 = band_rows(self.h, self.rank, self.world)
             self.pair.push_band(r0, r1, self.rank, self.seq)
 
+    def run_and_gather(self, params):
+        """One step: this rank's band search + the gather.  Ranks > 0 run the search with the gather fused into its
+        resolve pass (sr_search_run_push: int16 stores into rank 0's window, no CV_64F band, no push kernel); rank 0
+        searches its own band and widens the others' as their flags arrive."""
+        r0, r1 = band_rows(self.h, self.rank, self.world)
+        if self.world == 1:
+            self.pair.run(params, r0, r1)
+            return
+        self.seq += 1
+        if self.rank == 0:
+            self.pair.run(params, r0, r1)
+            self.pair.collect_bands(self.world, self.seq)
+        else:
+            self.pair.run_push(params, r0, r1, self.rank, self.seq)
+
 
 def gather_bands(full, h, rank, world, group=None):
     """`full` is an (h, w) tensor on every rank whose rows band_rows(h, rank, world) hold this rank's

@@ -1,0 +1,95 @@
+"""Thin spots of the parity suite, hardened (round-1 review): randomised varBlock against the literal oracle (itself
+pinned to the compiled reference), the Left variant and LinearSearch at real-image sizes, the wide-image fallback of the
+smoothing raster pass, and the lifetime of the left-referenced map of the LR check."""
+import numpy as np
+import pytest
+
+from refdata import load_pair
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def sr():
+    import stereo_reconstruction_b200 as s
+    return s
+
+
+@pytest.fixture(scope="module")
+def ctx(sr):
+    return sr.capi.default_context()
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_varblock_random_vs_literal_oracle(sr, ctx, orc, seed):
+    """varBlock (BlockSearch.cpp:125-145): smooth content so that windows grow, thresholds from 'never grows' to 'grows
+    until the window is the whole image'; the map AND the printed max block size must equal the literal restatement."""
+    rng = np.random.default_rng(9000 + seed)
+    h, w = int(rng.integers(14, 40)), int(rng.integers(30, 90))
+    base = rng.integers(0, 256, (h // 4 + 2, w // 4 + 2, 3)).astype(np.float32)
+    R = np.kron(base, np.ones((4, 4, 1), np.float32))[:h, :w] + rng.integers(0, [2, 6, 30][seed % 3], (h, w, 3))
+    R = np.clip(R, 1, 255).astype(np.uint8)
+    L = np.clip(np.roll(R, 3, axis=1).astype(np.int32) + rng.integers(-2, 3, R.shape), 1, 255).astype(np.uint8)
+    if seed % 4 == 0:
+        R[3:6, 5:9] = 0                                      # black pixels are skipped before the growth loop
+    thres = [5.0, 19.0, 60.0, 150.0, 400.0, 2000.0][seed % 6]
+    block = int(rng.choice([3, 5, 9, 17]))
+    smooth = float(rng.choice([1.0, 0.9]))
+    D = int(rng.integers(4, 16))
+    want, mb = orc.block_search_right(L, R, block, 0, D, smooth, True, thres, return_max_block=True)
+    bs = sr.BlockSearch(L, R, block, 0, D, ctx=ctx)
+    got = bs.computeDisparityMapRight(smooth, True, thres)
+    np.testing.assert_array_equal(got, want)
+    assert bs.maxBlockSize == mb
+    if thres >= 2000.0:
+        assert mb >= 2 * max(h, w) - 8                       # the window grew to the whole image and stopped there
+
+
+def test_left_variant_on_a_middeval_pair(sr, ctx, orc):
+    """computeDisparityMapLeft (BlockSearch.cpp:24-86) on ArtL at its shipped size (694x554), smooth 0.9: the genuine
+    raster dependency across a whole image, against the literal oracle (O(window), a few seconds of CPU)."""
+    L, R = load_pair("middeval", "ArtL")
+    L, R = np.ascontiguousarray(L[:200]), np.ascontiguousarray(R[:200])   # 200 rows keep the literal oracle at ~5 s
+    for block, max_d, smooth in ((9, 64, 0.9), (5, 32, 1.0)):
+        want = orc.block_search_left(L, R, block, max_d, smooth)
+        got = sr.BlockSearch(L, R, block, 0, max_d, ctx=ctx).computeDisparityMapLeft(smooth)
+        np.testing.assert_array_equal(got, want)
+
+
+def test_linear_search_on_a_rectified_pair(sr, ctx, orc):
+    """LinearSearch(leftRect, rightRect).computeDisparityMap(1.0) as rectification_main.cpp:194-195 calls it, on the
+    reference's own rectified Teddy pair (candidates clamped to k < w1 where the reference reads out of bounds)."""
+    L, R = load_pair("rectified", "Teddy")
+    for smooth in (1.0, 0.9):
+        want = orc.linear_search(L, R, smooth)
+        got = sr.LinearSearch(L, R, ctx=ctx).computeDisparityMap(smooth)
+        np.testing.assert_array_equal(got, want)
+
+
+def test_smoothing_rule_on_a_very_wide_image(sr, ctx, orc):
+    """w2 > 8192 takes smooth_raster_kernel (more than 256 words per row) instead of the single-warp raster kernels."""
+    w, h, D = 8320, 24, 16
+    L, R = orc.synth_pair(0xB200, 9, w, h, 0, D)
+    R[5:9, 4000:4100] = 0
+    for smooth in (0.9, 1.3):
+        want = orc.block_search_right_fast(L, R, 9, 0, D, smooth)
+        got = sr.BlockSearch(L, R, 9, 0, D, ctx=ctx).computeDisparityMapRight(smooth)
+        np.testing.assert_array_equal(got, want)
+
+
+def test_left_map_of_lr_check_survives_other_searches(sr, ctx, orc):
+    """sr_search_left_disparity returns the map of THIS pair's last lr_check run even after searches on other pairs of
+    the same context (the buffer belongs to the pair, not to the context's shared scratch)."""
+    capi = sr.capi
+    w, h, D = 300, 90, 24
+    L, R = orc.synth_pair(0xB200, 11, w, h, 0, D)
+    a = capi.Pair(ctx, w, h, w, h); a.upload(L, R)
+    p = capi.search_params(block=9, min_disp=0, max_disp=D, smooth=1.0, lr_check=True)
+    a.run(p)
+    want, _, _ = orc.search_ext_fast(L, R, 9, 0, D, orc.COST_SSD_L2, left_ref=True)
+    L2, R2 = orc.synth_pair(0xB200, 12, 2 * w, 2 * h, 0, D)
+    b = capi.Pair(ctx, 2 * w, 2 * h, 2 * w, 2 * h); b.upload(L2, R2)
+    b.run(p)                                                   # larger pair: regrows the shared scratch
+    sr.BlockSearch(L2, R2, 9, 0, D, ctx=ctx).computeDisparityMapLeft(0.9)   # uses the same scratch slots
+    np.testing.assert_array_equal(a.left_disparity(), want)
+    a.close(); b.close()

@@ -1,11 +1,14 @@
 """Parity of the CUDA WindowSearch path (through the C-ABI) with the CPU oracle and the committed
 cv2-executed golden vectors.  Bar: bit-exact (integer disparities stored as CV_64F)."""
+import os
+
 import numpy as np
 import pytest
 
 from conftest import golden_cases
 
 pytestmark = pytest.mark.gpu
+os.environ.setdefault("SR_PEER_TIMEOUT_MS", "400")   # band-gather waits give up quickly in the protocol tests (default 10 s)
 
 
 @pytest.fixture(scope="module")
@@ -242,48 +245,82 @@ def test_host_register_enables_the_pipeline(sr, ctx, orc, monkeypatch):
             capi.host_unregister(a)
 
 
-@pytest.mark.parametrize("w", [404, 403])       # rows that start on / off the 4-element store alignment
+@pytest.mark.parametrize("w", [404, 403])       # even width: fused wire-format resolve; odd: search + push kernel
 def test_peer_memory_band_gather_protocol(sr, orc, w):
     """Band gather over peer memory (capi_peer.cu) with the peers standing in as pair objects of one process:
-    three "ranks" search their bands, ranks 1 and 2 push int16 rows into the root's window, the root collects.
-    Several steps on changing images exercise the step flags and the acknowledgement that guards the window."""
+    three "ranks" search their bands, ranks 1 and 2 store int16 rows into the root's window, the root collects.
+    Several steps on changing images exercise the step flags and the acknowledgement that guards the window; then a
+    failing step (sticky status on every rank, no acknowledgement) and a second generation on the same pairs."""
     capi = sr.capi
     h, D, block, world = 157, 24, 7, 3
     ctxs = [capi.Context(0) for _ in range(world)]
     pairs = [capi.Pair(c, w, h, w, h) for c in ctxs]
     p = capi.search_params(block=block, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD)
+
+    def step(seq, fused):
+        L, R = synth(orc, w, h, 0, D, seed=40 + seq)
+        if seq == 2:
+            R[50:60, 100:140] = 0                      # black pixels: 0.0 in the map
+        want = orc.block_search_right_fast(L, R, block, 0, D, 1.0, cost=1)   # holds negative entries (-x) too
+        for r in range(world):
+            pairs[r].upload(L, R)
+        # pushes first: on one GPU the collect kernel's waiting blocks would otherwise keep the SMs busy
+        for r in (2, 1):
+            r0, r1 = capi.band_rows(h, r, world)
+            if fused:
+                n0 = ctxs[r].launches
+                pairs[r].run_push(p, r0, r1, r, seq)   # the resolve pass writes the wire format and publishes the step
+                fused_launches = ctxs[r].launches - n0
+            else:
+                pairs[r].run(p, r0, r1)
+                pairs[r].push_band(r0, r1, r, seq)
+        pairs[0].run(p, *capi.band_rows(h, 0, world))
+        pairs[0].collect_bands(world, seq)
+        np.testing.assert_array_equal(pairs[0].download(p), want, err_msg=f"step {seq}")
+        return fused_launches if fused else None
+
     try:
         handle = pairs[0].peer_export()
         assert len(handle) == 64
         for r in (1, 2):
             pairs[r].peer_attach_local(pairs[0])
-        for seq in (1, 2, 3):
-            L, R = synth(orc, w, h, 0, D, seed=40 + seq)
-            if seq == 2:
-                R[50:60, 100:140] = 0                      # black pixels: 0.0 in the map
-            want = orc.block_search_right_fast(L, R, block, 0, D, 1.0, cost=1)   # holds negative entries (-x) too
-            for r in range(world):
-                pairs[r].upload(L, R)
-                r0, r1 = capi.band_rows(h, r, world)
-                pairs[r].run(p, r0, r1)
-            # pushes first: on one GPU the collect kernel's waiting blocks would otherwise keep the SMs busy
-            for r in (2, 1):
-                r0, r1 = capi.band_rows(h, r, world)
-                pairs[r].push_band(r0, r1, r, seq)
-            pairs[0].collect_bands(world, seq)
-            np.testing.assert_array_equal(pairs[0].download(p), want, err_msg=f"step {seq}")
-        # step 4: rank 1 pushes values outside the int16 wire format (a sub-pixel map) -> refused on rank 1;
-        # rank 2's band never arrives -> the root's collect kernel gives up instead of hanging, the download reports it
+        step(1, False)
+        n_fused = step(2, True)
+        step(3, True)
+        # memset is not a kernel: search + (wait-ack + wire resolve) when fused, search + resolve + push otherwise
+        assert n_fused == 3
+        # step 4: rank 1 holds values outside the int16 wire format (a sub-pixel map) -> refused on rank 1, never
+        # published; rank 2 stays silent -> the root's collect kernel gives up instead of hanging and does NOT
+        # acknowledge the step; every later call on the failed ranks reports the (sticky) failure
         ps = capi.search_params(block=block, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD, subpixel=True)
         pairs[1].run(ps)
         pairs[1].push_band(0, h, 1, 4)
         with pytest.raises(capi.SrError) as e:
-            pairs[1].download(ps)
+            pairs[1].peer_status()
         assert e.value.code == capi.E_BADARG
+        with pytest.raises(capi.SrError):
+            pairs[1].push_band(0, h, 1, 5)             # sticky
+        with pytest.raises(capi.SrError):
+            ctxs[1].sync()                             # and visible at the context's synchronisation
         pairs[0].run(p, *capi.band_rows(h, 0, world))
         pairs[0].collect_bands(world, 4)
         with pytest.raises(capi.SrError, match="did not arrive"):
             pairs[0].download(p)
+        with pytest.raises(capi.SrError, match="did not arrive"):
+            pairs[0].collect_bands(world, 5)           # sticky on the root as well
+        # rank 2 was never told that step 4 failed; its next push waits for an acknowledgement that never comes
+        r0, r1 = capi.band_rows(h, 2, world)
+        pairs[2].run(p, r0, r1)
+        pairs[2].push_band(r0, r1, 2, 5)
+        with pytest.raises(capi.SrError, match="did not arrive"):
+            pairs[2].peer_status()
+        # a second generation on the same pairs: export again (header and status reset), attach again, steps restart at 1
+        pairs[0].peer_export()
+        for r in (1, 2):
+            pairs[r].peer_detach()
+            pairs[r].peer_attach_local(pairs[0])
+        step(1, True)
+        step(2, False)
     finally:
         for r in (1, 2):
             pairs[r].peer_detach()

@@ -118,7 +118,7 @@ def test_shim_caller_equals_reference_caller(tmp_path, orc):
         logs[tag] = r.stdout
         outs[tag] = {f: open(os.path.join(root, "out", f), "rb").read() for f in sorted(os.listdir(root / "out")) if os.path.isfile(root / "out" / f)}
         outs[tag]["reconstruction_mesh.off"] = open(root / "results" / "reconstruction_mesh.off", "rb").read()
-    assert sorted(outs["ref"]) == sorted(outs["b200"]) and len(outs["ref"]) == 11
+    assert sorted(outs["ref"]) == sorted(outs["b200"]) and len(outs["ref"]) == 10
     for f in outs["ref"]:
         assert outs["ref"][f] == outs["b200"][f], f"{f} differs between the reference build and the shim build"
     assert logs["ref"] == logs["b200"]                              # "max block size: ..", "h1:..", "h2:..", "Failed to write mesh!" lines
