@@ -243,7 +243,7 @@ def run_reference(args, rank, world):
             "config": config_for(args, world), "cpu_baseline": cpu,
             "e2e": {"value": val, "unit": "MDE/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def recon_roofline(ctx, pair, w, h, iters=5):
@@ -310,8 +310,26 @@ def cpu_baseline(args, L, R, w, h, D, block, cost):
     return out
 
 
+def emit(line):
+    """The ONE JSON line of this run goes to the real stdout; everything else that writes to fd 1 (NCCL's version banner,
+    library chatter) was sent to stderr by quiet_stdout()."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
+def quiet_stdout():
+    global _REAL_STDOUT
+    if _REAL_STDOUT == 1:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
 def main():
     args = parse()
+    quiet_stdout()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -354,7 +372,7 @@ def main():
     total_evals = synth.effective_evals(w, w, h, block, 0, D)
     # band gather: stores into rank 0's HBM over NVLink (capi_peer.cu); NCCL point-to-point where peer mapping fails
     peer = None
-    if world > 1 and os.environ.get("SR_GATHER", "peer") != "nccl":
+    if world > 1 and os.environ.get("SR_GATHER", "peer") != "nccl":   # "peer" (default), "peer2" (two-kernel form), "nccl"
         try:
             peer = sharding.PeerGather(pair, h, rank, world)
         except RuntimeError as e:
@@ -378,8 +396,13 @@ def main():
         if world > 1:
             dist.barrier()
 
+    two_kernel = os.environ.get("SR_GATHER") == "peer2"   # development: search + separate push kernel (round-1 form)
+
     def step_resident():
-        if peer is not None:
+        if peer is not None and two_kernel:
+            pair.run(params, r0, r1)
+            peer.gather()
+        elif peer is not None:
             peer.run_and_gather(params)      # ranks > 0: the resolve pass stores the int16 wire format into rank 0's window
         else:
             pair.run(params, r0, r1)
@@ -428,8 +451,14 @@ def main():
     for _ in range(max(args.warmup, 3)):
         ctx.l2_flush()                       # warm-up steps look exactly like timed steps (first flush allocates)
         step_resident()
-    launches0 = ctx.launches
     barrier()
+    if world > 1:
+        # The ranks leave the host-side barrier up to ~1 ms apart; rank 0's first step would wait that long for the other
+        # ranks' bands (measured: 1.73 ms against 0.92 ms for every later step at N=2).  One untimed step lets the gather's
+        # flag / acknowledgement words pull the ranks into step; the K timed steps follow.
+        ctx.l2_flush()
+        step_resident()
+    launches0 = ctx.launches
     step_ms, kern_ms = [], []
     for _ in range(args.steps):
         ctx.l2_flush()                       # between timed iterations: write 384 MB > 126 MB L2
@@ -555,7 +584,7 @@ def main():
                 line["roofline_recon"] = {"error": str(e)}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, L, R, w, h, D, block, cost)
-        print(json.dumps(line), flush=True)
+        emit(line)
     barrier()
     capi.free_pinned(lp_h); capi.free_pinned(rp_h); capi.free_pinned(out_h)
     if world > 1:
@@ -604,22 +633,24 @@ def run_batch(args, rank, world, local_rank):
         if world > 1:
             dist.barrier()
 
-    # device-resident leg: the same n pairs' kernels on one resident pair
-    pair = capi.Pair(ctx, w, h, w, h); pair.upload(Ls[0], Rs[0])
+    # device-resident leg: the n pairs' kernels on resident pairs, 8 per tile-kernel launch (sr_search_run_batch)
+    res = [capi.Pair(ctx, w, h, w, h) for _ in range(ring)]
+    for i, q in enumerate(res):
+        q.upload(Ls[i], Rs[i])
     sampler = ClockSampler(local_rank) if rank == 0 else None
     for _ in range(max(args.warmup, 3)):
-        pair.run(p)
+        capi.search_run_batch(ctx, res, p)
     l0 = ctx.launches
     barrier()
     ctx.timer_start()
     for _ in range(args.steps):
-        for _ in range(n):
-            pair.run(p)
+        for i0 in range(0, n, ring):
+            capi.search_run_batch(ctx, res[:min(ring, n - i0)], p)
     dev_ms = ctx.timer_stop()
     launches = ctx.launches - l0
     barrier()
     for _ in range(2):
-        capi.block_search_batch(ctx, lb[:ring], rb[:ring], p, ob[:ring])
+        capi.block_search_batch(ctx, lb, rb, p, ob)       # same path as the timed calls (the first one builds the ring of pairs)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
@@ -642,7 +673,7 @@ def run_batch(args, rank, world, local_rank):
                         "h2d_bytes_per_step": int(n * 2 * w * h * 3), "d2h_bytes_per_step": int(n * w * h * 8),
                         "api": "sr_block_search_batch (pinned host buffers)"},
                 "gpu_launches": int(launches), "kernel_family": ctx.last_kernel, "clocks": clocks, "roofline": None}
-        print(json.dumps(line), flush=True)
+        emit(line)
     barrier()
     for x in hs:
         capi.free_pinned(x)

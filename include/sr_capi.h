@@ -127,6 +127,10 @@ int sr_pair_upload(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_im
  * row-band sharding -- a band needs smooth == 1). */
 int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1);
 int sr_search_download(sr_ctx* ctx, sr_pair* pair, double* disp_out, size_t out_pitch, int row0, int row1);
+/* The same for n uploaded pairs (config 5: batches of small pairs): pairs of one shape share ONE launch of the fused
+ * cost + WTA kernel in groups of up to 16 (a 1280x720 / 128-disparity pair alone gives 148 SMs too few work items),
+ * where the request allows it (Right variant, SSD / SAD, plain or sub-pixel result); results as sr_search_run per pair. */
+int sr_search_run_batch(sr_ctx* ctx, sr_pair* const* pairs, int n, const sr_search_params* p);
 /* One rank's share of a row-band sharded pair, from host images (north_star: "by row bands with halo
  * rows for single very large pairs"): uploads only the image rows that output rows [row0,row1) and their
  * window halo read, searches the band and -- when disp_out is not NULL -- downloads it to rows

@@ -54,7 +54,7 @@ SYMBOLS = [
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
     "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
     "sr_search_kernel_ms", "sr_int_peak", "sr_pair_reconstruct_warp", "sr_average_disparity", "sr_pfm_info", "sr_read_pfm",
-    "sr_read_calib", "sr_search_run_push", "sr_pair_peer_status",
+    "sr_read_calib", "sr_search_run_push", "sr_pair_peer_status", "sr_search_run_batch",
 ]
 
 _lib = None
@@ -327,6 +327,12 @@ def search_params(variant=VARIANT_RIGHT, block=17, min_disp=0, max_disp=200, smo
                   thres=19.0, cost=COST_SSD_L2, subpixel=False, lr_check=False):
     return SrSearchParams(int(variant), int(block), int(min_disp), int(max_disp), float(smooth), int(bool(var_block)),
                           float(thres), int(cost), int(bool(subpixel)), int(bool(lr_check)))
+
+
+def search_run_batch(ctx, pairs, params):
+    """sr_search_run_batch: kernels of n uploaded pairs, one tile-kernel launch per group of up to 16 pairs of one shape."""
+    arr = (C.c_void_p * len(pairs))(*[q.h for q in pairs])
+    ctx.check(ctx._l.sr_search_run_batch(ctx.h, arr, len(pairs), C.byref(params)))
 
 
 def block_search(ctx, left, right, params, out=None, return_max_block=False):

@@ -1,6 +1,7 @@
 // capi_recon.cu -- Reconstruction entry points of the C-ABI: host-pointer wrappers around recon.cu.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 #include "recon.cuh"
@@ -98,6 +99,32 @@ int sr_mesh_faces(sr_ctx* ctx, const sr_vertex* v, int w, int h, float thr, uint
     return sr_ctx_sync(ctx);
 }
 
+// sr_pair_reconstruct(_warp) with the 8-bit hand-off, outlier removal and a face count / list wanted: the integer-exact
+// pipeline of recon.cu (four launches, the float map is only formed when the caller wants it back)
+static int reconstruct_device_u8(sr_ctx* ctx, const double* d_disp64, const uint8_t* d_bgr, int w, int h, int ksize, float thr_front,
+                                 float thr_back, float focal, float baseline, float fx, float fy, float cx, float cy, float thr_mesh,
+                                 float* disp_filtered, float* depth, sr_vertex* vertices, uint32_t* tri, uint32_t* n_faces) {
+    size_t n = (size_t)w * h;
+    size_t cells = (size_t)(w - 1) * (h - 1);
+    float* d_disp = disp_filtered ? (float*)sr_scratch(ctx, SL_DISP, n * 4) : nullptr;
+    float* d_depth = (float*)sr_scratch(ctx, SL_DEPTH, n * 4);
+    sr_vertex* d_v = (sr_vertex*)sr_scratch(ctx, SL_VERT, n * sizeof(sr_vertex));
+    uint32_t* d_t = tri ? (uint32_t*)sr_scratch(ctx, SL_TRI, (cells ? cells : 1) * 6 * 4) : nullptr;
+    if ((disp_filtered && !d_disp) || !d_depth || !d_v || (tri && !d_t)) return SR_E_CUDA;
+    TRY(recon_u8_pipeline(ctx, d_disp64, d_bgr, (size_t)w * 3, w, h, ksize, thr_front, thr_back, focal, baseline, fx, fy, cx, cy, thr_mesh,
+                          d_disp, d_depth, d_v));
+    if (disp_filtered) TRY(down2d(ctx, disp_filtered, (size_t)w * 4, d_disp, (size_t)w * 4, (size_t)w * 4, h));
+    if (depth) TRY(down2d(ctx, depth, (size_t)w * 4, d_depth, (size_t)w * 4, (size_t)w * 4, h));
+    if (vertices) SR_CUDA(ctx, cudaMemcpyAsync(vertices, d_v, n * sizeof(sr_vertex), cudaMemcpyDeviceToHost, ctx->stream));
+    TRY(recon_mesh_faces(ctx, nullptr, w, h, thr_mesh, d_t, n_faces));
+    if (tri && *n_faces) SR_CUDA(ctx, cudaMemcpyAsync(tri, d_t, (size_t)*n_faces * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    return sr_ctx_sync(ctx);
+}
+static bool use_u8_pipeline(int quantize_u8, int ksize, const uint32_t* n_faces, int w, int h) {
+    const char* off = getenv("SR_RECON_GENERAL");   // test hook: force the general kernels (read per call)
+    return quantize_u8 && ksize > 0 && n_faces && !(off && atoi(off)) && recon_u8_pipeline_applies(w, h, ksize);
+}
+
 // shared tail of sr_reconstruct / sr_pair_reconstruct: d_disp (device, tight) -> outputs
 static int reconstruct_device(sr_ctx* ctx, float* d_disp, const uint8_t* d_bgr, int w, int h, int ksize, float thr_front,
                               float thr_back, float focal, float baseline, float fx, float fy, float cx, float cy,
@@ -146,6 +173,9 @@ int sr_pair_reconstruct(sr_ctx* ctx, sr_pair* pair, int quantize_u8, int ksize, 
     SR_CUDA(ctx, cudaSetDevice(ctx->device));
     int w = pair->ow, h = pair->oh;
     size_t n = (size_t)w * h;
+    if (use_u8_pipeline(quantize_u8, ksize, n_faces, w, h))
+        return reconstruct_device_u8(ctx, pair->out, pair->rawR, w, h, ksize, thr_front, thr_back, focal, baseline, fx, fy, cx, cy, thr_mesh,
+                                     disp_filtered, depth, vertices, tri, n_faces);
     float* d = (float*)sr_scratch(ctx, SL_DISP, n * 4);
     if (!d) return SR_E_CUDA;
     TRY(recon_quantize(ctx, pair->out, d, n, quantize_u8));   // main.cpp:41-50 (8-bit hand-off) or plain cast
@@ -175,6 +205,9 @@ int sr_pair_reconstruct_warp(sr_ctx* ctx, sr_pair* pair, const double M[9], int 
     }
     TRY(sr_launch_warp_nearest(ctx, pair->out, pair->ow, pair->oh, dwarp, dw, dh, M));   // rectification.cpp:82-87
     if (disp_warped) SR_CUDA(ctx, cudaMemcpyAsync(disp_warped, dwarp, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (use_u8_pipeline(quantize_u8, ksize, n_faces, dw, dh))
+        return reconstruct_device_u8(ctx, dwarp, d_bgr, dw, dh, ksize, thr_front, thr_back, focal, baseline, fx, fy, cx, cy, thr_mesh,
+                                     disp_filtered, depth, vertices, tri, n_faces);
     TRY(recon_quantize(ctx, dwarp, d, n, quantize_u8));                                   // main.cpp:41-50
     return reconstruct_device(ctx, d, d_bgr, dw, dh, ksize, thr_front, thr_back, focal, baseline, fx, fy, cx, cy, thr_mesh,
                               disp_filtered, depth, vertices, tri, n_faces, quantize_u8 != 0);

@@ -295,6 +295,46 @@ static int block_search_pipelined(sr_ctx* ctx, sr_pair* pair, const sr_image* le
     return SR_OK;
 }
 
+// n pairs of one shape, whole maps, ONE tile-kernel launch (sr_launch_search_tile_multi), then per pair the resolve pass
+// or the sub-pixel pass.  Returns 1 when done, 0 when the request needs the per-pair path (nothing was launched), < 0 on
+// error.  Same results as sr_search_run on each pair.
+int sr_search_run_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const sr_search_params* p) {
+    if (n < 2 || n > 16 || p->variant != SR_VARIANT_RIGHT || p->var_block || p->lr_check || p->min_disp < 0) return 0;
+    if (p->cost != SR_COST_SSD_L2 && p->cost != SR_COST_SAD) return 0;
+    if (p->subpixel ? (!sr_ext_subpix_out_applies(p) || p->smooth != 1.0) : (p->smooth != 1.0 && p->min_disp == 0)) return 0;
+    sr_pair* p0 = pairs[0];
+    for (int q = 1; q < n; q++)
+        if (pairs[q]->w1 != p0->w1 || pairs[q]->h1 != p0->h1 || pairs[q]->w2 != p0->w2 || pairs[q]->h2 != p0->h2) return 0;
+    SearchGeom g;
+    g.w1 = p0->w1; g.h1 = p0->h1; g.w2 = p0->w2; g.h2 = p0->h2;
+    g.height = g.h1 < g.h2 ? g.h1 : g.h2;
+    g.block = p->block; g.half = (p->block - 1) / 2;
+    g.dlo = p->min_disp; g.dhi = p->max_disp;
+    if (g.dhi > g.w1) g.dhi = g.w1;
+    if (g.dhi < g.dlo) g.dhi = g.dlo;
+    g.row0 = 0; g.row1 = g.h2;
+    if (g.half < 1 || g.half > 8 || g.w2 == 1 || g.h2 == 1 || !rows_fit(g.h1, g.h2, g.half)) return 0;
+    for (int q = 0; q < n; q++) {
+        sr_pair* pair = pairs[q];
+        pair->evals_valid = false;
+        pair->disp_left = nullptr;
+        int init0[2] = {p->block, SR_OK};
+        SR_CUDA(ctx, cudaMemcpyAsync(pair->maxblock, init0, sizeof init0, cudaMemcpyHostToDevice, ctx->stream));
+        pair->ow = g.w2; pair->oh = g.h2;
+        pair->last_row0 = 0; pair->last_row1 = g.h2;
+    }
+    int handled = sr_launch_search_tile_multi(ctx, pairs, n, g, p->cost);
+    if (handled <= 0) return handled;
+    for (int q = 0; q < n; q++) {
+        int rc = p->subpixel ? sr_launch_ext_subpix_out(ctx, pairs[q], p, 0, g.h2) : sr_launch_resolve_right(ctx, pairs[q], g, 1.0, 0, 0);
+        if (rc != SR_OK) return rc;
+        pairs[q]->last_geom = g;
+        pairs[q]->evals_valid = !p->subpixel;
+    }
+    ctx->last_kernel = p->subpixel ? "tile+ext" : "tile";
+    return 1;
+}
+
 extern "C" {
 
 int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1) {
@@ -387,6 +427,27 @@ int sr_search_run_push(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, in
     pair->wire_rank = 0; pair->wire_seq = 0; pair->wire_done = false;
     if (rc != SR_OK) return rc;
     return done ? SR_OK : sr_search_push_band(ctx, pair, row0, row1, rank, seq);
+}
+
+// Device-resident batch form: kernels only, asynchronous on the context stream, results stay in HBM.  Pairs of one shape
+// in groups of up to 16 share ONE tile-kernel launch where the request allows it (Right variant, SSD / SAD, plain or
+// sub-pixel result); otherwise each pair runs sr_search_run.
+int sr_search_run_batch(sr_ctx* ctx, sr_pair* const* pairs, int n, const sr_search_params* p) {
+    if (!ctx || !pairs || !p || n < 0) return sr_fail(ctx, SR_E_BADARG, "sr_search_run_batch: bad argument");
+    for (int i = 0; i < n; i++) { int rc = validate(ctx, pairs[i], p); if (rc != SR_OK) return rc; }
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    for (int i0 = 0; i0 < n; i0 += 16) {
+        int cnt = n - i0 < 16 ? n - i0 : 16;
+        int done = cnt >= 2 ? sr_search_run_multi(ctx, pairs + i0, cnt, p) : 0;
+        if (done < 0) return done;
+        if (!done)
+            for (int j = 0; j < cnt; j++) {
+                int oh = p->variant == SR_VARIANT_LEFT ? pairs[i0 + j]->h1 : pairs[i0 + j]->h2;
+                int rc = sr_search_run(ctx, pairs[i0 + j], p, 0, oh);
+                if (rc != SR_OK) return rc;
+            }
+    }
+    return SR_OK;
 }
 
 void* sr_search_result_dev(sr_ctx* ctx, sr_pair* pair) { return pair ? (void*)pair->out : nullptr; }

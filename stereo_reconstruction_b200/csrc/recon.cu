@@ -437,8 +437,28 @@ __global__ void __launch_bounds__(FACE_THREADS) face_count_kernel(Pos pos, int w
 // cell_flags() on the stored vertices.
 #define DBF_T 128
 #define DBF_ROWS 16
+// where the disparity of a pixel comes from: a float map, or -- the 8-bit hand-off with removeDisparityOutliers -- the
+// u8 map and the int32 column prefixes of its row window sums (recon_u8_pipeline below): the blurred value and the
+// outlier rule (reconstruction.cpp:8-17) are evaluated on the fly, the filtered map is stored only when asked for
+struct DispFromMap {
+    const float* disp;
+    __device__ __forceinline__ float operator()(int x, int y, int w) const { return disp[(size_t)y * w + x]; }
+};
+struct DispFromU8Blur {
+    const uint8_t* q8; const int* pe; int k; double scale; float thr_front, thr_back; float* disp_out;
+    __device__ __forceinline__ float operator()(int x, int y, int w) const {
+        const size_t i = (size_t)y * w + x;
+        const int hi = pe[(size_t)(y + k - 1) * w + x], lo = y > 0 ? pe[(size_t)(y - 1) * w + x] : 0;
+        const float b = (float)((double)(hi - lo) * scale);   // ColumnSum<double,float>: (float)(sum * 1/(k*k)), sum exact
+        const float d = (float)q8[i];
+        const float v = (d > thr_front * b || d < thr_back * b) ? b : d;
+        if (disp_out) disp_out[i] = v;
+        return v;
+    }
+};
+template <class Disp>
 __global__ void __launch_bounds__(DBF_T) depth_backproject_faces_kernel(
-    const float* __restrict__ disp, const uint8_t* __restrict__ bgr, size_t bgr_pitch, int w, int h, float focal,
+    Disp disp, const uint8_t* __restrict__ bgr, size_t bgr_pitch, int w, int h, float focal,
     float baseline, float fx, float fy, float cx, float cy, float thr, float* __restrict__ depth_out,
     sr_vertex* __restrict__ vert, uint8_t* __restrict__ flags) {
     __shared__ float4 spos[2][DBF_T];
@@ -451,7 +471,7 @@ __global__ void __launch_bounds__(DBF_T) depth_backproject_faces_kernel(
     float dn = 0.f;
     uint32_t cn = 0;
     if (incol) {
-        dn = disp[(size_t)y0 * w + x];
+        dn = disp(x, y0, w);
         const uint8_t* p = bgr + (size_t)y0 * bgr_pitch + 3 * (size_t)x;
         cn = (uint32_t)p[2] | ((uint32_t)p[1] << 8) | ((uint32_t)p[0] << 16) | 0xFF000000u;
     }
@@ -463,7 +483,7 @@ __global__ void __launch_bounds__(DBF_T) depth_backproject_faces_kernel(
         const float d = dn;
         const uint32_t colour = cn;
         if (incol && r < DBF_ROWS && y + 1 < h) {            // prefetch the next row
-            dn = disp[(size_t)(y + 1) * w + x];
+            dn = disp(x, y + 1, w);
             const uint8_t* p = bgr + (size_t)(y + 1) * bgr_pitch + 3 * (size_t)x;
             cn = (uint32_t)p[2] | ((uint32_t)p[1] << 8) | ((uint32_t)p[0] << 16) | 0xFF000000u;
         }
@@ -655,8 +675,127 @@ int recon_depth_backproject_faces(sr_ctx* ctx, const float* d_disp, const uint8_
     uint8_t* flags = face_buffers(ctx, ncells, nblocks, &block_total);
     if (!flags) return SR_E_CUDA;
     dim3 grid(cdiv(w, DBF_T - 1), cdiv(h, DBF_ROWS));
-    depth_backproject_faces_kernel<<<grid, DBF_T, 0, ctx->stream>>>(d_disp, d_bgr, bgr_pitch, w, h, focal, baseline, fx, fy, cx, cy,
-                                                                    thr, d_depth_out, d_vert, flags);
+    depth_backproject_faces_kernel<DispFromMap><<<grid, DBF_T, 0, ctx->stream>>>(DispFromMap{d_disp}, d_bgr, bgr_pitch, w, h, focal, baseline,
+                                                                                 fx, fy, cx, cy, thr, d_depth_out, d_vert, flags);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
+// ---- main.cpp:41-65 for the 8-bit hand-off, integer-exact ----------------------------------------------------------
+// After the PNG hand-off every disparity is an integer 0..255, so every sum cv::blur forms is an integer far below 2^31
+// (a window holds at most 255 k^2, a column prefix at most 255 k (h + k - 1)): the whole box filter runs in int32 --
+// half the bytes of the fp64 prefix path, exact by construction (no proof kernel) -- and the last step,
+// (float)((double)sum * (1/(k*k))), is the one OpenCV performs.  Four launches instead of nine:
+//   u8_rowsum_kernel     CV_64F map -> u8 map (rint half-even, saturate) + row window sums (one CTA per row, prefix in smem)
+//   blur_cols_seg/prefix column prefixes of the row sums (int32)
+//   depth_backproject_faces_kernel<DispFromU8Blur>   blurred value + outlier rule + depth + vertex + face flags
+// ~75 B/pixel of traffic against ~125 through the general kernels.
+#define U8R_T 512
+__global__ void __launch_bounds__(U8R_T) u8_rowsum_kernel(const double* __restrict__ src, int w, int h, int k, uint8_t* __restrict__ q8,
+                                                          int* __restrict__ rows) {
+    extern __shared__ int pi[];                  // w + k - 1 prefix values of the reflect-101 extended row
+    __shared__ int wsum[U8R_T / 32];
+    const int y = blockIdx.x, t = threadIdx.x, a = k / 2, we = w + k - 1;
+    const double* sr = src + (size_t)y * w;
+    // quantise the row once (main.cpp:41-50), staged at its place inside the extended row
+    for (int x = t; x < w; x += U8R_T) {
+        const double v = sr[x];
+        long long q = (v != v) ? 0 : __double2ll_rn(fmax(-1e9, fmin(1e9, v)));
+        q = q < 0 ? 0 : (q > 255 ? 255 : q);
+        pi[x + a] = (int)q;
+        q8[(size_t)y * w + x] = (uint8_t)q;
+    }
+    __syncthreads();
+    for (int j = t; j < we; j += U8R_T) {        // the reflected borders (reads of the staged centre part only)
+        const int xs = j - a;
+        if (xs < 0 || xs >= w) pi[j] = pi[reflect101(xs, w) + a];
+    }
+    __syncthreads();
+    const int C = (we + U8R_T - 1) / U8R_T, j0 = min(t * C, we), j1 = min(j0 + C, we);
+    int acc = 0;
+    for (int j = j0; j < j1; j++) { acc += pi[j]; pi[j] = acc; }
+    int v = acc;
+    for (int off = 1; off < 32; off <<= 1) { int u = __shfl_up_sync(0xffffffffu, v, off); if ((t & 31) >= off) v += u; }
+    if ((t & 31) == 31) wsum[t >> 5] = v;
+    __syncthreads();
+    int base = v - acc;
+    for (int i = 0; i < (t >> 5); i++) base += wsum[i];
+    for (int j = j0; j < j1; j++) pi[j] += base;
+    __syncthreads();
+    int* o = rows + (size_t)y * w;
+    for (int x = t; x < w; x += U8R_T) o[x] = pi[x + k - 1] - (x > 0 ? pi[x - 1] : 0);
+}
+#define U8_NSEG 64
+__global__ void u8_cols_seg_kernel(const int* __restrict__ rows, int w, int h, int k, int* __restrict__ seg) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, sgi = blockIdx.y;
+    if (x >= w) return;
+    const int a = k / 2, he = h + k - 1, SL = (he + U8_NSEG - 1) / U8_NSEG;
+    const int j0 = sgi * SL, j1 = min(j0 + SL, he);
+    int a0 = 0, a1 = 0, a2 = 0, a3 = 0, j = j0;
+    for (; j + 3 < j1; j += 4) {
+        a0 += rows[(size_t)reflect101(j - a, h) * w + x]; a1 += rows[(size_t)reflect101(j + 1 - a, h) * w + x];
+        a2 += rows[(size_t)reflect101(j + 2 - a, h) * w + x]; a3 += rows[(size_t)reflect101(j + 3 - a, h) * w + x];
+    }
+    for (; j < j1; j++) a0 += rows[(size_t)reflect101(j - a, h) * w + x];
+    seg[(size_t)sgi * w + x] = (a0 + a1) + (a2 + a3);
+}
+__global__ void u8_cols_prefix_kernel(const int* __restrict__ rows, int w, int h, int k, const int* __restrict__ seg, int* __restrict__ pe) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, sgi = blockIdx.y;
+    if (x >= w) return;
+    const int a = k / 2, he = h + k - 1, SL = (he + U8_NSEG - 1) / U8_NSEG;
+    const int j0 = sgi * SL, j1 = min(j0 + SL, he);
+    int acc = 0;
+    for (int i = 0; i < sgi; i++) acc += seg[(size_t)i * w + x];
+    int j = j0;
+    for (; j + 3 < j1; j += 4) {
+        int r0 = rows[(size_t)reflect101(j - a, h) * w + x], r1 = rows[(size_t)reflect101(j + 1 - a, h) * w + x];
+        int r2 = rows[(size_t)reflect101(j + 2 - a, h) * w + x], r3 = rows[(size_t)reflect101(j + 3 - a, h) * w + x];
+        acc += r0; pe[(size_t)j * w + x] = acc;
+        acc += r1; pe[(size_t)(j + 1) * w + x] = acc;
+        acc += r2; pe[(size_t)(j + 2) * w + x] = acc;
+        acc += r3; pe[(size_t)(j + 3) * w + x] = acc;
+    }
+    for (; j < j1; j++) { acc += rows[(size_t)reflect101(j - a, h) * w + x]; pe[(size_t)j * w + x] = acc; }
+}
+
+// Applies when the sums fit int32 and a row fits shared memory; the caller falls back to the general kernels otherwise.
+bool recon_u8_pipeline_applies(int w, int h, int k) {
+    if (w < 2 || h < 2 || k < 1) return false;
+    if ((size_t)(w + k - 1) * sizeof(int) > 200 * 1024) return false;
+    return 255.0 * k * ((double)h + k - 1) < 2147483647.0 && 255.0 * ((double)w + k - 1) < 2147483647.0;
+}
+int recon_u8_pipeline(sr_ctx* ctx, const double* d_disp64, const uint8_t* d_bgr, size_t bgr_pitch, int w, int h, int k, float thr_front,
+                      float thr_back, float focal, float baseline, float fx, float fy, float cx, float cy, float thr,
+                      float* d_disp_out, float* d_depth_out, sr_vertex* d_vert) {
+    const int he = h + k - 1;
+    const size_t n = (size_t)w * h;
+    // scratch: row sums (slot 1), u8 map (slot 2), prefix array + segment sums (slot 15)
+    int* rows = (int*)sr_scratch(ctx, 1, n * sizeof(int));
+    uint8_t* q8 = (uint8_t*)sr_scratch(ctx, 2, n + 16);
+    int* pe = (int*)sr_scratch(ctx, 15, ((size_t)he * w + (size_t)U8_NSEG * w) * sizeof(int));
+    if (!rows || !q8 || !pe) return SR_E_CUDA;
+    int* seg = pe + (size_t)he * w;
+    unsigned ncells = (unsigned)(w - 1) * (unsigned)(h - 1);
+    unsigned nblocks = (ncells + FACE_THREADS - 1) / FACE_THREADS;
+    uint32_t* block_total = nullptr;
+    uint8_t* flags = face_buffers(ctx, ncells, nblocks, &block_total);
+    if (!flags) return SR_E_CUDA;
+    static DeviceOnce configured;
+    if (configured.need(ctx->device)) {
+        SR_CUDA(ctx, cudaFuncSetAttribute(u8_rowsum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured.done(ctx->device);
+    }
+    u8_rowsum_kernel<<<h, U8R_T, (size_t)(w + k - 1) * sizeof(int), ctx->stream>>>(d_disp64, w, h, k, q8, rows);
+    SR_LAUNCHED(ctx);
+    dim3 gs(cdiv(w, 128), U8_NSEG);
+    u8_cols_seg_kernel<<<gs, 128, 0, ctx->stream>>>(rows, w, h, k, seg);
+    SR_LAUNCHED(ctx);
+    u8_cols_prefix_kernel<<<gs, 128, 0, ctx->stream>>>(rows, w, h, k, seg, pe);
+    SR_LAUNCHED(ctx);
+    DispFromU8Blur src{q8, pe, k, 1.0 / ((double)k * (double)k), thr_front, thr_back, d_disp_out};
+    dim3 grid(cdiv(w, DBF_T - 1), cdiv(h, DBF_ROWS));
+    depth_backproject_faces_kernel<DispFromU8Blur><<<grid, DBF_T, 0, ctx->stream>>>(src, d_bgr, bgr_pitch, w, h, focal, baseline, fx, fy, cx,
+                                                                                    cy, thr, d_depth_out, d_vert, flags);
     SR_LAUNCHED(ctx);
     return SR_OK;
 }

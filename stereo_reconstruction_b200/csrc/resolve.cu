@@ -123,11 +123,17 @@ __global__ void resolve_plain2_kernel(SearchGeom g, int have_c0 /* 0 or 2 */, Pl
 // publishes the step in the root's flag word of this rank (the acknowledgement of the previous step was awaited by a
 // one-thread kernel earlier on the stream, sr_peer_wait_ack).  Values outside int16 (an image wider than 32767 pixels
 // whose "no candidate" value -x does not fit) set the pair's sticky status instead of the flag.
-__global__ void resolve_wire16_kernel(SearchGeom g, Planes pl, const uint32_t* __restrict__ Rp, int pitchR, short* win16,
-                                      volatile unsigned* flags, int rank, unsigned seq, unsigned* counter, int* status) {
-    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
-    const int y = g.row0 + blockIdx.y;
-    if (x < g.w2 && y < g.row1) {
+__global__ void __launch_bounds__(128) resolve_wire16_kernel(SearchGeom g, Planes pl, const uint32_t* __restrict__ Rp, int pitchR,
+                                                             short* win16, volatile unsigned* flags, int rank, unsigned seq,
+                                                             unsigned* counter, int* status) {
+    // a few resident CTAs per SM walk the (row, 256-pixel segment) tiles: ONE system-scope fence per CTA at the end (a
+    // fence waits for the NVLink write acknowledgements; one per 128-thread tile made the kernel latency-bound)
+    const int segs = (g.w2 + 255) / 256, rows = g.row1 - g.row0;
+    int bad = 0;
+    for (int tile = blockIdx.x; tile < segs * rows; tile += gridDim.x) {
+        const int x = 2 * ((tile % segs) * 128 + threadIdx.x);
+        const int y = g.row0 + tile / segs;
+        if (x >= g.w2) continue;
         const size_t i = (size_t)y * g.w2 + x;
         const bool yin = y < g.height;
         const uint2 px2 = yin ? __ldg(reinterpret_cast<const uint2*>(Rp + (size_t)y * pitchR + x)) : make_uint2(0u, 0u);
@@ -155,14 +161,15 @@ __global__ void resolve_wire16_kernel(SearchGeom g, Planes pl, const uint32_t* _
             else if (n == 0) v[e] = 0 - xe;
             else if (bc[e] != 0xFFFFFFFFu) v[e] = bd[e];
             else v[e] = 0 - xe;
-            if (v[e] < -32768 || v[e] > 32767) { *status = SR_E_BADARG; v[e] = 0; }
+            if (v[e] < -32768 || v[e] > 32767) { bad = 1; v[e] = 0; }
         }
         *reinterpret_cast<short2*>(win16 + i) = make_short2((short)v[0], (short)v[1]);
     }
+    if (bad) *status = SR_E_BADARG;
     __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
-        if (atomicAdd(counter, 1u) == gridDim.x * gridDim.y - 1) {   // last block: every block's stores are fenced
+        if (atomicAdd(counter, 1u) == gridDim.x - 1) {   // last block: every block's stores are fenced
             *counter = 0;
             __threadfence_system();
             if (*(volatile int*)status == SR_OK) flags[rank] = seq;
@@ -370,7 +377,9 @@ int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, dou
         (((uintptr_t)pl.planes | (uintptr_t)pair->R.px) & 7) == 0 && pair->peer_win && (pair->peer_mode == 2 || pair->peer_mode == 3)) {
         int rc = sr_peer_wait_ack(ctx, pair, pair->wire_seq);
         if (rc != SR_OK) return rc;
-        resolve_wire16_kernel<<<dim3(cdiv(g.w2, 256), rows), 128, 0, ctx->stream>>>(g, pl, pair->R.px, pair->R.pitch, sr_peer_window16(pair),
+        int wgrid = cdiv(g.w2, 256) * rows;
+        if (wgrid > ctx->sms * 16) wgrid = ctx->sms * 16;
+        resolve_wire16_kernel<<<wgrid, 128, 0, ctx->stream>>>(g, pl, pair->R.px, pair->R.pitch, sr_peer_window16(pair),
                                                                                    sr_peer_flags(pair), pair->wire_rank, pair->wire_seq,
                                                                                    pair->peer_counter, pair->peer_status_d);
         SR_LAUNCHED(ctx);

@@ -251,6 +251,51 @@ __global__ void __launch_bounds__(128) ext_from_planes_kernel(const uint32_t* __
     if (subpix) subpix[o] = dsub;
 }
 
+// The same for the integer costs when nothing else follows (no LR check): winner from the key plane(s), the two
+// parabola neighbours recomputed in ONE walk over the window (the right-image pixel is loaded once for both, packed
+// BGRx words, VABSDIFF4.ACC / IDP.4A), sub-pixel value written straight into the CV_64F map -- one kernel instead of
+// ext_from_planes_kernel (generic seven-moment window statistics, twice) + ext_finish_kernel.
+template <int COST>
+__global__ void __launch_bounds__(128) ext_subpix_out_kernel(const uint32_t* __restrict__ Lp, int pitchL,
+                                                             const uint32_t* __restrict__ Rp, int pitchR, ExtGeom g,
+                                                             const uint32_t* __restrict__ planes, size_t stride, int npass,
+                                                             int dbase, int shift, double* __restrict__ out) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = g.row0 + blockIdx.y;
+    if (x >= g.wr) return;
+    size_t o = (size_t)y * g.wr + x;
+    float dsub = 0.0f;
+    if (y < g.height && (__ldg(Rp + (size_t)y * pitchR + x) & 0xFFFFFFu) != 0) {
+        uint32_t bc = 0xFFFFFFFFu; int bd = -1;
+        for (int p = 0; p < npass; p++) {
+            uint32_t k = __ldg(planes + (size_t)p * stride + o);
+            if (k != 0xFFFFFFFFu && (k >> shift) < bc) { bc = k >> shift; bd = dbase + 64 * p + (int)(k & ((1u << shift) - 1u)); }
+        }
+        if (bd >= 0) {
+            dsub = (float)bd;
+            const int l = min(x, g.half), r = min(g.wr - x - 1, g.half), u = min(y, g.half), dn = min(g.hr - y - 1, g.half);
+            if (bd - 1 >= g.dlo && bd + 1 < g.dhi && x + bd + 1 + r < g.wo) {
+                uint32_t cm = 0, cp = 0;   // a window of < 2^14 pixels fits 32 bits for both costs
+                for (int rr = y - u; rr < y + dn; rr++) {
+                    const uint32_t* rrow = Rp + (size_t)rr * pitchR + (x - l);
+                    const uint32_t* lrow = Lp + (size_t)rr * pitchL + (x - l + bd);
+                    for (int i = 0; i < l + r; i++) {
+                        const uint32_t q = __ldg(rrow + i), a = __ldg(lrow + i - 1), b = __ldg(lrow + i + 1);
+                        if (COST == SR_COST_SAD) {
+                            asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(cm) : "r"(a), "r"(q));
+                            asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(cp) : "r"(b), "r"(q));
+                        } else {
+                            const uint32_t da = __vabsdiffu4(a, q), db = __vabsdiffu4(b, q);
+                            cm = __dp4a(da, da, cm); cp = __dp4a(db, db, cp);
+                        }
+                    }
+                }
+                dsub = parabola(dsub, __uint2float_rn(cm), __uint2float_rn(bc), __uint2float_rn(cp));
+            }
+        }
+    }
+    out[o] = (double)dsub;
+}
+
 // NCC interior pixels: first maximum of the per-pass (score, d) planes of search_ncc.cu (passes ascend in d,
 // strict > keeps the smaller d), plus the parabola through the directly recomputed neighbour costs.
 __global__ void __launch_bounds__(128) ncc_merge_kernel(const uint32_t* __restrict__ Lp, int pitchL,
@@ -329,6 +374,27 @@ __global__ void ext_finish_kernel(const int* __restrict__ disp_r, const float* _
     out[o] = ok ? (subpix ? (double)subpix[o] : (double)d) : 0.0;
 }
 
+// winner + parabola straight into pair->out from the key planes the tile kernel left in pair->planes (SSD / SAD, no LR check)
+bool sr_ext_subpix_out_applies(const sr_search_params* p) {
+    return p->subpixel && !p->lr_check && (p->cost == SR_COST_SAD || p->cost == SR_COST_SSD_L2) &&
+           3ull * p->block * p->block * 65025ull < 0xFFFFFFFFull;
+}
+int sr_launch_ext_subpix_out(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1) {
+    const int w1 = pair->w1, h1 = pair->h1, w2 = pair->w2, h2 = pair->h2, half = (p->block - 1) / 2;
+    int dhi = p->max_disp, dlo = p->min_disp;
+    if (dhi < dlo) dhi = dlo;
+    ExtGeom g{w2, h2, w1, h1, h1 < h2 ? h1 : h2, half, dlo, dhi, 0, p->cost, row0};
+    dim3 grid(cdiv(w2, 128), row1 - row0);
+    if (p->cost == SR_COST_SAD)
+        ext_subpix_out_kernel<SR_COST_SAD><<<grid, 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, pair->planes,
+                                                                          pair->npx_cap, pair->npass, pair->plane_dbase, pair->key_shift, pair->out);
+    else
+        ext_subpix_out_kernel<SR_COST_SSD_L2><<<grid, 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, pair->planes,
+                                                                             pair->npx_cap, pair->npass, pair->plane_dbase, pair->key_shift, pair->out);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
 static int rows_fit_ext(int ho, int hr, int half) {
     int height = ho < hr ? ho : hr;
     for (int y = (height - half - 2 > 0 ? height - half - 2 : 0); y < height; y++) {
@@ -369,6 +435,10 @@ int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int
         sg.row0 = row0; sg.row1 = row1;
         int handled = sr_launch_search_tile(ctx, pair, sg, p->cost, 0);
         if (handled < 0) return handled;
+        if (handled && sr_ext_subpix_out_applies(p)) {
+            ctx->last_kernel = "tile+ext";
+            return sr_launch_ext_subpix_out(ctx, pair, p, row0, row1);
+        }
         if (handled) {
             tiled = true;
             ext_from_planes_kernel<<<dim3(cdiv(w2, 128), row1 - row0), 128, 0, ctx->stream>>>(

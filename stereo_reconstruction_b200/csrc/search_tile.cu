@@ -122,7 +122,11 @@ __device__ __forceinline__ void vertical_update(uint32_t (&col)[XT][DT], uint32_
     }
 }
 
+constexpr int MAXP = 16;  // pairs of one launch (sr_launch_search_tile_multi)
+struct PairPtrs { const uint32_t* L; const uint32_t* R; uint32_t* planes; };
 struct TileArgs {
+    int npairs;          // > 0: the work items span several pairs of one shape (item.x = tile | pair << 16), images and
+    PairPtrs pp[MAXP];   //      key planes from pp[pair]; 0: the single pair below
     const uint32_t* L; int pitchL;
     const uint32_t* R; int pitchR;
     uint32_t* planes;    // one u32 key plane (cost*64 + d_local) per pass of 64 disparities
@@ -220,7 +224,9 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     // One CTA per work item {tile, first row, end row, pass}.  The list is built on the host (tile_work_list):
     // the hardware hands out CTAs in list order, so the order of the list is the schedule.
     const int4 wk = __ldg(a.work + blockIdx.x);
-    const int CB = -XT + TILE_OUT * wk.x;                      // first own column of lane 0
+    const int CB = -XT + TILE_OUT * (wk.x & 0xFFFF);           // first own column of lane 0
+    const uint32_t* imgL = a.L; const uint32_t* imgR = a.R; uint32_t* planes = a.planes;
+    if (a.npairs > 0) { const PairPtrs pp = a.pp[wk.x >> 16]; imgL = pp.L; imgR = pp.R; planes = pp.planes; }
     const int yb0 = wk.y, yb1 = wk.z;
     if (yb0 >= yb1) return;
     const int cb = CB + XT * lane;                             // this thread's own columns [cb, cb+16)
@@ -258,7 +264,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
         for (int y = yb0 + warp; y < yb1; y += NW)
             for (int q = lane; q < TILE_OUT; q += 32) {
                 int x = CB + h + q;
-                if (x >= 0 && x < a.w2) a.planes[(size_t)pass * a.plane_stride + (size_t)y * a.w2 + x] = 0xFFFFFFFFu;
+                if (x >= 0 && x < a.w2) planes[(size_t)pass * a.plane_stride + (size_t)y * a.w2 + x] = 0xFFFFFFFFu;
             }
         return;
     }
@@ -282,7 +288,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const uint32_t ld_dst = smem_base + 16u * (ld_right ? padpos(tid) : RPOS + padpos(tid - RCH));
     const int ld_pitch = ld_right ? a.pitchR : a.pitchL;
     int r_pf = y_start + h - 1;                                // next row to stage
-    const uint32_t* ld_ptr = (ld_right ? a.R : a.L + dcta) + (ptrdiff_t)r_pf * ld_pitch + CB + 4 * (ld_right ? tid : tid - RCH);
+    const uint32_t* ld_ptr = (ld_right ? imgR : imgL + dcta) + (ptrdiff_t)r_pf * ld_pitch + CB + 4 * (ld_right ? tid : tid - RCH);
     uint32_t slot_pf = slot_of(r_pf);
     auto issue_row = [&]() {
         if (row_ok(r_pf) && ld_on) cp_async16_s(slot_pf + ld_dst, ld_ptr);
@@ -298,7 +304,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int xq = CB + h + rq;
     const bool red_on = rgrp < 31 && xq >= 0 && xq < a.w2;
     const uint32_t red_b = keys_base + 4u * (20 * rgrp + (lane & 15));
-    uint32_t* pl = a.planes + (a.merged ? (size_t)0 : (size_t)pass * a.plane_stride) + (size_t)yb0 * a.w2 + xq;
+    uint32_t* pl = planes + (a.merged ? (size_t)0 : (size_t)pass * a.plane_stride) + (size_t)yb0 * a.w2 + xq;
     const bool merged = a.merged != 0;
     const int mshift = a.shift - 6;
     const uint32_t mpass = (uint32_t)pass * (DT * NW);
@@ -408,16 +414,12 @@ int dispatch_h2(sr_ctx* ctx, const TileArgs& a, int nwork) {
 //    run at the same time and share its image rows in L2, so DRAM reads stay near one sweep of the two images
 //    (pass-major order re-reads them once per wave: 295 MB instead of 106 MB on the 4K pair).
 //  * The rows are cut into `nb` equal bands followed by a tail of bands 1/div as tall over the last `pct` percent of
-//    the rows: the last CTAs to start are short, so the SMs run dry together at the end of the kernel.  (nb, pct, div)
-//    is chosen by SIMULATING the hardware's list scheduling of that very list on the device's SM count (one CTA per
-//    SM, the next CTA of the list goes to the SM that frees first) with a cost model of one unit per output row, 0.3
-//    per warm-up row, a fixed launch share and 20 % more for passes on the break-rule diagonal; the plan with the
-//    smallest makespan wins.  A 270-row band of the 4K pair at 8 GPUs (62 (tile, pass) columns on 148 SMs) thus
-//    becomes two bands of ~118 rows and a short tail instead of two of 135.
+//    the rows: the last CTAs to start are short, so the SMs run dry together at the end of the kernel.
 //  * With the merged key plane, (tile, pass) combinations without a single candidate (break rule at the right
 //    image edge) are left out altogether.
 // Lists are cached per geometry on the context (the row-chunk pipeline repeats the same few shapes).
 int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx, int rows, const int4** work, int* nwork) {
+    const int npairs = a.npairs > 0 ? a.npairs : 1;
     static const char* ord_env = getenv("SR_TILE_ORDER");   // 0: pass-major (development comparison)
     static const char* tl_env = getenv("SR_TILE_TAIL");     // "percent,divisor" tuning override
     static const char* nb_env = getenv("SR_TILE_NBANDS");   // tuning override
@@ -426,7 +428,7 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
     if (tl_env) sscanf(tl_env, "%d,%d", &f_pct, &f_div);
     const int no_tail = ctx->more_chunks_follow ? 1 : 0;   // row-chunk pipeline: the next chunk's CTAs fill the end of this launch
     TileWork key;
-    const int kv[TileWork::NKEY] = {g.w1, g.w2, g.half, a.dlo, a.dhi, a.row0, a.row1, a.merged, order, f_pct * 64 + f_div, f_nb, no_tail};
+    const int kv[TileWork::NKEY] = {g.w1, g.w2, g.half, a.dlo, a.dhi, a.row0, a.row1, a.merged, order, f_pct * 64 + f_div, f_nb, no_tail + 2 * npairs};
     for (int i = 0; i < TileWork::NKEY; i++) key.key[i] = kv[i];
     for (TileWork& t : ctx->tile_work)
         if (!memcmp(t.key, key.key, sizeof key.key)) { t.stamp = ++ctx->tile_work_clock; *work = t.dev; *nwork = t.n; return SR_OK; }
@@ -437,18 +439,16 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
         return g.w1 - x - r < a.dhi ? g.w1 - x - r : a.dhi;
     };
     auto x_first_of = [&](int tile) { int x = -XT + TILE_OUT * tile + g.half; return x < 0 ? 0 : x; };
-    auto has_candidates = [&](int tile, int pass) { return a.dbase + 64 * pass < dlim_at(x_first_of(tile)); };
+    auto has_candidates = [&](int tile, int pass) { return a.dbase + 64 * pass < dlim_at(x_first_of(tile & 0xFFFF)); };
     // (tile, pass) columns in launch order within a band, with their relative cost per row
-    struct Col { int tile, pass; float w; };
+    struct Col { int tile, pass; };
     std::vector<Col> cols;
-    for (int t = 0; t < ntx; t++)
-        for (int p = a.npass - 1; p >= 0; p--) {
-            if (a.merged && !has_candidates(t, p)) continue;   // planes mode: the CTA still writes its "none" keys
-            int x_last = -XT + TILE_OUT * (t + 1) + g.half - 1;
-            if (x_last > g.w2 - 1) x_last = g.w2 - 1;
-            bool masked = a.dbase + 64 * p < a.dlo || a.dbase + 64 * (p + 1) > dlim_at(x_last);
-            cols.push_back({t, p, has_candidates(t, p) ? (masked ? 1.2f : 1.0f) : 0.1f});
-        }
+    for (int q = 0; q < npairs; q++)                           // several pairs: more columns per band, taller bands
+        for (int t = 0; t < ntx; t++)
+            for (int p = a.npass - 1; p >= 0; p--) {
+                if (a.merged && !has_candidates(t, p)) continue;   // planes mode: the CTA still writes its "none" keys
+                cols.push_back({t | (q << 16), p});
+            }
     auto make_bands = [&](int nb, int pct, int div) {
         std::vector<int2> bands;
         int rows_tail = (div > 1 && pct > 0) ? rows * pct / 100 : 0;
@@ -464,39 +464,29 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
         for (; y < a.row1; y += band2) bands.push_back(make_int2(y, y + band2 < a.row1 ? y + band2 : a.row1));
         return bands;
     };
-    std::vector<double> sm_free((size_t)ctx->sms);
-    auto makespan = [&](const std::vector<int2>& bands) {
-        std::fill(sm_free.begin(), sm_free.end(), 0.0);
-        // a binary heap would do; the lists are a few hundred to a few thousand items and SMs free up in order
-        double end = 0;
-        auto run = [&](const Col& c, int2 b) {
-            size_t k = 0;
-            for (size_t i = 1; i < sm_free.size(); i++) if (sm_free[i] < sm_free[k]) k = i;
-            sm_free[k] += 3.0 + c.w * ((b.y - b.x) + 0.3 * warm);
-            if (sm_free[k] > end) end = sm_free[k];
-        };
-        if (order) { for (int2 b : bands) for (const Col& c : cols) run(c, b); }
-        else { for (int p = a.npass - 1; p >= 0; p--) for (int2 b : bands) for (const Col& c : cols) if (c.pass == p) run(c, b); }
-        return end;
-    };
+    // nb: CTAs are list-scheduled one per SM and their durations vary (masked passes on the break-rule diagonal, image
+    // edges), so the end of the launch costs about one CTA duration on top of the average load: minimise
+    // (CTAs + SMs) / SMs x (band + warm-up rows).  Tail: the last 10 % of the rows in bands a quarter as tall (20 % in
+    // thirds for launches of 600 rows or fewer, e.g. one of 8 row bands of a 4K pair).  Both from the measured sweep
+    // profiles/r02_tile_schedule_sweep.log (4K: 20-24 bands + 10 %/4 = 1.73 ms against 1.86-2.15 ms for 8-24 bands
+    // without a tail; 270 rows: 6-8 bands + 20 %/3 = 0.267-0.270 ms against 0.30 ms without).  A list-scheduling
+    // simulation with per-CTA cost estimates was tried in its place and chose too few, too tall bands (1.85 ms): the real
+    // spread of CTA durations is wider than any estimate I could justify, and short CTAs absorb it.
     std::vector<int2> best_bands;
-    double best = -1;
     if (!cols.empty()) {
-        const int maxnb = rows / minband < 1 ? 1 : (rows / minband > 96 ? 96 : rows / minband);
-        static const int pcts[] = {0, 6, 10, 14, 18, 24, 30, 38}, divs[] = {2, 3, 4};
-        for (int nb = (f_nb > 0 ? f_nb : 1); nb <= (f_nb > 0 ? f_nb : maxnb); nb++) {
-            if ((size_t)nb * cols.size() > 6000) break;        // makespan() is O(items x SMs)
-            for (int pct : pcts) {
-                if (f_pct >= 0 && pct != pcts[0]) continue;
-                if (no_tail && pct) continue;
-                for (int div : divs) {
-                    if ((pct == 0 || f_pct >= 0) && div != divs[0]) continue;
-                    std::vector<int2> bands = make_bands(nb, f_pct >= 0 ? (no_tail ? 0 : f_pct) : pct, f_div > 0 ? f_div : div);
-                    double m = makespan(bands);
-                    if (best < 0 || m < best * 0.999) { best = m; best_bands.swap(bands); }
-                }
-            }
+        const int maxnb = rows / minband < 1 ? 1 : (rows / minband > 256 ? 256 : rows / minband);
+        int nb_best = 1;
+        double best = -1;
+        for (int nb = 1; nb <= maxnb; nb++) {
+            int bnd = (rows + nb - 1) / nb, nbe = (rows + bnd - 1) / bnd;
+            double c = ((double)cols.size() * nbe + ctx->sms) / ctx->sms * (bnd + warm + 2);
+            if (best < 0 || c < best) { best = c; nb_best = nbe; }
         }
+        if (f_nb > 0) nb_best = f_nb < maxnb ? f_nb : maxnb;
+        int pct = rows <= 600 ? 20 : 10, div = rows <= 600 ? 3 : 4;
+        if (f_pct >= 0) { pct = f_pct; div = f_div > 0 ? f_div : 2; }
+        if (no_tail || !order || nb_best < 4) pct = f_pct >= 0 && !no_tail ? pct : 0;
+        best_bands = make_bands(nb_best, pct, div);
     }
     std::vector<int4> items;
     if (order) {
@@ -506,10 +496,9 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
     }
     static const char* dbg_env = getenv("SR_TILE_PLAN_DEBUG");
     if (dbg_env) {
-        fprintf(stderr, "[tile plan] rows %d..%d cols %zu bands %zu (first %d, last %d rows) items %zu makespan %.0f ideal %.0f\n", a.row0, a.row1,
+        fprintf(stderr, "[tile plan] rows %d..%d cols %zu bands %zu (first %d, last %d rows) items %zu\n", a.row0, a.row1,
                 cols.size(), best_bands.size(), best_bands.empty() ? 0 : best_bands.front().y - best_bands.front().x,
-                best_bands.empty() ? 0 : best_bands.back().y - best_bands.back().x, items.size(), best,
-                cols.size() * (double)rows / ctx->sms);
+                best_bands.empty() ? 0 : best_bands.back().y - best_bands.back().x, items.size());
     }
     key.n = (int)items.size();
     key.dev = nullptr;
@@ -532,14 +521,22 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
 
 }  // namespace
 
-int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref) {
-    if (left_ref) return 0;
+// One launch over `n` pairs of one shape (n == 1: the plain call).  With several pairs the work list carries the pair
+// index: a 1280x720 / 128-disparity pair alone is 6 (tile, pass) columns for 148 SMs -- 50 bands of 15 rows, a third of
+// every CTA's rows warm-up; eight pairs make 48 columns and bands of ~100 rows.  Key planes of the pairs lie one after
+// the other in the context's scratch slot 0 (pair q: planes + q * npass * npx_cap).
+int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom& g, int cost) {
+    if (n < 1 || n > MAXP) return 0;
+    sr_pair* pair = pairs[0];
     if (g.half < 1 || g.half > 8) return 0;
     if (cost != SR_COST_SSD_L2 && cost != SR_COST_SAD) return 0;
     int r1 = g.row1 < g.height ? g.row1 : g.height;
-    if (r1 <= g.row0) { pair->npass = 0; return 1; }  // nothing to compute: the resolve pass fills the rows
+    if (r1 <= g.row0) { for (int q = 0; q < n; q++) pairs[q]->npass = 0; return 1; }  // nothing to compute: the resolve pass fills the rows
     TileArgs a;
+    a.npairs = n > 1 ? n : 0;
     a.L = pair->L.px; a.pitchL = pair->L.pitch; a.R = pair->R.px; a.pitchR = pair->R.pitch;
+    for (int q = 1; q < n; q++)
+        if (pairs[q]->L.pitch != a.pitchL || pairs[q]->R.pitch != a.pitchR || pairs[q]->npx_cap != pair->npx_cap) return 0;
     a.w1 = g.w1; a.h1 = g.h1; a.w2 = g.w2; a.h2 = g.h2; a.half = g.half;
     a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
     a.npass = (g.dhi - a.dbase + 63) / 64;
@@ -555,7 +552,7 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     int rows = r1 - g.row0;
     if (a.npass <= 0) {
         // empty candidate range: every record is "none"
-        pair->npass = 0;
+        for (int q = 0; q < n; q++) pairs[q]->npass = 0;
         return 1;
     }
     // Key planes.  Where cost and candidate index fit one u32 together (cost << shift | d - dbase), all passes
@@ -569,16 +566,27 @@ int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int c
     a.merged = a.npass > 1 && ((cmax + 1) << shift) < 0xFFFFFFFFull && !(mg_env && atoi(mg_env) == 0);
     if (!a.merged) shift = 6;
     a.shift = shift;
-    pair->npass = a.merged ? 1 : a.npass; pair->plane_dbase = a.dbase; pair->key_shift = shift;
-    pair->planes = (uint32_t*)sr_scratch(ctx, 0, (size_t)pair->npass * pair->npx_cap * sizeof(uint32_t));
-    if (!pair->planes) return SR_E_CUDA;
+    const int planes_per_pair = a.merged ? 1 : a.npass;
+    uint32_t* base = (uint32_t*)sr_scratch(ctx, 0, (size_t)n * planes_per_pair * pair->npx_cap * sizeof(uint32_t));
+    if (!base) return SR_E_CUDA;
+    for (int q = 0; q < n; q++) {
+        sr_pair* pq = pairs[q];
+        pq->npass = planes_per_pair; pq->plane_dbase = a.dbase; pq->key_shift = shift;
+        pq->planes = base + (size_t)q * planes_per_pair * pair->npx_cap;
+        a.pp[q].L = pq->L.px; a.pp[q].R = pq->R.px; a.pp[q].planes = pq->planes;
+        if (a.merged)
+            SR_CUDA(ctx, cudaMemsetAsync(pq->planes + (size_t)g.row0 * g.w2, 0xFF, (size_t)(r1 - g.row0) * g.w2 * sizeof(uint32_t), ctx->stream));
+    }
     a.planes = pair->planes; a.plane_stride = pair->npx_cap;
-    if (a.merged)
-        SR_CUDA(ctx, cudaMemsetAsync(pair->planes + (size_t)g.row0 * g.w2, 0xFF, (size_t)(r1 - g.row0) * g.w2 * sizeof(uint32_t), ctx->stream));
     int nwork = 0;
     int rc = tile_work_list(ctx, g, a, ntx, rows, &a.work, &nwork);
     if (rc != SR_OK) return rc;
     if (nwork == 0) return 1;                                // merged plane, no (tile, pass) has a candidate: all "none"
     if (cost == SR_COST_SAD) return dispatch_h2<SR_COST_SAD>(ctx, a, nwork);
     return dispatch_h2<SR_COST_SSD_L2>(ctx, a, nwork);
+}
+
+int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref) {
+    if (left_ref) return 0;
+    return sr_launch_search_tile_multi(ctx, &pair, 1, g, cost);
 }

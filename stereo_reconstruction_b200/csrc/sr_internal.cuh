@@ -163,6 +163,11 @@ int sr_launch_pack_rows2(sr_ctx* ctx, const uint8_t* rawa, size_t pitcha, int wa
 // Fast path: fixed window, SSD/SAD, first minimum over [dlo,dhi) -> pair->best.
 // Returns 1 when it handled the request, 0 when the shape is not supported (caller falls back).
 int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref);
+// The same in ONE launch over n <= 16 pairs of one shape (batches of small pairs: more work items per band).
+int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom& g, int cost);
+// Right-variant search of n pairs of one shape with one tile launch (plain result, or sub-pixel without LR check);
+// 0 when the request needs the per-pair path (capi_search.cu)
+int sr_search_run_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const sr_search_params* p);
 // Universal path: per-pixel windows (var_block), any size; wide costs -> c0/cr/dr/nwin.
 int sr_launch_search_direct(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int var_block,
                             double thres, int want_c0);
@@ -183,5 +188,7 @@ volatile unsigned* sr_peer_flags(sr_pair* pair);
 int sr_launch_count_evals(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g);
 // NCC through sliding sums: interior pixels -> per-pass (score, d) planes (search_ncc.cu)
 int sr_launch_search_ncc(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, float** pscore, int** pdisp, void** tab);
+bool sr_ext_subpix_out_applies(const sr_search_params* p);
+int sr_launch_ext_subpix_out(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1);
 // NCC / sub-pixel / LR-check extension path (search_ext.cu)
 int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1);

@@ -33,6 +33,9 @@ def test_varblock_random_vs_literal_oracle(sr, ctx, orc, seed):
     if seed % 4 == 0:
         R[3:6, 5:9] = 0                                      # black pixels are skipped before the growth loop
     thres = [5.0, 19.0, 60.0, 150.0, 400.0, 2000.0][seed % 6]
+    if thres >= 2000.0:                                      # nearly uniform content: the deviation norm never reaches thres
+        R = (100 + rng.integers(0, 2, (h, w, 3))).astype(np.uint8)
+        L = np.ascontiguousarray(np.roll(R, 3, axis=1))
     block = int(rng.choice([3, 5, 9, 17]))
     smooth = float(rng.choice([1.0, 0.9]))
     D = int(rng.integers(4, 16))
@@ -42,7 +45,8 @@ def test_varblock_random_vs_literal_oracle(sr, ctx, orc, seed):
     np.testing.assert_array_equal(got, want)
     assert bs.maxBlockSize == mb
     if thres >= 2000.0:
-        assert mb >= 2 * max(h, w) - 8                       # the window grew to the whole image and stopped there
+        assert mb >= 2 * max(h, w) - 1                       # the window grew to the whole image and stopped there
+        #                                                      (the reference would loop forever here: documented deviation)
 
 
 def test_left_variant_on_a_middeval_pair(sr, ctx, orc):

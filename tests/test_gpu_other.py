@@ -169,6 +169,41 @@ def test_pair_reconstruct_device_resident(sr, ctx, orc):
     np.testing.assert_array_equal(got["faces"], orc.mesh_faces(v, 400, 90, 2.0))
 
 
+@pytest.mark.parametrize("w,h,k", [(900, 750, 500), (400, 90, 25), (333, 61, 7), (64, 40, 1), (1436, 992, 500), (50, 30, 200)])
+def test_u8_handoff_pipeline_integer_exact(sr, ctx, orc, monkeypatch, w, h, k):
+    """main.cpp:41-65 for the 8-bit hand-off runs integer-exact (recon.cu: u8 row sums, int32 column prefixes, blurred
+    value + outlier rule inside the depth / vertex / face kernel): every output equals the oracle chain
+    quantize -> removeDisparityOutliers(k) -> convertDisparityToDepth -> reconstruction -> WriteMesh, and the same
+    outputs come out of the general (fp64 prefix) kernels.  Kernel sizes from 1 to larger than the map (reflect-101
+    folds several times), values that round / saturate at the hand-off."""
+    rng = np.random.default_rng(w * 31 + k)
+    Rr = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    L = np.ascontiguousarray(np.roll(Rr, 5, axis=1))
+    K = np.array([[500.0, 0, w / 2], [0, 500.0, h / 2], [0, 0, 1]], np.float32)
+    pair = sr.capi.Pair(ctx, w, h, w, h)
+    pair.upload(L, Rr)
+    p = sr.capi.search_params(block=9, min_disp=0, max_disp=min(300, w - 20), smooth=1.0, cost=sr.capi.COST_SAD)
+    pair.run(p)
+    disp64 = pair.download(p)
+    got = sr.reconstruction.pairReconstruct(pair, K, K[0, 0], 1.0, True, k, 1.5, 0.8, 2.0)
+    n0 = ctx.launches
+    sr.reconstruction.pairReconstruct(pair, K, K[0, 0], 1.0, True, k, 1.5, 0.8, 2.0)
+    assert ctx.launches - n0 == 7          # rowsum, seg, prefix, fused depth kernel, block totals, scan, scatter
+    d = orc.remove_outliers(orc.quantize_u8(disp64), k, 1.5, 0.8)
+    depth = orc.disparity_to_depth(d, K[0, 0], 1.0)
+    v = orc.backproject(Rr, depth, K[0, 0], K[1, 1], K[0, 2], K[1, 2])
+    np.testing.assert_array_equal(got["disp"], d)
+    np.testing.assert_array_equal(got["depth"], depth)
+    assert got["vertices"].tobytes() == v.tobytes()
+    np.testing.assert_array_equal(got["faces"], orc.mesh_faces(v, w, h, 2.0))
+    monkeypatch.setenv("SR_RECON_GENERAL", "1")
+    gen = sr.reconstruction.pairReconstruct(pair, K, K[0, 0], 1.0, True, k, 1.5, 0.8, 2.0)
+    for key in ("disp", "depth", "faces"):
+        np.testing.assert_array_equal(gen[key], got[key])
+    assert gen["vertices"].tobytes() == got["vertices"].tobytes()
+    pair.close()
+
+
 @pytest.mark.parametrize("name,z", golden_cases("warp"), ids=lambda v: v if isinstance(v, str) else "")
 def test_warp_golden(sr, ctx, orc, name, z):
     """cv2.warpPerspective(INTER_NEAREST) goldens incl. half-pixel landings, strong perspective, (near-)singular M."""
@@ -257,6 +292,52 @@ def test_batch_api(sr, ctx, orc):
     for i, (L, R) in enumerate(pairs):
         _, _, sp = orc.search_ext(L, R, 7, 0, D, orc.COST_SAD, want_subpix=True)
         np.testing.assert_array_equal(outs[i], sp.astype(np.float64))
+
+
+@pytest.mark.parametrize("subpixel,cost", [(True, 1), (False, 1), (False, 0), (True, 0)])
+def test_batch_multi_pair_launch(sr, ctx, orc, subpixel, cost):
+    """Batches of small pairs share ONE launch of the fused cost + WTA kernel (work items carry the pair index):
+    sr_search_run_batch on resident pairs and the grouped pipeline of sr_block_search_batch (pinned buffers, >= 16
+    pairs) give each pair exactly what sr_search_run gives it alone -- and what the oracle says."""
+    import ctypes as C
+    capi = sr.capi
+    n, w, h, D = 19, 300, 66, 40
+    data = [orc.synth_pair(0xB200, 100 + i, w, h, 0, D, quant=(i % 3 == 0)) for i in range(n)]
+    data[2][1][10:20, 50:90] = 0
+    p = capi.search_params(block=7, min_disp=0, max_disp=D, smooth=1.0, cost=cost, subpixel=subpixel)
+    want = []
+    for L, R in data:
+        if subpixel:
+            want.append(orc.search_ext_fast(L, R, 7, 0, D, cost, want_subpix=True)[2].astype(np.float64))
+        else:
+            want.append(orc.block_search_right_fast(L, R, 7, 0, D, 1.0, cost=cost))
+    # resident form
+    pairs = [capi.Pair(ctx, w, h, w, h) for _ in range(n)]
+    for q, (L, R) in zip(pairs, data):
+        q.upload(L, R)
+    n0 = ctx.launches
+    capi.search_run_batch(ctx, pairs, p)
+    assert ctx.launches - n0 == 2 + n            # 19 pairs = groups of 16 + 3: two tile launches + one resolve / sub-pixel pass per pair
+    for q, wnt in zip(pairs, want):
+        np.testing.assert_array_equal(q.download(p), wnt)
+    for q in pairs:
+        q.close()
+    # host form: grouped pipeline with pinned buffers
+    bufs, Ls, Rs, outs = [], (capi.SrImage * n)(), (capi.SrImage * n)(), []
+    for i, (L, R) in enumerate(data):
+        Lp, a = capi.pinned_empty(L.shape, np.uint8); Rp, b = capi.pinned_empty(R.shape, np.uint8); o, c = capi.pinned_empty((h, w), np.float64)
+        Lp[...] = L; Rp[...] = R; o[...] = -5.0
+        bufs += [a, b, c]
+        _, Ls[i] = capi.image(Lp); _, Rs[i] = capi.image(Rp)
+        outs.append((Lp, Rp, o))
+    try:
+        optrs = (C.c_void_p * n)(*[o.ctypes.data for _, _, o in outs])
+        ctx.check(ctx._l.sr_block_search_batch(ctx.h, n, Ls, Rs, C.byref(p), optrs, C.c_size_t(w * 8)))
+        for (_, _, o), wnt in zip(outs, want):
+            np.testing.assert_array_equal(np.asarray(o), wnt)
+    finally:
+        for x in bufs:
+            capi.free_pinned(x)
 
 
 @pytest.mark.parametrize("cost", [0, 1, 2])

@@ -15,7 +15,7 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ctx = capi.Context(local)
-w, h, D, block = 1283, 721, 64, 9
+w, h, D, block = (1283 if os.environ.get("SR_CHECK_ODD") else 1284), 721, 64, 9   # even width: gather fused into the resolve pass; odd: push kernel
 pair = capi.Pair(ctx, w, h, w, h)
 p = capi.search_params(block=block, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD)
 peer = sharding.PeerGather(pair, h, rank, world)
@@ -25,8 +25,11 @@ gathered = []
 for step in range(steps):
     L, R = synth.synth_pair(0xB200, step, w, h, 0, D)
     pair.upload(L, R)
-    pair.run(p, r0, r1)
-    peer.gather()
+    if step % 4 == 3:
+        pair.run(p, r0, r1)           # the two-kernel form of the same protocol step
+        peer.gather()
+    else:
+        peer.run_and_gather(p)        # ranks > 0: sr_search_run_push
     if rank == 0:
         gathered.append((L, R, pair.download(p)))
     elif step % 3 == rank % 3:
@@ -39,6 +42,7 @@ if rank == 0:
             bad += 1
             print(f"step {step}: gathered map differs", flush=True)
     print(f"peer gather over {world} ranks: {steps - bad}/{steps} steps identical to the single-GPU map", flush=True)
+pair.peer_status()                    # a failed protocol step is an error on every rank
 ctx.sync()
 dist.barrier()
 dist.destroy_process_group()
