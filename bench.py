@@ -453,11 +453,13 @@ def main():
         step_resident()
     barrier()
     if world > 1:
-        # The ranks leave the host-side barrier up to ~1 ms apart; rank 0's first step would wait that long for the other
-        # ranks' bands (measured: 1.73 ms against 0.92 ms for every later step at N=2).  One untimed step lets the gather's
-        # flag / acknowledgement words pull the ranks into step; the K timed steps follow.
-        ctx.l2_flush()
-        step_resident()
+        # The ranks leave the host-side barrier up to ~1 ms apart; the first step after it would measure that skew (rank 0
+        # waiting for the late ranks' bands: 1.73 ms against 0.92 ms for every later step at N=2; at N=8 the pushers' NEXT
+        # step waiting for the late root's acknowledgement: 0.81 against 0.30 ms).  Two untimed steps let the gather's flag
+        # and acknowledgement words pull the ranks into step; the K timed steps follow.
+        for _ in range(2):
+            ctx.l2_flush()
+            step_resident()
     launches0 = ctx.launches
     step_ms, kern_ms = [], []
     for _ in range(args.steps):

@@ -278,8 +278,11 @@ __global__ void __launch_bounds__(128) ext_subpix_out_kernel(const uint32_t* __r
                 for (int rr = y - u; rr < y + dn; rr++) {
                     const uint32_t* rrow = Rp + (size_t)rr * pitchR + (x - l);
                     const uint32_t* lrow = Lp + (size_t)rr * pitchL + (x - l + bd);
-                    for (int i = 0; i < l + r; i++) {
-                        const uint32_t q = __ldg(rrow + i), a = __ldg(lrow + i - 1), b = __ldg(lrow + i + 1);
+                    // the two windows are two columns apart: one left-image load per column feeds both (a three-word shift)
+                    uint32_t a = __ldg(lrow - 1), mid = __ldg(lrow), b;
+                    for (int i = 0; i < l + r; i++, a = mid, mid = b) {
+                        const uint32_t q = __ldg(rrow + i);
+                        b = __ldg(lrow + i + 1);
                         if (COST == SR_COST_SAD) {
                             asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(cm) : "r"(a), "r"(q));
                             asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(cp) : "r"(b), "r"(q));

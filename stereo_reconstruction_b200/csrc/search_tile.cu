@@ -22,6 +22,7 @@
 // r=min(w2-x-1,h), u=min(y,h), dn=min(h2-y-1,h)  ==  the fixed window [x-h,x+h) x [y-h,y+h) with
 // the pointwise cost forced to 0 outside columns [0,w2-1) and rows [0,h2-1).
 #include <cstdlib>
+#include <functional>
 #include "sr_internal.cuh"
 #include <stdio.h>
 #include <string.h>
@@ -73,8 +74,9 @@ __device__ __forceinline__ uint4 lds128(uint32_t saddr) {
 // col - (pointwise cost): the row leaving the window.  Both integer pipes issue 64 lanes/clk/SM (ALU: VABSDIFF4,
 // IADD3, VIMNMX3; FMA: IDP.4A, IMAD), so the subtraction goes to the FMA pipe, which the rest of the loop leaves
 // idle: SAD = VABSDIFF4 (ALU) + IDP.4A.U8.S8 with the byte multipliers -1 (FMA) instead of VABSDIFF4 + IADD
-// (ALU + ALU); SSD = VABSDIFF4 + IDP.4A + (FSUB ? IMAD by -1 : IADD).  km1 = 0xFFFFFFFF is a kernel argument so that
-// the IMAD is not strength-reduced to an ALU subtract.
+// (ALU + ALU); SSD = VABSDIFF4 + IDP.4A + IADD (an IMAD by -1 in its place -- FSUB, km1 = 0xFFFFFFFF as a kernel argument
+// so that it is not strength-reduced -- measured 1 % faster on 4K / 9x9 and slower on small shapes, where the second
+// copy of the subtract phase in the instruction stream costs more than it wins: not instantiated).
 template <int COST, bool FSUB>
 __device__ __forceinline__ uint32_t pcost_sub(uint32_t l, uint32_t r, uint32_t acc, uint32_t km1) {
     uint32_t ad = __vabsdiffu4(l, r);
@@ -126,7 +128,7 @@ constexpr int MAXP = 16;  // pairs of one launch (sr_launch_search_tile_multi)
 struct PairPtrs { const uint32_t* L; const uint32_t* R; uint32_t* planes; };
 struct TileArgs {
     int npairs;          // > 0: the work items span several pairs of one shape (item.x = tile | pair << 16), images and
-    PairPtrs pp[MAXP];   //      key planes from pp[pair]; 0: the single pair below
+    const PairPtrs* pp;  //      key planes from pp[pair] (device array); 0: the single pair below
     const uint32_t* L; int pitchL;
     const uint32_t* R; int pitchR;
     uint32_t* planes;    // one u32 key plane (cost*64 + d_local) per pass of 64 disparities
@@ -145,7 +147,6 @@ struct TileArgs {
     uint32_t km1;        // == 0xFFFFFFFF (-1): IMAD-based subtract
     int red_mode;        // 1: half of the warps merge the previous row's keys at the end of the iteration
     uint32_t zmask;      // bit w: warp w slides its window sums on the FMA pipe (window_wta ZMODE)
-    uint32_t fmask;      // bit w: warp w subtracts the leaving row's SSD cost with an IMAD (pcost_sub FSUB)
 };
 
 // horizontal window sums + in-thread WTA for one output row.  Disparities are processed in pairs so
@@ -226,7 +227,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int4 wk = __ldg(a.work + blockIdx.x);
     const int CB = -XT + TILE_OUT * (wk.x & 0xFFFF);           // first own column of lane 0
     const uint32_t* imgL = a.L; const uint32_t* imgR = a.R; uint32_t* planes = a.planes;
-    if (a.npairs > 0) { const PairPtrs pp = a.pp[wk.x >> 16]; imgL = pp.L; imgR = pp.R; planes = pp.planes; }
+    if (a.npairs > 0) { const PairPtrs* pp = a.pp + (wk.x >> 16); imgL = pp->L; imgR = pp->R; planes = pp->planes; }
     const int yb0 = wk.y, yb1 = wk.z;
     if (yb0 >= yb1) return;
     const int cb = CB + XT * lane;                             // this thread's own columns [cb, cb+16)
@@ -236,7 +237,6 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int d0 = dcta + DT * warp;                            // this warp's 4 disparities
     const uint32_t dkey0 = (uint32_t)(DT * warp);               // candidate index within the pass: the key's low 6 bits
     const bool zmode = (a.zmask >> warp) & 1u;
-    const bool fsub = (a.fmask >> warp) & 1u;
     const bool late_sub = (warp >> 2) & 1;
     const bool red_late = a.red_mode && ((warp >> 3) & 1);   // spreads the LDS burst of the key merge over the iteration
 
@@ -345,25 +345,21 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
             // Phase staggering: the warps of one scheduler alternate between "subtract now" and
             // "subtract at the start of the next iteration", so that ALU-only phases (pointwise
             // costs) of some warps overlap the FMA-heavy window/WTA phase of the others.
-            if (late_sub && y - 1 >= yb0 && row_ok(y - 1 - h) && colmask != 0) {
-                if (COST == SR_COST_SSD_L2 && fsub) vertical_update<COST, false, true>(col, smem_base + s_prev, lane_b, uo, colmask, km1);
-                else vertical_update<COST, false, false>(col, smem_base + s_prev, lane_b, uo, colmask, km1);
-            }
+            if (late_sub && y - 1 >= yb0 && row_ok(y - 1 - h) && colmask != 0)
+                vertical_update<COST, false, false>(col, smem_base + s_prev, lane_b, uo, colmask, km1);
             if (row_ok(y + h - 1) && colmask != 0) vertical_update<COST, true, false>(col, smem_base + s_in, lane_b, uo, colmask, km1);
             if (y >= yb0) {
                 uint32_t keys[XT];
 #pragma unroll
                 for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
                 if (needmask) window_wta<H2, true, false>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
-                else if (zmode) window_wta<H2, false, true>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
+                else if (COST == SR_COST_SAD && zmode) window_wta<H2, false, true>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
                 else window_wta<H2, false, false>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
 #pragma unroll
                 for (int k = 0; k < 4; k++)
                     sts128(key_st + buf + 16 * k, keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
-                if (!late_sub && y + 1 < yb1 && row_ok(y - h) && colmask != 0) {
-                    if (COST == SR_COST_SSD_L2 && fsub) vertical_update<COST, false, true>(col, smem_base + s_out, lane_b, uo, colmask, km1);
-                    else vertical_update<COST, false, false>(col, smem_base + s_out, lane_b, uo, colmask, km1);
-                }
+                if (!late_sub && y + 1 < yb1 && row_ok(y - h) && colmask != 0)
+                    vertical_update<COST, false, false>(col, smem_base + s_out, lane_b, uo, colmask, km1);
             }
         } else if (y >= yb0) {
 #pragma unroll
@@ -418,7 +414,9 @@ int dispatch_h2(sr_ctx* ctx, const TileArgs& a, int nwork) {
 //  * With the merged key plane, (tile, pass) combinations without a single candidate (break rule at the right
 //    image edge) are left out altogether.
 // Lists are cached per geometry on the context (the row-chunk pipeline repeats the same few shapes).
-int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx, int rows, const int4** work, int* nwork) {
+// `trial(list, n)` (may be empty) runs the kernel on a candidate list and returns its time in ms: see "autotuned" below.
+int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx, int rows, const int4** work, int* nwork,
+                   const std::function<float(const int4*, int)>& trial) {
     const int npairs = a.npairs > 0 ? a.npairs : 1;
     static const char* ord_env = getenv("SR_TILE_ORDER");   // 0: pass-major (development comparison)
     static const char* tl_env = getenv("SR_TILE_TAIL");     // "percent,divisor" tuning override
@@ -451,27 +449,39 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
             }
     auto make_bands = [&](int nb, int pct, int div) {
         std::vector<int2> bands;
-        int rows_tail = (div > 1 && pct > 0) ? rows * pct / 100 : 0;
-        if (rows_tail < minband) rows_tail = 0;
-        int main_rows = rows - rows_tail;
         if (nb < 1) nb = 1;
-        int band = (main_rows + nb - 1) / nb;
+        int band = (rows + nb - 1) / nb;
         if (band < minband) band = minband;
-        int y = a.row0;
-        for (; y + band <= a.row0 + main_rows; y += band) bands.push_back(make_int2(y, y + band));
-        int band2 = rows_tail ? band / div : band;
+        int band2 = div > 1 ? band / div : band;
         if (band2 < minband) band2 = minband;
-        for (; y < a.row1; y += band2) bands.push_back(make_int2(y, y + band2 < a.row1 ? y + band2 : a.row1));
+        int rows_tail = (div > 1 && pct > 0) ? rows * pct / 100 : 0;
+        int nb1 = (rows - rows_tail + band - 1) / band;
+        int split = a.row0 + (nb1 * band < rows ? nb1 * band : rows);
+        for (int y = a.row0; y < split; y += band) bands.push_back(make_int2(y, y + band < split ? y + band : split));
+        for (int y = split; y < a.row1; y += band2) bands.push_back(make_int2(y, y + band2 < a.row1 ? y + band2 : a.row1));
         return bands;
     };
-    // nb: CTAs are list-scheduled one per SM and their durations vary (masked passes on the break-rule diagonal, image
-    // edges), so the end of the launch costs about one CTA duration on top of the average load: minimise
-    // (CTAs + SMs) / SMs x (band + warm-up rows).  Tail: the last 10 % of the rows in bands a quarter as tall (20 % in
-    // thirds for launches of 600 rows or fewer, e.g. one of 8 row bands of a 4K pair).  Both from the measured sweep
-    // profiles/r02_tile_schedule_sweep.log (4K: 20-24 bands + 10 %/4 = 1.73 ms against 1.86-2.15 ms for 8-24 bands
-    // without a tail; 270 rows: 6-8 bands + 20 %/3 = 0.267-0.270 ms against 0.30 ms without).  A list-scheduling
-    // simulation with per-CTA cost estimates was tried in its place and chose too few, too tall bands (1.85 ms): the real
-    // spread of CTA durations is wider than any estimate I could justify, and short CTAs absorb it.
+    auto make_items = [&](const std::vector<int2>& bands) {
+        std::vector<int4> items;
+        if (order) {
+            for (int2 b : bands) for (const Col& c : cols) items.push_back(make_int4(c.tile, b.x, b.y, c.pass));
+        } else {
+            for (int p = a.npass - 1; p >= 0; p--) for (int2 b : bands) for (const Col& c : cols) if (c.pass == p) items.push_back(make_int4(c.tile, b.x, b.y, c.pass));
+        }
+        return items;
+    };
+    // Heuristic: CTAs are list-scheduled one per SM and their durations vary (masked passes on the break-rule diagonal,
+    // image edges), so the end of the launch costs about one CTA duration on top of the average load: nb minimises
+    // (CTAs + SMs) / SMs x (band + warm-up rows); the last 10 % of the rows go in bands a quarter as tall (20 % in thirds
+    // for launches of 600 rows or fewer).
+    // AUTOTUNED on first use of a geometry: the kernel's time is very sensitive to how the CTA count falls on the 148 SMs
+    // (1436x992 / 145 disparities / block 17: 0.198 ms with 34 bands, 0.244 ms with 37; 4K: 1.73 ms with 20-24 bands + tail,
+    // 1.86-2.15 ms without a tail, profiles/r02_tile_schedule_sweep.log), and no formula I tried tracks it -- a
+    // list-scheduling simulation with per-CTA cost estimates chose 12 tall bands for the 4K pair (1.85 ms).  So the first
+    // launch of a geometry on a context runs up to 12 candidate schedules (0.5 ... 1.5 x the heuristic's band count, two
+    // tail shapes) twice each on the real data, keeps the fastest and caches it (every candidate computes the same, correct
+    // result; a few ms to a few tens of ms once per shape; SR_TILE_AUTOTUNE=0 or the row-chunk pipeline: heuristic only).
+    std::vector<int4> items;
     std::vector<int2> best_bands;
     if (!cols.empty()) {
         const int maxnb = rows / minband < 1 ? 1 : (rows / minband > 256 ? 256 : rows / minband);
@@ -487,12 +497,51 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
         if (f_pct >= 0) { pct = f_pct; div = f_div > 0 ? f_div : 2; }
         if (no_tail || !order || nb_best < 4) pct = f_pct >= 0 && !no_tail ? pct : 0;
         best_bands = make_bands(nb_best, pct, div);
-    }
-    std::vector<int4> items;
-    if (order) {
-        for (int2 b : best_bands) for (const Col& c : cols) items.push_back(make_int4(c.tile, b.x, b.y, c.pass));
-    } else {
-        for (int p = a.npass - 1; p >= 0; p--) for (int2 b : best_bands) for (const Col& c : cols) if (c.pass == p) items.push_back(make_int4(c.tile, b.x, b.y, c.pass));
+        items = make_items(best_bands);
+        static const char* at_env = getenv("SR_TILE_AUTOTUNE");
+        if (trial && !(at_env && atoi(at_env) == 0) && f_nb <= 0 && f_pct < 0 && !no_tail && order) {
+            struct Cand { int nb, pct, div; };
+            std::vector<Cand> cands;
+            static const double scale[] = {0.5, 0.7, 0.85, 1.0, 1.2, 1.5};
+            for (double sc : scale) {
+                int nb = (int)(nb_best * sc + 0.5);
+                nb = nb < 1 ? 1 : (nb > maxnb ? maxnb : nb);
+                bool dup = false;
+                for (const Cand& c : cands) dup = dup || c.nb == nb;
+                if (dup) continue;
+                if (nb >= 4) { cands.push_back({nb, 10, 4}); cands.push_back({nb, 20, 3}); }
+                else cands.push_back({nb, 0, 1});
+            }
+            int4* tmp = nullptr;
+            size_t tmp_cap = 0;
+            float best_ms = -1;
+            // the heuristic's own plan first: a candidate replaces it only when it is at least 2 % faster (timing noise
+            // must not trade a good plan for an equal one)
+            cands.insert(cands.begin(), Cand{nb_best, pct, div});
+            bool first = true;
+            for (const Cand& c : cands) {
+                std::vector<int2> bands = make_bands(c.nb, c.pct, c.div);
+                std::vector<int4> it = make_items(bands);
+                if (it.empty() || it.size() > 60000) continue;
+                if (it.size() > tmp_cap) {
+                    cudaFree(tmp);
+                    tmp_cap = it.size() + 1024;
+                    SR_CUDA(ctx, cudaMalloc((void**)&tmp, tmp_cap * sizeof(int4)));
+                }
+                SR_CUDA(ctx, cudaMemcpy(tmp, it.data(), it.size() * sizeof(int4), cudaMemcpyHostToDevice));
+                float ms = -1;
+                for (int rep = 0; rep < 3; rep++) {
+                    float m = trial(tmp, (int)it.size());
+                    if (m < 0) { ms = -1; break; }
+                    if (ms < 0 || m < ms) ms = m;
+                }
+                if (ms < 0) break;
+                if (getenv("SR_TILE_PLAN_DEBUG")) fprintf(stderr, "[tile tune] nb %d tail %d/%d: %zu bands, %zu items, %.4f ms\n", c.nb, c.pct, c.div, bands.size(), it.size(), ms);
+                if (first || ms < 0.98f * best_ms) { best_ms = ms; best_bands.swap(bands); items.swap(it); }
+                first = false;
+            }
+            cudaFree(tmp);
+        }
     }
     static const char* dbg_env = getenv("SR_TILE_PLAN_DEBUG");
     if (dbg_env) {
@@ -541,11 +590,9 @@ int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const
     a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
     a.npass = (g.dhi - a.dbase + 63) / 64;
     a.row0 = g.row0; a.row1 = r1; a.k64 = 64u; a.nk64 = (uint32_t)-64; a.merged = 0; a.shift = 6; a.km1 = 0xFFFFFFFFu;
-    // per-warp instruction mixes (window_wta, pcost_sub); SR_TILE_ZMASK / SR_TILE_FMASK override for tuning
+    // per-warp instruction mix of the SAD window phase (window_wta ZMODE); SR_TILE_ZMASK overrides for tuning
     static const char* zm_env = getenv("SR_TILE_ZMASK");
-    static const char* fm_env = getenv("SR_TILE_FMASK");
-    a.zmask = zm_env ? (uint32_t)strtoul(zm_env, nullptr, 0) : (cost == SR_COST_SAD ? 0xFFF0u : 0x0000u);   // measured: tools/tune_tile.sh
-    a.fmask = fm_env ? (uint32_t)strtoul(fm_env, nullptr, 0) : 0xFFFFu;
+    a.zmask = zm_env ? (uint32_t)strtoul(zm_env, nullptr, 0) : 0xFFF0u;   // measured: tools/tune_tile.sh
     static const char* rm_env = getenv("SR_TILE_REDMODE");
     a.red_mode = rm_env ? atoi(rm_env) : 1;
     int ntx = (g.w2 + XT - g.half + TILE_OUT - 1) / TILE_OUT;
@@ -569,17 +616,36 @@ int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const
     const int planes_per_pair = a.merged ? 1 : a.npass;
     uint32_t* base = (uint32_t*)sr_scratch(ctx, 0, (size_t)n * planes_per_pair * pair->npx_cap * sizeof(uint32_t));
     if (!base) return SR_E_CUDA;
+    PairPtrs hp[MAXP];
     for (int q = 0; q < n; q++) {
         sr_pair* pq = pairs[q];
         pq->npass = planes_per_pair; pq->plane_dbase = a.dbase; pq->key_shift = shift;
         pq->planes = base + (size_t)q * planes_per_pair * pair->npx_cap;
-        a.pp[q].L = pq->L.px; a.pp[q].R = pq->R.px; a.pp[q].planes = pq->planes;
+        hp[q].L = pq->L.px; hp[q].R = pq->R.px; hp[q].planes = pq->planes;
         if (a.merged)
             SR_CUDA(ctx, cudaMemsetAsync(pq->planes + (size_t)g.row0 * g.w2, 0xFF, (size_t)(r1 - g.row0) * g.w2 * sizeof(uint32_t), ctx->stream));
     }
     a.planes = pair->planes; a.plane_stride = pair->npx_cap;
+    a.pp = nullptr;
+    if (n > 1) {
+        // the pointer table of the pairs: a small pageable H2D copy, staged by the driver at call time (the same form as
+        // the status-word initialisation of sr_search_run); kept out of the kernel's parameter block on purpose
+        if (!ctx->pair_ptrs) SR_CUDA(ctx, cudaMalloc(&ctx->pair_ptrs, sizeof hp));
+        PairPtrs* dp = (PairPtrs*)ctx->pair_ptrs;
+        SR_CUDA(ctx, cudaMemcpyAsync(dp, hp, sizeof(PairPtrs) * n, cudaMemcpyHostToDevice, ctx->stream));
+        a.pp = dp;
+    }
     int nwork = 0;
-    int rc = tile_work_list(ctx, g, a, ntx, rows, &a.work, &nwork);
+    // a trial run for the autotuner: the same launch on a candidate list, timed with the launch's own events
+    std::function<float(const int4*, int)> trial = [&](const int4* list, int cnt) -> float {
+        TileArgs t = a;
+        t.work = list;
+        int ok = cost == SR_COST_SAD ? dispatch_h2<SR_COST_SAD>(ctx, t, cnt) : dispatch_h2<SR_COST_SSD_L2>(ctx, t, cnt);
+        float ms = -1.f;
+        if (ok != 1 || cudaEventSynchronize(ctx->kev1) != cudaSuccess || cudaEventElapsedTime(&ms, ctx->kev0, ctx->kev1) != cudaSuccess) return -1.f;
+        return ms;
+    };
+    int rc = tile_work_list(ctx, g, a, ntx, rows, &a.work, &nwork, trial);
     if (rc != SR_OK) return rc;
     if (nwork == 0) return 1;                                // merged plane, no (tile, pass) has a candidate: all "none"
     if (cost == SR_COST_SAD) return dispatch_h2<SR_COST_SAD>(ctx, a, nwork);

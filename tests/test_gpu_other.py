@@ -315,6 +315,7 @@ def test_batch_multi_pair_launch(sr, ctx, orc, subpixel, cost):
     pairs = [capi.Pair(ctx, w, h, w, h) for _ in range(n)]
     for q, (L, R) in zip(pairs, data):
         q.upload(L, R)
+    capi.search_run_batch(ctx, pairs, p)         # first use of the two group geometries: the schedule autotuner runs here
     n0 = ctx.launches
     capi.search_run_batch(ctx, pairs, p)
     assert ctx.launches - n0 == 2 + n            # 19 pairs = groups of 16 + 3: two tile launches + one resolve / sub-pixel pass per pair

@@ -97,7 +97,7 @@ if "c5" not in skip:
         Ls.append(Lp); Rs.append(Rp); outs.append(o); hs += [lh, rh, oh]
     p = capi.search_params(block=7, min_disp=0, max_disp=D, smooth=1.0, cost=capi.COST_SAD, subpixel=True)
     lb = [Ls[i % ring] for i in range(n)]; rb = [Rs[i % ring] for i in range(n)]; ob = [outs[i % ring] for i in range(n)]
-    capi.block_search_batch(ctx, lb[:ring], rb[:ring], p, ob[:ring])
+    capi.block_search_batch(ctx, lb, rb, p, ob)            # the first call builds the ring of resident pairs
     t0 = time.perf_counter()
     capi.block_search_batch(ctx, lb, rb, p, ob)
     dt = time.perf_counter() - t0
@@ -106,6 +106,46 @@ if "c5" not in skip:
                       "seconds": round(dt, 4), "pairs_per_s": round(n / dt, 1), "effective_MDE_per_s": round(n * ev / dt / 1e6, 1),
                       "h2d_bytes_per_pair": 2 * w * h * 3, "d2h_bytes_per_pair": w * h * 8}), flush=True)
     for x in hs:
+        capi.free_pinned(x)
+if "secondary" not in skip:
+    # the reference-exact secondary paths (round-1 review: unmeasured): Left variant, varBlock, block > 17 (direct kernels,
+    # O(window) per candidate like the reference), LinearSearch; and the reference's default call end to end
+    def variant_case(tag, L, R, params, note):
+        pair = capi.Pair(ctx, L.shape[1], L.shape[0], R.shape[1], R.shape[0])
+        pair.upload(L, R)
+        ms = timed(lambda: pair.run(params))
+        w2, h2 = R.shape[1], R.shape[0]
+        D = params.max_disp - params.min_disp
+        print(json.dumps({"case": tag, "w": w2, "h": h2, "D": D, "block": params.block, "kernel_family": ctx.last_kernel, "ms": round(ms, 4),
+                          "nominal_MDE_per_s": round(w2 * h2 * D / ms / 1e3, 1), "note": note}), flush=True)
+        pair.close()
+    L, R = synth.synth_pair(0xB200, 0, 900, 750, 0, 128)
+    variant_case("left-variant", L, R, capi.search_params(variant=capi.VARIANT_LEFT, block=17, min_disp=0, max_disp=128, smooth=0.9),
+                 "computeDisparityMapLeft(0.9), Teddy-sized: top-3 candidates in parallel + row wavefront")
+    variant_case("varblock", L, R, capi.search_params(block=17, min_disp=0, max_disp=128, smooth=0.9, var_block=True, thres=19.0),
+                 "computeDisparityMapRight(0.9, varBlock = true, 19.0): per-pixel window growth, direct kernel")
+    variant_case("block-21-direct", L, R, capi.search_params(block=21, min_disp=0, max_disp=128, smooth=1.0),
+                 "windows beyond 17: direct kernel, O(window) per candidate")
+    variant_case("block-17-tile", L, R, capi.search_params(block=17, min_disp=0, max_disp=128, smooth=1.0), "the same shape through the tile kernel, for scale")
+    variant_case("linear-search", L, R, capi.search_params(variant=capi.VARIANT_LINEAR, block=1, min_disp=0, max_disp=200, smooth=1.0),
+                 "LinearSearch::computeDisparityMap(1.0): 200 candidates, one-pixel window")
+    # main.cpp:40 end to end from and to pinned host buffers: BlockSearch(17, 0, 145).computeDisparityMapRight(0.9)
+    w, h, D = 1436, 992, 145
+    L, R = synth.synth_pair(0xB200, 0, w, h, 0, D)
+    Lp, a1 = capi.pinned_empty(L.shape, np.uint8); Lp[...] = L
+    Rp, a2 = capi.pinned_empty(R.shape, np.uint8); Rp[...] = R
+    o, a3 = capi.pinned_empty((h, w), np.float64)
+    for smooth in (0.9, 1.0):
+        p = capi.search_params(block=17, min_disp=0, max_disp=D, smooth=smooth)
+        for _ in range(3):
+            capi.block_search(ctx, Lp, Rp, p, out=o)
+        t0 = time.perf_counter()
+        for _ in range(a.iters):
+            capi.block_search(ctx, Lp, Rp, p, out=o)
+        dt = (time.perf_counter() - t0) / a.iters
+        print(json.dumps({"case": "config1-shape-e2e", "w": w, "h": h, "D": D, "block": 17, "smooth": smooth, "ms": round(dt * 1e3, 4),
+                          "note": "sr_block_search from and to pinned host buffers (H2D 8.5 MB + D2H 11.4 MB inside)"}), flush=True)
+    for x in (a1, a2, a3):
         capi.free_pinned(x)
 if "recon" not in skip:
     from stereo_reconstruction_b200 import reconstruction as rec
