@@ -39,7 +39,7 @@ __device__ __forceinline__ PixRec load_rec(int from_direct, int have_c0, size_t 
         uint32_t bc = 0xFFFFFFFFu; int bd = 0;
         for (int p = 0; p < pl.npass; p++) {
             uint32_t k = __ldg(pl.planes + (size_t)p * pl.stride + i);
-            if (k != 0xFFFFFFFFu && (k >> pl.shift) < bc) { bc = k >> pl.shift; bd = pl.dbase + 64 * p + (int)(k & ((1u << pl.shift) - 1u)); }
+            if (k != 0xFFFFFFFFu && (k >> pl.shift) < bc) { bc = k >> pl.shift; bd = pl.dbase + (p << pl.shift) + (int)(k & ((1u << pl.shift) - 1u)); }
         }
         r.cr = bc == 0xFFFFFFFFu ? SR_NONE64 : (unsigned long long)bc;
         r.dr = bd;
@@ -94,7 +94,7 @@ __global__ void resolve_plain2_kernel(SearchGeom g, int have_c0 /* 0 or 2 */, Pl
         for (int e = 0; e < 2; e++)
             if (k[e] != 0xFFFFFFFFu && (k[e] >> pl.shift) < bc[e]) {
                 bc[e] = k[e] >> pl.shift;
-                bd[e] = pl.dbase + 64 * p + (int)(k[e] & ((1u << pl.shift) - 1u));
+                bd[e] = pl.dbase + (p << pl.shift) + (int)(k[e] & ((1u << pl.shift) - 1u));
             }
     }
     const uint2 c02 = have_c0 == 2 ? __ldg(reinterpret_cast<const uint2*>(c0u + i)) : make_uint2(0u, 0u);
@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(128) resolve_wire16_kernel(SearchGeom g, Plane
             for (int e = 0; e < 2; e++)
                 if (k[e] != 0xFFFFFFFFu && (k[e] >> pl.shift) < bc[e]) {
                     bc[e] = k[e] >> pl.shift;
-                    bd[e] = pl.dbase + 64 * p + (int)(k[e] & ((1u << pl.shift) - 1u));
+                    bd[e] = pl.dbase + (p << pl.shift) + (int)(k[e] & ((1u << pl.shift) - 1u));
                 }
         }
         const uint32_t px[2] = {px2.x, px2.y};

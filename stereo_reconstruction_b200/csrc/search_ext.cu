@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(128) ext_from_planes_kernel(const uint32_t* __
         uint32_t bc = 0xFFFFFFFFu; int bd = -1;
         for (int p = 0; p < npass; p++) {
             uint32_t k = __ldg(planes + (size_t)p * stride + o);
-            if (k != 0xFFFFFFFFu && (k >> shift) < bc) { bc = k >> shift; bd = dbase + 64 * p + (int)(k & ((1u << shift) - 1u)); }
+            if (k != 0xFFFFFFFFu && (k >> shift) < bc) { bc = k >> shift; bd = dbase + (p << shift) + (int)(k & ((1u << shift) - 1u)); }
         }
         if (bd >= 0) {
             dbest = bd;
@@ -268,7 +268,7 @@ __global__ void __launch_bounds__(128) ext_subpix_out_kernel(const uint32_t* __r
         uint32_t bc = 0xFFFFFFFFu; int bd = -1;
         for (int p = 0; p < npass; p++) {
             uint32_t k = __ldg(planes + (size_t)p * stride + o);
-            if (k != 0xFFFFFFFFu && (k >> shift) < bc) { bc = k >> shift; bd = dbase + 64 * p + (int)(k & ((1u << shift) - 1u)); }
+            if (k != 0xFFFFFFFFu && (k >> shift) < bc) { bc = k >> shift; bd = dbase + (p << shift) + (int)(k & ((1u << shift) - 1u)); }
         }
         if (bd >= 0) {
             dsub = (float)bd;
@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(128) left_from_mirror_planes_kernel(const uint
         uint32_t bc = 0xFFFFFFFFu;
         for (int p = 0; p < npass; p++) {
             uint32_t k = __ldg(planes + (size_t)p * stride + o);
-            if (k != 0xFFFFFFFFu && (k >> shift) < bc) { bc = k >> shift; dbest = dbase + 64 * p + (int)(k & ((1u << shift) - 1u)); }
+            if (k != 0xFFFFFFFFu && (k >> shift) < bc) { bc = k >> shift; dbest = dbase + (p << shift) + (int)(k & ((1u << shift) - 1u)); }
         }
     }
     disp[(size_t)y * w1 + x] = dbest;

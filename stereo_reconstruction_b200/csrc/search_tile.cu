@@ -128,7 +128,8 @@ constexpr int MAXP = 16;  // pairs of one launch (sr_launch_search_tile_multi)
 struct PairPtrs { const uint32_t* L; const uint32_t* R; uint32_t* planes; };
 struct TileArgs {
     int npairs;          // > 0: the work items span several pairs of one shape (item.x = tile | pair << 16), images and
-    const PairPtrs* pp;  //      key planes from pp[pair] (device array); 0: the single pair below
+    PairPtrs ppv[MAXP];  //      key planes from ppv[pair]; 0: the single pair below.  (Kept inside the parameter block: the same
+                         //      table behind a device pointer compiled to a 3 % slower SAD kernel -- 1.779 vs 1.725 ms per 4K step.)
     const uint32_t* L; int pitchL;
     const uint32_t* R; int pitchR;
     uint32_t* planes;    // one u32 key plane (cost*64 + d_local) per pass of 64 disparities
@@ -227,7 +228,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int4 wk = __ldg(a.work + blockIdx.x);
     const int CB = -XT + TILE_OUT * (wk.x & 0xFFFF);           // first own column of lane 0
     const uint32_t* imgL = a.L; const uint32_t* imgR = a.R; uint32_t* planes = a.planes;
-    if (a.npairs > 0) { const PairPtrs* pp = a.pp + (wk.x >> 16); imgL = pp->L; imgR = pp->R; planes = pp->planes; }
+    if (a.npairs > 0) { const PairPtrs pp = a.ppv[wk.x >> 16]; imgL = pp.L; imgR = pp.R; planes = pp.planes; }
     const int yb0 = wk.y, yb1 = wk.z;
     if (yb0 >= yb1) return;
     const int cb = CB + XT * lane;                             // this thread's own columns [cb, cb+16)
@@ -304,10 +305,11 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int xq = CB + h + rq;
     const bool red_on = rgrp < 31 && xq >= 0 && xq < a.w2;
     const uint32_t red_b = keys_base + 4u * (20 * rgrp + (lane & 15));
-    uint32_t* pl = planes + (a.merged ? (size_t)0 : (size_t)pass * a.plane_stride) + (size_t)yb0 * a.w2 + xq;
+    // merged: 2^(shift-6) consecutive passes share a plane (key = cost << shift | index within the plane's range)
+    uint32_t* pl = planes + (size_t)(a.merged ? pass >> (a.shift - 6) : pass) * a.plane_stride + (size_t)yb0 * a.w2 + xq;
     const bool merged = a.merged != 0;
     const int mshift = a.shift - 6;
-    const uint32_t mpass = (uint32_t)pass * (DT * NW);
+    const uint32_t mpass = (uint32_t)(pass & ((1 << mshift) - 1)) * (DT * NW);
     auto reduce_row = [&](uint32_t buf) {
         if (red_on) {
             uint32_t kk[NW];
@@ -602,18 +604,21 @@ int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const
         for (int q = 0; q < n; q++) pairs[q]->npass = 0;
         return 1;
     }
-    // Key planes.  Where cost and candidate index fit one u32 together (cost << shift | d - dbase), all passes
-    // fold into ONE plane with RED.MIN: the plane stays in L2, the kernel's DRAM writes drop from npass planes to
-    // one and the resolve pass reads one plane.  Otherwise (SSD on large windows / ranges) one plane per pass
-    // with key = cost*64 + d_local, merged by the resolve kernels.
-    int shift = 6;
-    while ((64 << (shift - 6)) < a.npass * 64) shift++;
+    // Key planes.  Where cost and candidate index fit one u32 together (cost << shift | index), 2^(shift-6) consecutive
+    // passes fold into ONE plane with RED.MIN -- all of them when the cost is small enough (SAD always; SSD on small
+    // windows / ranges), else as many as fit (SSD 9x9 at 512 disparities: 2 planes of 4 passes instead of 8 planes -- the
+    // kernel's DRAM writes drop from 209 to ~55 MB and the resolve pass reads 2 planes instead of 8).  The planes stay in
+    // L2; a plane's candidate range is [dbase + (p << shift), +2^shift).  shift == 6: one plane per pass, plain stores.
+    int full = 6;
+    while ((64 << (full - 6)) < a.npass * 64) full++;
     unsigned long long cmax = (unsigned long long)g.block * g.block * 3ull * (cost == SR_COST_SAD ? 255ull : 65025ull);
-    static const char* mg_env = getenv("SR_TILE_MERGE");    // tuning / test override
-    a.merged = a.npass > 1 && ((cmax + 1) << shift) < 0xFFFFFFFFull && !(mg_env && atoi(mg_env) == 0);
-    if (!a.merged) shift = 6;
+    static const char* mg_env = getenv("SR_TILE_MERGE");    // tuning / test override: 0 = never merge
+    int shift = 6;
+    if (!(mg_env && atoi(mg_env) == 0))
+        while (shift < full && ((cmax + 1) << (shift + 1)) < 0xFFFFFFFFull) shift++;
+    a.merged = shift > 6;
     a.shift = shift;
-    const int planes_per_pair = a.merged ? 1 : a.npass;
+    const int planes_per_pair = (a.npass + (1 << (shift - 6)) - 1) >> (shift - 6);
     uint32_t* base = (uint32_t*)sr_scratch(ctx, 0, (size_t)n * planes_per_pair * pair->npx_cap * sizeof(uint32_t));
     if (!base) return SR_E_CUDA;
     PairPtrs hp[MAXP];
@@ -623,18 +628,12 @@ int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const
         pq->planes = base + (size_t)q * planes_per_pair * pair->npx_cap;
         hp[q].L = pq->L.px; hp[q].R = pq->R.px; hp[q].planes = pq->planes;
         if (a.merged)
-            SR_CUDA(ctx, cudaMemsetAsync(pq->planes + (size_t)g.row0 * g.w2, 0xFF, (size_t)(r1 - g.row0) * g.w2 * sizeof(uint32_t), ctx->stream));
+            for (int pp = 0; pp < planes_per_pair; pp++)
+                SR_CUDA(ctx, cudaMemsetAsync(pq->planes + (size_t)pp * pair->npx_cap + (size_t)g.row0 * g.w2, 0xFF,
+                                             (size_t)(r1 - g.row0) * g.w2 * sizeof(uint32_t), ctx->stream));
     }
     a.planes = pair->planes; a.plane_stride = pair->npx_cap;
-    a.pp = nullptr;
-    if (n > 1) {
-        // the pointer table of the pairs: a small pageable H2D copy, staged by the driver at call time (the same form as
-        // the status-word initialisation of sr_search_run); kept out of the kernel's parameter block on purpose
-        if (!ctx->pair_ptrs) SR_CUDA(ctx, cudaMalloc(&ctx->pair_ptrs, sizeof hp));
-        PairPtrs* dp = (PairPtrs*)ctx->pair_ptrs;
-        SR_CUDA(ctx, cudaMemcpyAsync(dp, hp, sizeof(PairPtrs) * n, cudaMemcpyHostToDevice, ctx->stream));
-        a.pp = dp;
-    }
+    for (int q = 0; q < n; q++) a.ppv[q] = hp[q];
     int nwork = 0;
     // a trial run for the autotuner: the same launch on a candidate list, timed with the launch's own events
     std::function<float(const int4*, int)> trial = [&](const int4* list, int cnt) -> float {

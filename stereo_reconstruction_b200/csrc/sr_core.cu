@@ -88,7 +88,6 @@ void sr_ctx_destroy(sr_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     sr_stage_pool_destroy(ctx->stage_pool);
-    cudaFree(ctx->pair_ptrs);
     for (sr_pair* p : ctx->batch_pairs) sr_pair_destroy(ctx, p);
     ctx->batch_pairs.clear();
     for (cudaEvent_t e : ctx->pipe_ev) cudaEventDestroy(e);

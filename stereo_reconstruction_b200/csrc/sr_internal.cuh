@@ -54,7 +54,6 @@ struct sr_ctx {
     std::vector<sr_pair*> peer_pairs;  // pairs with a gather window: sr_ctx_sync reports their protocol status
     std::vector<cudaEvent_t> pipe_ev;  // events of the row-chunk pipeline of sr_block_search
     sr_stage_pool* stage_pool = nullptr;
-    void* pair_ptrs = nullptr;         // device table of image / key-plane pointers of a multi-pair tile launch
     std::vector<TileWork> tile_work;   // schedules of the tile kernel, by geometry
     uint64_t tile_work_clock = 0;
     bool more_chunks_follow = false;   // set by the row-chunk pipeline around all launches but the last chunk's

@@ -58,7 +58,12 @@ def algorithmic_bytes(kernel, faces, pack_rows):
         "blur_cols_out_kernel": N * (2 * 8 + 4),             # two prefix rows in, float out
         "outlier_replace_kernel": N * (4 + 4 + 4),           # disp + blurred in, disp out (upper bound: all replaced)
         "depth_backproject_kernel": N * (4 + 3 + 4 + 32),
-        "depth_backproject_faces_kernel": N * (4 + 3 + 4 + 32) + CELLS,   # + one flag byte per cell
+        # general form: float disparity in; u8 form (DispFromU8Blur): two int32 prefix values + one u8 in -- 9 B instead of 4
+        "depth_backproject_faces_kernel": N * ((9 if os.environ.get("SR_RECON_U8", "1") != "0" else 4) + 3 + 4 + 32) + CELLS,
+        # round 2: the integer-exact pipeline of the 8-bit hand-off
+        "u8_rowsum_kernel": N * (8 + 1 + 4),                 # CV_64F in, u8 map + int32 row sums out
+        "u8_cols_seg_kernel": N * 4,                         # row sums in
+        "u8_cols_prefix_kernel": N * (4 + 4),                # row sums in, int32 column prefix out ((h+k-1)/h rows of it)
         "face_blocktotal_kernel": CELLS,
         "face_count_kernel": N * 32 + CELLS,                 # every vertex once (L1/L2 serve the other three reads), flags out
         "face_scatter_kernel": CELLS + faces * 12,
