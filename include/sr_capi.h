@@ -193,6 +193,19 @@ int sr_remove_outliers(sr_ctx* ctx, float* disp, int w, int h, size_t pitch, int
                        float thr_front, float thr_back);
 /* cv::blur(disp, Size(k,k)) alone (reconstruction.cpp:8), tightly packed output. */
 int sr_box_blur(sr_ctx* ctx, const float* src, float* dst, int w, int h, int ksize);
+/* The same blur for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO counterpart in the reference.  d_src and d_dst are
+ * DEVICE pointers (tightly packed h x w floats, d_dst != d_src); the only intermediate, the fp64 row sums, lives in a
+ * file-scope __device__ array of SR_BLUR_STATIC_MAX_PIXELS doubles (8 MiB, held by every GPU that loads the library
+ * until exit).  The call makes no cudaMalloc / cudaFree / allocating library call, enqueues two kernels on `stream`
+ * (a cudaStream_t; NULL = the context's stream) and returns without synchronising; the context must have been
+ * created beforehand, and the first call per device also looks up the array's device address (cudaGetSymbolAddress),
+ * so make that call outside a capture.  w * h > SR_BLUR_STATIC_MAX_PIXELS -> SR_E_SHAPE (use sr_box_blur).  All calls
+ * share the one array: it keeps the last call's contents (nothing in it needs clearing, every value read is written
+ * first), and two calls that overlap on the GPU -- different streams, or contexts, of one device -- race.  Results
+ * are bit-identical to sr_box_blur. */
+#define SR_BLUR_STATIC_MAX_PIXELS (1u << 20)
+int sr_box_blur_static(sr_ctx* ctx, const float* d_src, float* d_dst, int w, int h, int ksize, void* stream);
 /* scaleDisparityMap(disp, f), reconstruction.cpp:21-27. */
 int sr_scale(sr_ctx* ctx, float* disp, int w, int h, size_t pitch, float f);
 /* convertDisparityToDepth(disp, focal, baseline), reconstruction.cpp:30-43. */

@@ -47,7 +47,7 @@ def test_recon_roofline_summary_of_committed_launch_list():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     out = subprocess.run([sys.executable, os.path.join(root, "tools", "recon_roofline.py"), "--summarise",
                           os.path.join(root, "profiles", "r01_launches_recon_4k.csv"), "--peak", "6553"],
-                         check=True, capture_output=True, text=True, env=dict(os.environ, SR_FACES="16026827")).stdout
+                         check=True, capture_output=True, text=True, env=dict(os.environ, SR_FACES="16026827", SR_RECON_U8="0")).stdout   # round-1 list: the general (float map) pipeline
     rows = {j["kernel"]: j for j in map(json.loads, out.splitlines())}
     n = 3840 * 2160
     assert rows["quantize_kernel"]["algorithmic_bytes"] == n * 12
