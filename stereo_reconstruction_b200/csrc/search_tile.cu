@@ -39,6 +39,7 @@ constexpr int LPOS = LCH + LCH / 4;
 constexpr int SLOT_U4 = RPOS + LPOS;  // uint4 per ring slot
 constexpr int KEY_U4 = 160;           // uint4 per warp key row (128 chunks padded)
 constexpr int PF = 2;                 // rows prefetched ahead
+#define SR_TILE_OVERSHOOT_PAD 768     // right padding of the shifted right image of the Left variant: one tile of overshoot + halo
 
 __device__ __forceinline__ int padpos(int c) { return c + (c >> 2); }
 
@@ -148,6 +149,12 @@ struct TileArgs {
     uint32_t km1;        // == 0xFFFFFFFF (-1): IMAD-based subtract
     int red_mode;        // 1: half of the warps merge the previous row's keys at the end of the iteration
     uint32_t zmask;      // bit w: warp w slides its window sums on the FMA pipe (window_wta ZMODE)
+    // Left-variant geometry (kernel template LM, BlockSearch.cpp:24-86): full window [x-h, x-h+H2) x [y-h, y-h+H2) with
+    // H2 = blockSize odd, every image column < cmax / row < rmax contributes (no clamped windows), candidate index
+    // i = off - d ascending (= d descending: the smallest i of equal costs is the LARGEST d, :76) with per-column
+    // bounds max(dlo, lo_a - x) <= i < min(dhi, lim_a - x).  w2 = width of the reference (output) image.
+    int lmode, hwin;     // hwin: window size H2 (2*half, or 2*half + 1 in lmode)
+    int cmax, rmax, lim_a, lo_a;
 };
 
 // horizontal window sums + in-thread WTA for one output row.  Disparities are processed in pairs so
@@ -159,7 +166,7 @@ struct TileArgs {
 // With the leaving-row subtract on the FMA pipe (pcost_sub) a SAD evaluation is 3.5 ALU + 2 FMA instructions
 // without ZMODE and 2.5 + 3 with it; one warp in four without ZMODE balances the pipes at 2.75 each.
 // MASKED: candidates outside [dlo, dlim(x)) are discarded (tiles that touch the break rule or the range ends).
-template <int H2, bool MASKED, bool ZMODE>
+template <int H2, bool MASKED, bool ZMODE, bool LM = false>
 __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32_t (&keys)[XT], uint32_t k64,
                                            uint32_t nk64, uint32_t dl0, int d0, int x0, const TileArgs& a) {
     constexpr int HALO = H2 - 1;
@@ -185,9 +192,10 @@ __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32
             else { ka = S0 * k64 + dla; kb = S1 * k64 + dlb; }
             if (MASKED) {
                 int x = x0 + j;
-                int lim = min(a.dhi, a.w1 - x - min(a.w2 - x - 1, a.half));
-                if (d0 + tp < a.dlo || d0 + tp >= lim) ka = 0xFFFFFFFFu;
-                if (d0 + tp + 1 < a.dlo || d0 + tp + 1 >= lim) kb = 0xFFFFFFFFu;
+                int lim = LM ? min(a.dhi, a.lim_a - x) : min(a.dhi, a.w1 - x - min(a.w2 - x - 1, a.half));
+                int lo = LM ? max(a.dlo, a.lo_a - x) : a.dlo;
+                if (d0 + tp < lo || d0 + tp >= lim) ka = 0xFFFFFFFFu;
+                if (d0 + tp + 1 < lo || d0 + tp + 1 >= lim) kb = 0xFFFFFFFFu;
             }
             keys[j] = min(min(keys[j], ka), kb);
             if (j + 1 < XT) {
@@ -212,7 +220,7 @@ __device__ __forceinline__ uint32_t lds32(uint32_t saddr) {
     return v;
 }
 
-template <int H2, int COST, int NW>
+template <int H2, int COST, int NW, bool LM = false>
 __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     constexpr int NSLOT = H2 + PF + 1;   // +1: half of the warps subtract the leaving row one iteration late
     constexpr uint32_t SLOT_B = SLOT_U4 * 16, RING_B = NSLOT * SLOT_B, KEYROW_B = KEY_U4 * 16, KEYBUF_B = NW * KEYROW_B;
@@ -223,6 +231,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler
     const int h = a.half;
+    const int e_in = LM ? H2 - 1 - h : h - 1;                  // row y + e_in enters the window of output row y (H2 == 2h unless LM)
     // One CTA per work item {tile, first row, end row, pass}.  The list is built on the host (tile_work_list):
     // the hardware hands out CTAs in list order, so the order of the list is the schedule.
     const int4 wk = __ldg(a.work + blockIdx.x);
@@ -244,19 +253,23 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     // own columns that contribute (inside [0, w2-1)); others are forced to 0
     uint32_t colmask = 0;
 #pragma unroll
-    for (int j = 0; j < XT; j++) colmask |= (uint32_t)(cb + j >= 0 && cb + j < a.w2 - 1) << j;
+    for (int j = 0; j < XT; j++) colmask |= (uint32_t)(cb + j >= 0 && cb + j < (LM ? a.cmax : a.w2 - 1)) << j;
     // per-output candidate limit: d < min(dhi, w1 - x - r(x))  (break rule, BlockSearch.cpp:148)
-    int dlim_min = 0x7fffffff;
+    auto lim_of = [&](int x) { return LM ? min(a.dhi, a.lim_a - x) : min(a.dhi, a.w1 - x - min(a.w2 - x - 1, h)); };
+    int dlim_min = 0x7fffffff, dlo_max = a.dlo;
 #pragma unroll
     for (int j = 0; j < XT; j++) {
         int x = cb + h + j;
-        if (x >= 0 && x < a.w2) dlim_min = min(dlim_min, min(a.dhi, a.w1 - x - min(a.w2 - x - 1, h)));
+        if (x >= 0 && x < a.w2) {
+            dlim_min = min(dlim_min, lim_of(x));
+            if (LM) dlo_max = max(dlo_max, a.lo_a - x);
+        }
     }
-    const bool needmask = __any_sync(0xffffffffu, d0 < a.dlo || d0 + DT - 1 >= dlim_min);
+    const bool needmask = __any_sync(0xffffffffu, d0 < dlo_max || d0 + DT - 1 >= dlim_min);
     // The break rule cuts a triangle off the (x, d) plane at the right image edge: the largest limit of
     // the tile (its first output column) decides which warps / whole CTAs have no candidate at all.
     const int x_first = max(CB + h, 0);                         // first output column of the tile inside the image (the limit never grows with x)
-    const int dlim_tile = min(a.dhi, a.w1 - x_first - min(a.w2 - x_first - 1, h));
+    const int dlim_tile = lim_of(x_first);
     const bool active = d0 < dlim_tile;                         // warps with at least one candidate
     if (dcta >= dlim_tile) {
         // nothing to search in this (tile, pass): the planes still get their "no candidate" keys
@@ -280,7 +293,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     for (int i = 0; i < 5; i++) uo[i] = 16u * (RPOS + padpos(warp + i));
     auto slot_of = [&](int r) { return (uint32_t)(((r % NSLOT) + NSLOT) % NSLOT) * SLOT_B; };
     auto next_slot = [&](uint32_t sb) { return sb + SLOT_B == RING_B ? 0u : sb + SLOT_B; };
-    auto row_ok = [&](int r) { return r >= 0 && r < a.h2 - 1; };
+    auto row_ok = [&](int r) { return r >= 0 && r < (LM ? a.rmax : a.h2 - 1); };
 
     // staging: thread t copies chunk t of every row (right chunks first, then left chunks)
     const int y_start = yb0 - (H2 - 1);
@@ -288,7 +301,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     const bool ld_right = tid < RCH;
     const uint32_t ld_dst = smem_base + 16u * (ld_right ? padpos(tid) : RPOS + padpos(tid - RCH));
     const int ld_pitch = ld_right ? a.pitchR : a.pitchL;
-    int r_pf = y_start + h - 1;                                // next row to stage
+    int r_pf = y_start + e_in;                                 // next row to stage
     const uint32_t* ld_ptr = (ld_right ? imgR : imgL + dcta) + (ptrdiff_t)r_pf * ld_pitch + CB + 4 * (ld_right ? tid : tid - RCH);
     uint32_t slot_pf = slot_of(r_pf);
     auto issue_row = [&]() {
@@ -335,7 +348,7 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
 #pragma unroll
     for (int i = 0; i < PF; i++) issue_row();                  // rows of the first PF iterations
 
-    uint32_t s_in = slot_of(y_start + h - 1), s_out = slot_of(y_start - h), s_prev = slot_of(y_start - h - 1);
+    uint32_t s_in = slot_of(y_start + e_in), s_out = slot_of(y_start - h), s_prev = slot_of(y_start - h - 1);
     const uint32_t key_st = keys_base + warp * KEYROW_B + lane_b;
     for (int y = y_start; y < yb1; y++) {
         const uint32_t buf = (y & 1) ? KEYBUF_B : 0u;
@@ -349,12 +362,12 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
             // costs) of some warps overlap the FMA-heavy window/WTA phase of the others.
             if (late_sub && y - 1 >= yb0 && row_ok(y - 1 - h) && colmask != 0)
                 vertical_update<COST, false, false>(col, smem_base + s_prev, lane_b, uo, colmask, km1);
-            if (row_ok(y + h - 1) && colmask != 0) vertical_update<COST, true, false>(col, smem_base + s_in, lane_b, uo, colmask, km1);
+            if (row_ok(y + e_in) && colmask != 0) vertical_update<COST, true, false>(col, smem_base + s_in, lane_b, uo, colmask, km1);
             if (y >= yb0) {
                 uint32_t keys[XT];
 #pragma unroll
                 for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
-                if (needmask) window_wta<H2, true, false>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
+                if (needmask) window_wta<H2, true, false, LM>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
                 else if (COST == SR_COST_SAD && zmode) window_wta<H2, false, true>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
                 else window_wta<H2, false, false>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
 #pragma unroll
@@ -375,17 +388,17 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     reduce_row(((yb1 - 1) & 1) ? KEYBUF_B : 0u);
 }
 
-template <int H2, int COST>
+template <int H2, int COST, bool LM = false>
 int launch(sr_ctx* ctx, const TileArgs& a, int nwork) {
     constexpr int NW = 16;
     size_t smem = ((size_t)(H2 + PF + 1) * SLOT_U4 + 2 * NW * KEY_U4) * sizeof(uint4);
     static DeviceOnce configured;
     if (configured.need(ctx->device)) {
-        SR_CUDA(ctx, cudaFuncSetAttribute(search_tile_kernel<H2, COST, NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(ctx, cudaFuncSetAttribute(search_tile_kernel<H2, COST, NW, LM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured.done(ctx->device);
     }
     SR_CUDA(ctx, cudaEventRecord(ctx->kev0, ctx->stream));
-    search_tile_kernel<H2, COST, NW><<<nwork, NW * 32, smem, ctx->stream>>>(a);
+    search_tile_kernel<H2, COST, NW, LM><<<nwork, NW * 32, smem, ctx->stream>>>(a);
     SR_LAUNCHED(ctx);
     SR_CUDA(ctx, cudaEventRecord(ctx->kev1, ctx->stream));
     ctx->kev_valid = true;
@@ -403,6 +416,21 @@ int dispatch_h2(sr_ctx* ctx, const TileArgs& a, int nwork) {
         case 12: return launch<12, COST>(ctx, a, nwork);
         case 14: return launch<14, COST>(ctx, a, nwork);
         case 16: return launch<16, COST>(ctx, a, nwork);
+        default: return 0;
+    }
+}
+
+// Left variant: odd windows 3 ... 17, SSD only (the reference's cost)
+int dispatch_left(sr_ctx* ctx, const TileArgs& a, int nwork) {
+    switch (a.hwin) {
+        case 3: return launch<3, SR_COST_SSD_L2, true>(ctx, a, nwork);
+        case 5: return launch<5, SR_COST_SSD_L2, true>(ctx, a, nwork);
+        case 7: return launch<7, SR_COST_SSD_L2, true>(ctx, a, nwork);
+        case 9: return launch<9, SR_COST_SSD_L2, true>(ctx, a, nwork);
+        case 11: return launch<11, SR_COST_SSD_L2, true>(ctx, a, nwork);
+        case 13: return launch<13, SR_COST_SSD_L2, true>(ctx, a, nwork);
+        case 15: return launch<15, SR_COST_SSD_L2, true>(ctx, a, nwork);
+        case 17: return launch<17, SR_COST_SSD_L2, true>(ctx, a, nwork);
         default: return 0;
     }
 }
@@ -428,13 +456,15 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
     if (tl_env) sscanf(tl_env, "%d,%d", &f_pct, &f_div);
     const int no_tail = ctx->more_chunks_follow ? 1 : 0;   // row-chunk pipeline: the next chunk's CTAs fill the end of this launch
     TileWork key;
-    const int kv[TileWork::NKEY] = {g.w1, g.w2, g.half, a.dlo, a.dhi, a.row0, a.row1, a.merged, order, f_pct * 64 + f_div, f_nb, no_tail + 2 * npairs};
+    const int kv[TileWork::NKEY] = {a.lmode ? a.lim_a : g.w1, g.w2, g.half, a.dlo, a.dhi, a.row0, a.row1, a.merged, order, f_pct * 64 + f_div, f_nb,
+                                    no_tail + 2 * npairs + 64 * a.lmode};
     for (int i = 0; i < TileWork::NKEY; i++) key.key[i] = kv[i];
     for (TileWork& t : ctx->tile_work)
         if (!memcmp(t.key, key.key, sizeof key.key)) { t.stamp = ++ctx->tile_work_clock; *work = t.dev; *nwork = t.n; return SR_OK; }
 
-    const int warm = 2 * g.half - 1, minband = 2 * g.half + 2;
+    const int warm = a.hwin - 1, minband = a.hwin + 2;
     auto dlim_at = [&](int x) {
+        if (a.lmode) return a.lim_a - x < a.dhi ? a.lim_a - x : a.dhi;
         int r = g.w2 - x - 1 < g.half ? g.w2 - x - 1 : g.half;
         return g.w1 - x - r < a.dhi ? g.w1 - x - r : a.dhi;
     };
@@ -576,7 +606,10 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
 // index: a 1280x720 / 128-disparity pair alone is 6 (tile, pass) columns for 148 SMs -- 50 bands of 15 rows, a third of
 // every CTA's rows warm-up; eight pairs make 48 columns and bands of ~100 rows.  Key planes of the pairs lie one after
 // the other in the context's scratch slot 0 (pair q: planes + q * npass * npx_cap).
-int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom& g, int cost) {
+namespace {
+// Left variant (lmode): images and bounds of the launch (see TileArgs)
+struct LeftMode { const uint32_t* searched; int pitch; int cmax, rmax, lim_a, lo_a; };
+int tile_launch_impl(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom& g, int cost, const LeftMode* lm) {
     if (n < 1 || n > MAXP) return 0;
     sr_pair* pair = pairs[0];
     if (g.half < 1 || g.half > 8) return 0;
@@ -592,6 +625,13 @@ int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const
     a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
     a.npass = (g.dhi - a.dbase + 63) / 64;
     a.row0 = g.row0; a.row1 = r1; a.k64 = 64u; a.nk64 = (uint32_t)-64; a.merged = 0; a.shift = 6; a.km1 = 0xFFFFFFFFu;
+    a.lmode = 0; a.hwin = 2 * g.half; a.cmax = a.rmax = a.lim_a = a.lo_a = 0;
+    if (lm) {
+        // reference image (window centre, output) = the LEFT image, searched image = the shifted copy of the right one
+        a.lmode = 1; a.hwin = 2 * g.half + 1;
+        a.L = lm->searched; a.pitchL = lm->pitch; a.R = pair->L.px; a.pitchR = pair->L.pitch;
+        a.cmax = lm->cmax; a.rmax = lm->rmax; a.lim_a = lm->lim_a; a.lo_a = lm->lo_a;
+    }
     // per-warp instruction mix of the SAD window phase (window_wta ZMODE); SR_TILE_ZMASK overrides for tuning
     static const char* zm_env = getenv("SR_TILE_ZMASK");
     a.zmask = zm_env ? (uint32_t)strtoul(zm_env, nullptr, 0) : 0xFFF0u;   // measured: tools/tune_tile.sh
@@ -639,7 +679,7 @@ int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const
     std::function<float(const int4*, int)> trial = [&](const int4* list, int cnt) -> float {
         TileArgs t = a;
         t.work = list;
-        int ok = cost == SR_COST_SAD ? dispatch_h2<SR_COST_SAD>(ctx, t, cnt) : dispatch_h2<SR_COST_SSD_L2>(ctx, t, cnt);
+        int ok = t.lmode ? dispatch_left(ctx, t, cnt) : cost == SR_COST_SAD ? dispatch_h2<SR_COST_SAD>(ctx, t, cnt) : dispatch_h2<SR_COST_SSD_L2>(ctx, t, cnt);
         float ms = -1.f;
         if (ok != 1 || cudaEventSynchronize(ctx->kev1) != cudaSuccess || cudaEventElapsedTime(&ms, ctx->kev0, ctx->kev1) != cudaSuccess) return -1.f;
         return ms;
@@ -647,8 +687,45 @@ int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const
     int rc = tile_work_list(ctx, g, a, ntx, rows, &a.work, &nwork, trial);
     if (rc != SR_OK) return rc;
     if (nwork == 0) return 1;                                // merged plane, no (tile, pass) has a candidate: all "none"
+    if (a.lmode) return dispatch_left(ctx, a, nwork);
     if (cost == SR_COST_SAD) return dispatch_h2<SR_COST_SAD>(ctx, a, nwork);
     return dispatch_h2<SR_COST_SSD_L2>(ctx, a, nwork);
+}
+}  // namespace
+
+int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom& g, int cost) {
+    return tile_launch_impl(ctx, pairs, n, g, cost, nullptr);
+}
+
+// Cost + first-minimum search of the Left variant (BlockSearch.cpp:24-86) through the tile kernel: per left pixel the
+// unbiased winner over cx = x - maxD ... x - 1.  The right image is packed a second time, shifted right by
+// off = maxD rounded up to 4 (pair->Rs), so that candidate index i = off - d addresses it at x + i like the Right
+// search addresses the left image: ascending i is the reference's iteration order (d descending) and the first minimum
+// is the reference's winner.  Key planes as usual (pair->planes, index i); *off_out = off.  Returns 1 when handled.
+int sr_launch_search_tile_leftvariant(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, int* off_out) {
+    const int w1 = pair->w1, h1 = pair->h1, w2 = pair->w2, h2 = pair->h2;
+    const int height = h1 < h2 ? h1 : h2, h = (block - 1) / 2;
+    if ((block & 1) == 0 || h < 1 || h > 8 || max_disp < 1 || max_disp > 4096) return 0;
+    if (height - 2 * h <= 0 || w1 - 2 * h <= 0) return 0;
+    const int off = (max_disp + 3) & ~3;
+    const int need_w = (w1 > w2 ? w1 : w2) + off;
+    if (!pair->Rs.base || pair->Rs.w < need_w || pair->Rs.h != h2) {
+        if (pair->Rs.base) { SR_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); cudaFree(pair->Rs.base); pair->Rs = PackedImage(); }
+        int rc = sr_alloc_packed(ctx, &pair->Rs, need_w, h2, SR_TILE_OVERSHOOT_PAD);
+        if (rc != SR_OK) return rc;
+    }
+    // the shift differs from call to call: clear, then pack the image columns at px + off
+    SR_CUDA(ctx, cudaMemsetAsync(pair->Rs.base, 0, (size_t)pair->Rs.pitch * h2 * sizeof(uint32_t), ctx->stream));
+    PackedImage view = pair->Rs;
+    view.px = pair->Rs.px + off; view.w = w2;
+    int rc = sr_launch_pack(ctx, pair->rawR, (size_t)w2 * 3, w2, h2, &view);
+    if (rc != SR_OK) return rc;
+    SearchGeom g;
+    g.w1 = w2; g.h1 = h2; g.w2 = w1; g.h2 = h1; g.height = height; g.block = block; g.half = h;
+    g.dlo = off - max_disp; g.dhi = off; g.row0 = h; g.row1 = height - h;
+    LeftMode lm{pair->Rs.px, pair->Rs.pitch, w1, height, w2 - h + off, h + off};
+    *off_out = off;
+    return tile_launch_impl(ctx, &pair, 1, g, SR_COST_SSD_L2, &lm);
 }
 
 int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref) {

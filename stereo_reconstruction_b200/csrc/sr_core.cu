@@ -286,7 +286,7 @@ void sr_pair_destroy(sr_ctx* ctx, sr_pair* p) {
     sr_pair_peer_detach(ctx, p); cudaFree(p->peer_counter);
     if (p->peer_status_h) cudaFreeHost(p->peer_status_h);
     if (ctx) for (size_t i = 0; i < ctx->peer_pairs.size(); i++) if (ctx->peer_pairs[i] == p) { ctx->peer_pairs.erase(ctx->peer_pairs.begin() + i); break; }
-    cudaFree(p->L.base); cudaFree(p->R.base); cudaFree(p->Lm.base); cudaFree(p->Rm.base); cudaFree(p->ncc_tab); cudaFree(p->ncc_tab_m); cudaFree(p->out16); cudaFree(p->disp_left_own); cudaFree(p->rawL); cudaFree(p->rawR);
+    cudaFree(p->L.base); cudaFree(p->R.base); cudaFree(p->Lm.base); cudaFree(p->Rm.base); cudaFree(p->Rs.base); cudaFree(p->ncc_tab); cudaFree(p->ncc_tab_m); cudaFree(p->out16); cudaFree(p->disp_left_own); cudaFree(p->rawL); cudaFree(p->rawR);
     cudaFree(p->best); cudaFree(p->c0); cudaFree(p->cr); cudaFree(p->dr); cudaFree(p->nwin);
     cudaFree(p->bits); cudaFree(p->alt); cudaFree(p->out); cudaFree(p->outf); cudaFree(p->maxblock);
     delete p;

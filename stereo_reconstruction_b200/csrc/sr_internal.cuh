@@ -81,6 +81,7 @@ struct sr_pair {
     int w1 = 0, h1 = 0, w2 = 0, h2 = 0;
     uint8_t *rawL = nullptr, *rawR = nullptr;  // BGR as uploaded, tight pitch 3*w
     PackedImage L, R;
+    PackedImage Rs;            // right image packed with a column shift (Left variant through the tile kernel, search_tile.cu)
     PackedImage Lm, Rm;        // mirror-packed copies (stored[s] = image[w1-2-s]) for the left-referenced tile search
     int pad_disp = 0;          // right padding of L covers this many disparities
     // per-pixel records of the reference-side (output) image
@@ -163,6 +164,8 @@ int sr_launch_pack_rows2(sr_ctx* ctx, const uint8_t* rawa, size_t pitcha, int wa
 // Fast path: fixed window, SSD/SAD, first minimum over [dlo,dhi) -> pair->best.
 // Returns 1 when it handled the request, 0 when the shape is not supported (caller falls back).
 int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref);
+// Left variant's unbiased winners through the tile kernel (odd blocks 3..17): key planes over the index i = *off - d
+int sr_launch_search_tile_leftvariant(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, int* off);
 // The same in ONE launch over n <= 16 pairs of one shape (batches of small pairs: more work items per band).
 int sr_launch_search_tile_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom& g, int cost);
 // Right-variant search of n pairs of one shape with one tile launch (plain result, or sub-pixel without LR check);

@@ -38,6 +38,44 @@ def test_left_vs_oracle(sr, ctx, orc, smooth):
     np.testing.assert_array_equal(got, want)
 
 
+@pytest.mark.parametrize("w1,w2,h1,h2,block,max_d,smooth,quant", [
+    (1100, 1100, 40, 40, 5, 70, 0.9, False),     # three column tiles, two passes, range not a multiple of 4
+    (600, 600, 50, 50, 17, 40, 0.9, False),      # the largest window of the tile path
+    (300, 340, 45, 40, 9, 33, 1.0, False),       # right image wider and shorter
+    (340, 300, 40, 45, 3, 130, 0.8, False),      # left image wider: partners beyond w2 - h are no candidates; three passes
+    (120, 120, 30, 30, 11, 200, 0.9, False),     # range wider than the image
+    (260, 260, 40, 40, 7, 30, 0.5, True),        # quantised colours: ties, the largest d wins; strong bias
+    (260, 260, 40, 40, 7, 30, -1.0, True),       # negative factor: biased distances below every unbiased one
+    (530, 530, 36, 36, 13, 64, 1.3, False),      # penalty (> 1): three entries per pixel from the direct kernel
+    (64, 64, 20, 20, 19, 16, 0.9, False),        # window beyond 17: direct kernel
+])
+def test_left_variant_tile_path(sr, ctx, orc, w1, w2, h1, h2, block, max_d, smooth, quant):
+    """computeDisparityMapLeft (BlockSearch.cpp:24-86): unbiased winners from the tile kernel (odd windows 3..17, candidate
+    index off - d so that the first minimum is the largest d) + the raster rule as a multi-CTA wavefront, against the
+    literal oracle, on shapes that exercise every bound of the candidate range."""
+    w, h = max(w1, w2), max(h1, h2)
+    L, R = orc.synth_pair(0xB2 + block, 3, w, h, 0, min(max_d, 60), quant)
+    L = np.ascontiguousarray(L[:h1, :w1]); R = np.ascontiguousarray(R[:h2, :w2])
+    L[h1 // 2:h1 // 2 + 4, w1 // 3:w1 // 3 + 25] = 0          # black pixels are skipped (and stay 0)
+    want = orc.block_search_left(L, R, block, max_d, smooth)
+    bs = sr.BlockSearch(L, R, block, 0, max_d, ctx=ctx)
+    got = bs.computeDisparityMapLeft(smooth)
+    np.testing.assert_array_equal(got, want)
+    np.testing.assert_array_equal(bs.computeDisparityMapLeft(smooth), want)   # again on the same pair (buffers reused)
+
+
+@pytest.mark.parametrize("grid", ["1", "2"])
+def test_left_variant_wavefront_rounds(sr, ctx, orc, monkeypatch, grid):
+    """The row wavefront with fewer CTAs than rows / 16: every warp takes several rows (rounds), the hand-over between the
+    last warp of a CTA and warp 0 of the next one (or of the next round) goes through global memory, all others through
+    the shared-memory ring -- which the leader may not overrun (rows wider than the ring)."""
+    monkeypatch.setenv("SR_LEFT_GRID", grid)
+    L, R = orc.synth_pair(77, 1, 300, 80, 0, 24, True)
+    want = orc.block_search_left(L, R, 5, 24, 0.9)
+    got = sr.BlockSearch(L, R, 5, 0, 24, ctx=ctx).computeDisparityMapLeft(0.9)
+    np.testing.assert_array_equal(got, want)
+
+
 @pytest.mark.parametrize("name,z", golden_cases("linear"), ids=lambda v: v if isinstance(v, str) else "")
 def test_linear_golden(sr, ctx, name, z):
     out = sr.LinearSearch(z["left"], z["right"], ctx=ctx).computeDisparityMap(float(z["smooth"]))

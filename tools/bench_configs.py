@@ -121,7 +121,7 @@ if "secondary" not in skip:
         pair.close()
     L, R = synth.synth_pair(0xB200, 0, 900, 750, 0, 128)
     variant_case("left-variant", L, R, capi.search_params(variant=capi.VARIANT_LEFT, block=17, min_disp=0, max_disp=128, smooth=0.9),
-                 "computeDisparityMapLeft(0.9), Teddy-sized: top-3 candidates in parallel + row wavefront")
+                 "computeDisparityMapLeft(0.9), Teddy-sized: unbiased winners from the tile kernel + multi-CTA row wavefront")
     variant_case("varblock", L, R, capi.search_params(block=17, min_disp=0, max_disp=128, smooth=0.9, var_block=True, thres=19.0),
                  "computeDisparityMapRight(0.9, varBlock = true, 19.0): per-pixel window growth, direct kernel")
     variant_case("block-21-direct", L, R, capi.search_params(block=21, min_disp=0, max_disp=128, smooth=1.0),
