@@ -250,6 +250,12 @@ int sr_write_mesh(sr_ctx* ctx, const sr_vertex* v, int w, int h, const char* fil
 /* cv::warpPerspective(src, dst, M, size, INTER_NEAREST) on CV_64F, rectification.cpp:82-87. */
 int sr_warp_nearest_f64(sr_ctx* ctx, const double* src, int sw, int sh, double* dst, int dw, int dh,
                         const double M[9]);
+/* cv::warpPerspective(image, dst, M, size) with the default INTER_LINEAR / BORDER_CONSTANT(0) on CV_8UC3: the rectifying
+ * warp of the two input images, rectification.cpp:486-493 (M = H_ / Hp_ as passed; inverted inside like OpenCV does).
+ * OpenCV's fixed-point bilinear path (1/32-pixel positions, 15-bit weights), bit-identical to cv2.warpPerspective.
+ * Row pitches in bytes.  SR_E_SHAPE for sources of 32768 pixels or more per side (cv::remap's short coordinates). */
+int sr_warp_linear_bgr(sr_ctx* ctx, const uint8_t* src, int sw, int sh, size_t src_pitch, uint8_t* dst, int dw, int dh,
+                       size_t dst_pitch, const double M[9]);
 /* evaldisp, utils.cpp:123-168.  Counts exact; serr is a double-precision sum. */
 typedef struct { int n, bad, invalid; double serr; float bad_pct, invalid_pct, total_bad_pct, avg_err; } sr_eval;
 int sr_evaldisp(sr_ctx* ctx, const float* disp, const float* gt, const uint8_t* mask, int w, int h,

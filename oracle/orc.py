@@ -186,6 +186,19 @@ def warp_nearest_f64(src, M, dsize):
     return dst
 
 
+def warp_linear_bgr(src, M, dsize):
+    """cv::warpPerspective(image, dst, M, dsize) with the default flags on CV_8UC3 (rectification.cpp:486-493)."""
+    s = np.ascontiguousarray(src, np.uint8)
+    assert s.ndim == 3 and s.shape[2] == 3
+    dw, dh = dsize
+    dst = np.empty((dh, dw, 3), np.uint8)
+    m = np.ascontiguousarray(M, np.float64).reshape(9)
+    _chk(lib().orc_warp_linear_bgr(s.ctypes.data_as(C.c_void_p), s.shape[1], s.shape[0], C.c_size_t(s.strides[0]),
+                                   dst.ctypes.data_as(C.c_void_p), dw, dh, C.c_size_t(dst.strides[0]),
+                                   m.ctypes.data_as(C.c_void_p)), "warp_linear")
+    return dst
+
+
 def quantize_u8(disp):
     d = np.ascontiguousarray(disp, np.float64)
     o = np.empty(d.shape, np.float32)

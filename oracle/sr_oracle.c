@@ -512,6 +512,50 @@ int orc_warp_nearest_f64(const double* src, int sw, int sh, double* dst, int dw,
     return ORC_OK;
 }
 
+/* cv::warpPerspective(image, dst, M, size) with the default flags (INTER_LINEAR, BORDER_CONSTANT 0) on CV_8UC3 --
+ * rectification.cpp:486-493, the rectifying warp of both input images.  OpenCV's fixed-point bilinear path
+ * (imgwarp.cpp: WarpPerspectiveInvoker + remapBilinear<FixedPtCast<int, uchar, 15>>): the landing point is computed
+ * block-wise like the nearest warp above but scaled by INTER_TAB_SIZE = 32, rounded half-to-even to integers X, Y;
+ * source pixel (X >> 5, Y >> 5) saturated to short, fractions X & 31, Y & 31; the weights come from
+ * BilinearTab_i[fy * 32 + fx] = saturate_cast<short>((1-fy/32 | fy/32) * (1-fx/32 | fx/32) * 32768) -- exact integers
+ * (32-fy)(32-fx)*32 ...; the one entry that saturates (fx = fy = 0: 32767, OpenCV then adds the missing 1 to another
+ * entry) gives the same pixel value as 32768 for every input, so the closed form below is used; value =
+ * (sum of weight * neighbour + 2^14) >> 15, a neighbour outside the image counts as the border value 0.
+ * Pinned to cv2.warpPerspective by the tests/golden warplin_* cases. */
+int orc_warp_linear_bgr(const uint8_t* src, int sw, int sh, size_t spitch, uint8_t* dst, int dw, int dh, size_t dpitch,
+                        const double M[9]) {
+    double m[9];
+    if (!invert3(M, m)) memset(m, 0, sizeof m);
+    int bh0 = dh < 16 ? dh : 16;
+    int bw0 = 1024 / bh0 < dw ? 1024 / bh0 : dw;
+    for (int y = 0; y < dh; y++)
+        for (int x = 0; x < dw; x++) {
+            int bx = x - x % bw0, x1 = x - bx;
+            double X0 = m[0]*bx + m[1]*y + m[2], Y0 = m[3]*bx + m[4]*y + m[5], W0 = m[6]*bx + m[7]*y + m[8];
+            double W = W0 + m[6]*x1;
+            W = W != 0 ? 32.0 / W : 0;
+            double fX = fmax(-2147483648.0, fmin(2147483647.0, (X0 + m[0]*x1) * W));
+            double fY = fmax(-2147483648.0, fmin(2147483647.0, (Y0 + m[3]*x1) * W));
+            long X = lrint(fX), Y = lrint(fY);
+            long sx = X >> 5, sy = Y >> 5;
+            if (sx < -32768) sx = -32768; if (sx > 32767) sx = 32767;
+            if (sy < -32768) sy = -32768; if (sy > 32767) sy = 32767;
+            int fx = (int)(X & 31), fy = (int)(Y & 31);
+            int w[4] = {(32 - fy) * (32 - fx) * 32, (32 - fy) * fx * 32, fy * (32 - fx) * 32, fy * fx * 32};
+            for (int c = 0; c < 3; c++) {
+                int acc = 1 << 14;
+                for (int k = 0; k < 4; k++) {
+                    long px = sx + (k & 1), py = sy + (k >> 1);
+                    int v = (px >= 0 && px < sw && py >= 0 && py < sh) ? src[(size_t)py * spitch + 3 * px + c] : 0;
+                    acc += v * w[k];
+                }
+                int o = acc >> 15;
+                dst[(size_t)y * dpitch + 3 * x + c] = (uint8_t)(o < 0 ? 0 : o > 255 ? 255 : o);
+            }
+        }
+    return ORC_OK;
+}
+
 int orc_quantize_u8(const double* disp, int n, float* out) {
     for (int i = 0; i < n; i++) {
         double v = disp[i];

@@ -101,6 +101,8 @@ float orc_average_disparity(const float* disp, int w, int h);
  * constant-0 border.  M is the 3x3 row-major matrix PASSED to warpPerspective (H_.inv());
  * like OpenCV it is inverted internally (no WARP_INVERSE_MAP). */
 int orc_warp_nearest_f64(const double* src, int sw, int sh, double* dst, int dw, int dh, const double M[9]);
+int orc_warp_linear_bgr(const uint8_t* src, int sw, int sh, size_t spitch, uint8_t* dst, int dw, int dh, size_t dpitch,
+                        const double M[9]);
 
 /* main.cpp:41-50: CV_64F -> 8-bit (rint half-even, saturate) -> float32. */
 int orc_quantize_u8(const double* disp, int n, float* out);

@@ -54,7 +54,7 @@ SYMBOLS = [
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
     "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
     "sr_search_kernel_ms", "sr_int_peak", "sr_pair_reconstruct_warp", "sr_average_disparity", "sr_pfm_info", "sr_read_pfm",
-    "sr_read_calib", "sr_search_run_push", "sr_pair_peer_status", "sr_search_run_batch", "sr_box_blur_static",
+    "sr_read_calib", "sr_search_run_push", "sr_pair_peer_status", "sr_search_run_batch", "sr_box_blur_static", "sr_warp_linear_bgr",
 ]
 
 _lib = None

@@ -36,6 +36,66 @@ static bool invert3(const double m[9], double o[9]) {
     return true;
 }
 
+// cv::warpPerspective(image, dst, M, size) with the default INTER_LINEAR / BORDER_CONSTANT(0) on CV_8UC3
+// (rectification.cpp:486-493: the rectifying warp of both input images).  OpenCV's fixed-point bilinear path:
+// the landing point is computed like the nearest warp's but scaled by INTER_TAB_SIZE = 32 (W = 32 / W), rounded to
+// an integer X: source pixel sx = X >> 5 (saturated to short), fraction fx = X & 31; the four neighbours are blended
+// with the 15-bit weights (32-fy)(32-fx)*32, (32-fy)fx*32, fy(32-fx)*32, fy*fx*32 (the table BilinearTab_i: products
+// of exact float fractions, so its entries are these integers; its one saturated entry, fx = fy = 0 -> 32767 with the
+// missing 1 added elsewhere, yields the same pixel value as 32768), result = (sum + 2^14) >> 15; a neighbour outside
+// the image is the border value 0.  Four pixels per thread: 12 output bytes as three words.
+__device__ __forceinline__ uint32_t warp_linear_px(const uint8_t* __restrict__ src, int sw, int sh, size_t spitch, int bw0, int x, int y,
+                                                   double m0, double m1, double m2, double m3, double m4, double m5, double m6,
+                                                   double m7, double m8) {
+    const int bx = x - x % bw0, x1 = x - bx;
+    double X0 = __dadd_rn(__dadd_rn(__dmul_rn(m0, bx), __dmul_rn(m1, y)), m2);
+    double Y0 = __dadd_rn(__dadd_rn(__dmul_rn(m3, bx), __dmul_rn(m4, y)), m5);
+    double W0 = __dadd_rn(__dadd_rn(__dmul_rn(m6, bx), __dmul_rn(m7, y)), m8);
+    double W = __dadd_rn(W0, __dmul_rn(m6, x1));
+    W = W != 0 ? __ddiv_rn(32.0, W) : 0;
+    double fX = fmax(-2147483648.0, fmin(2147483647.0, __dmul_rn(__dadd_rn(X0, __dmul_rn(m0, x1)), W)));
+    double fY = fmax(-2147483648.0, fmin(2147483647.0, __dmul_rn(__dadd_rn(Y0, __dmul_rn(m3, x1)), W)));
+    const int X = __double2int_rn(fX), Y = __double2int_rn(fY);
+    const int sx = max(-32768, min(32767, X >> 5)), sy = max(-32768, min(32767, Y >> 5));
+    const int fx = X & 31, fy = Y & 31;
+    const int w00 = (32 - fy) * (32 - fx) * 32, w01 = (32 - fy) * fx * 32, w10 = fy * (32 - fx) * 32, w11 = fy * fx * 32;
+    const bool x0 = (unsigned)sx < (unsigned)sw, x1ok = (unsigned)(sx + 1) < (unsigned)sw;
+    const bool y0 = (unsigned)sy < (unsigned)sh, y1ok = (unsigned)(sy + 1) < (unsigned)sh;
+    const uint8_t* r0 = src + (size_t)(y0 ? sy : 0) * spitch;
+    const uint8_t* r1 = src + (size_t)(y1ok ? sy + 1 : 0) * spitch;
+    const int c0 = 3 * (x0 ? sx : 0), c1 = 3 * (x1ok ? sx + 1 : 0);
+    uint32_t out = 0;
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        int p00 = (y0 && x0) ? r0[c0 + c] : 0, p01 = (y0 && x1ok) ? r0[c1 + c] : 0;
+        int p10 = (y1ok && x0) ? r1[c0 + c] : 0, p11 = (y1ok && x1ok) ? r1[c1 + c] : 0;
+        int v = (p00 * w00 + p01 * w01 + p10 * w10 + p11 * w11 + (1 << 14)) >> 15;
+        out |= (uint32_t)min(255, max(0, v)) << (8 * c);
+    }
+    return out;
+}
+
+__global__ void __launch_bounds__(128) warp_linear_bgr_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t spitch,
+                                                              uint8_t* __restrict__ dst, int dw, int dh, size_t dpitch, int bw0,
+                                                              double m0, double m1, double m2, double m3, double m4, double m5,
+                                                              double m6, double m7, double m8, int words) {
+    const int x = 4 * (blockIdx.x * blockDim.x + threadIdx.x), y = blockIdx.y;
+    if (x >= dw) return;
+    uint32_t p[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        p[i] = x + i < dw ? warp_linear_px(src, sw, sh, spitch, bw0, x + i, y, m0, m1, m2, m3, m4, m5, m6, m7, m8) : 0u;
+    uint8_t* o = dst + (size_t)y * dpitch + 3 * (size_t)x;
+    if (words && x + 3 < dw) {                                   // 4-byte aligned rows: three words
+        uint32_t* ow = reinterpret_cast<uint32_t*>(o);
+        ow[0] = p[0] | (p[1] << 24);
+        ow[1] = (p[1] >> 8) | (p[2] << 16);
+        ow[2] = (p[2] >> 16) | (p[3] << 8);
+    } else {
+        for (int i = 0; i < 4 && x + i < dw; i++) { o[3 * i] = p[i] & 255; o[3 * i + 1] = (p[i] >> 8) & 255; o[3 * i + 2] = (p[i] >> 16) & 255; }
+    }
+}
+
 // evaldisp: one thread per pixel, integer counts by atomics, serr as a double sum
 __global__ void evaldisp_kernel(const float* __restrict__ disp, const float* __restrict__ gt, const uint8_t* __restrict__ mask,
                                 size_t n, float badthresh, float maxdisp, int rounddisp, int* __restrict__ counts,
@@ -78,7 +138,38 @@ int sr_launch_warp_nearest(sr_ctx* ctx, const double* d_src, int sw, int sh, dou
     return SR_OK;
 }
 
+// the same for the bilinear warp of a CV_8UC3 image (device buffers, row pitches in bytes)
+int sr_launch_warp_linear_bgr(sr_ctx* ctx, const uint8_t* d_src, int sw, int sh, size_t spitch, uint8_t* d_dst, int dw, int dh,
+                              size_t dpitch, const double M[9]) {
+    double m[9];
+    if (!invert3(M, m)) for (double& v : m) v = 0;
+    const int bh0 = dh < 16 ? dh : 16;
+    const int bw0 = 1024 / bh0 < dw ? 1024 / bh0 : dw;
+    const int words = (((uintptr_t)d_dst | dpitch) & 3) == 0;
+    warp_linear_bgr_kernel<<<dim3(cdiv(cdiv(dw, 4), 128), dh), 128, 0, ctx->stream>>>(d_src, sw, sh, spitch, d_dst, dw, dh, dpitch, bw0, m[0], m[1],
+                                                                                       m[2], m[3], m[4], m[5], m[6], m[7], m[8], words);
+    SR_LAUNCHED(ctx);
+    return SR_OK;
+}
+
 extern "C" {
+
+int sr_warp_linear_bgr(sr_ctx* ctx, const uint8_t* src, int sw, int sh, size_t src_pitch, uint8_t* dst, int dw, int dh,
+                       size_t dst_pitch, const double M[9]) {
+    if (!ctx || !src || !dst || !M || sw <= 0 || sh <= 0 || dw <= 0 || dh <= 0 || src_pitch < (size_t)sw * 3 || dst_pitch < (size_t)dw * 3)
+        return sr_fail(ctx, SR_E_BADARG, "sr_warp_linear_bgr: bad argument");
+    if (sw >= 32768 || sh >= 32768) return sr_fail(ctx, SR_E_SHAPE, "sr_warp_linear_bgr: source beyond 32767 pixels (cv::remap's short coordinates)");
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t srow = (size_t)sw * 3, drow = ((size_t)dw * 3 + 3) & ~(size_t)3;
+    uint8_t* ds = (uint8_t*)sr_scratch(ctx, 11, srow * sh);
+    uint8_t* dd = (uint8_t*)sr_scratch(ctx, 12, drow * dh);
+    if (!ds || !dd) return SR_E_CUDA;
+    SR_CUDA(ctx, cudaMemcpy2DAsync(ds, srow, src, src_pitch, srow, sh, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = sr_launch_warp_linear_bgr(ctx, ds, sw, sh, srow, dd, dw, dh, drow, M);
+    if (rc != SR_OK) return rc;
+    SR_CUDA(ctx, cudaMemcpy2DAsync(dst, dst_pitch, dd, drow, (size_t)dw * 3, dh, cudaMemcpyDeviceToHost, ctx->stream));
+    return sr_ctx_sync(ctx);
+}
 
 int sr_warp_nearest_f64(sr_ctx* ctx, const double* src, int sw, int sh, double* dst, int dw, int dh, const double M[9]) {
     if (!ctx || !src || !dst || !M || sw <= 0 || sh <= 0 || dw <= 0 || dh <= 0) return sr_fail(ctx, SR_E_BADARG, "sr_warp_nearest_f64: bad argument");

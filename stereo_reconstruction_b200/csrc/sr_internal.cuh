@@ -183,6 +183,9 @@ int sr_launch_search_left(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, d
 int sr_launch_search_linear(sr_ctx* ctx, sr_pair* pair, double smooth);
 // cv::warpPerspective(..., INTER_NEAREST) on device buffers (misc.cu); M as passed to warpPerspective
 int sr_launch_warp_nearest(sr_ctx* ctx, const double* d_src, int sw, int sh, double* d_dst, int dw, int dh, const double M[9]);
+// cv::warpPerspective(..., INTER_LINEAR, BORDER_CONSTANT 0) on CV_8UC3 device buffers (misc.cu), rectification.cpp:486-493
+int sr_launch_warp_linear_bgr(sr_ctx* ctx, const uint8_t* d_src, int sw, int sh, size_t spitch, uint8_t* d_dst, int dw, int dh,
+                              size_t dpitch, const double M[9]);
 // band gather over peer memory (capi_peer.cu)
 int sr_peer_check(sr_ctx* ctx, sr_pair* pair);                 // SR_OK, or the sticky protocol error of this pair
 int sr_peer_wait_ack(sr_ctx* ctx, sr_pair* pair, unsigned seq); // stream-ordered: the root has consumed step seq-1

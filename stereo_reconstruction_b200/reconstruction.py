@@ -205,6 +205,29 @@ def warpPerspectiveNearest(src, M, dsize, *, ctx=None):
     return out
 
 
+def warpPerspectiveLinear(image, M, dsize, *, ctx=None):
+    """cv::warpPerspective(image, dst, M, dsize) with the default INTER_LINEAR / BORDER_CONSTANT(0) on CV_8UC3: the
+    rectifying warp of the input images (rectification.cpp:486-493); bit-identical to cv2.warpPerspective."""
+    c = _ctx(ctx)
+    s = np.asarray(image)
+    if s.dtype != np.uint8 or s.ndim != 3 or s.shape[2] != 3:
+        raise capi.SrError(capi.E_BADARG, "image must be HxWx3 uint8 (CV_8UC3)")
+    if s.strides[2] != 1 or s.strides[1] != 3:
+        s = np.ascontiguousarray(s)
+    m = np.ascontiguousarray(M, dtype=np.float64).reshape(9)
+    dw, dh = dsize
+    out = np.empty((dh, dw, 3), np.uint8)
+    c.check(c._l.sr_warp_linear_bgr(c.h, C.c_void_p(s.ctypes.data), s.shape[1], s.shape[0], C.c_size_t(s.strides[0]),
+                                    C.c_void_p(out.ctypes.data), int(dw), int(dh), C.c_size_t(out.strides[0]), C.c_void_p(m.ctypes.data)))
+    return out
+
+
+def rectifyImages(leftImage, rightImage, H, Hp, leftSize, rightSize, *, ctx=None):
+    """The two warps at the end of ImageRectifier::computeRectification (rectification.cpp:483-493): left image by H_,
+    right image by Hp_, into the rectified sizes (cols, rows) that function derives from the transformed corners."""
+    return warpPerspectiveLinear(leftImage, H, leftSize, ctx=ctx), warpPerspectiveLinear(rightImage, Hp, rightSize, ctx=ctx)
+
+
 def evaldisp(disp, gtdisp, mask, badthresh, maxdisp, rounddisp=0, *, ctx=None):
     """utils.cpp:123-168 -> dict(n, bad, invalid, bad_pct, invalid_pct, total_bad_pct, avg_err)."""
     c = _ctx(ctx)

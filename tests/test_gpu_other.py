@@ -242,6 +242,29 @@ def test_u8_handoff_pipeline_integer_exact(sr, ctx, orc, monkeypatch, w, h, k):
     pair.close()
 
 
+@pytest.mark.parametrize("name,z", golden_cases("warplin"), ids=lambda v: v if isinstance(v, str) else "")
+def test_warp_linear_golden(sr, ctx, name, z):
+    """The rectifying warp of the input images (rectification.cpp:486-493) against cv2.warpPerspective goldens."""
+    out = sr.reconstruction.warpPerspectiveLinear(z["src"], z["M"], (int(z["dw"]), int(z["dh"])), ctx=ctx)
+    np.testing.assert_array_equal(out, z["out"])
+
+
+def test_warp_linear_vs_oracle_large_and_strided(sr, ctx, orc):
+    """A 1436 x 992 image (the Teddy pair's size class) under a rectification-like homography, odd output width (byte
+    stores instead of words at the row ends), and a source view with a row stride."""
+    rng = np.random.default_rng(5)
+    big = rng.integers(0, 256, (992, 1500, 3)).astype(np.uint8)
+    src = big[:, 32:1468]                                            # strided view, 1436 wide
+    M = np.array([[0.97, -0.03, 25.0], [0.02, 1.02, -11.0], [-4e-5, 1.5e-5, 1.0]])
+    for dsize in ((1501, 1011), (1436, 992), (3, 2)):
+        want = orc.warp_linear_bgr(np.ascontiguousarray(src), M, dsize)
+        got = sr.reconstruction.warpPerspectiveLinear(src, M, dsize, ctx=ctx)
+        np.testing.assert_array_equal(got, want)
+    L2, R2 = sr.reconstruction.rectifyImages(src, src[:, ::-1], M, np.linalg.inv(M), (700, 500), (640, 480), ctx=ctx)
+    np.testing.assert_array_equal(L2, orc.warp_linear_bgr(np.ascontiguousarray(src), M, (700, 500)))
+    np.testing.assert_array_equal(R2, orc.warp_linear_bgr(np.ascontiguousarray(src[:, ::-1]), np.linalg.inv(M), (640, 480)))
+
+
 @pytest.mark.parametrize("name,z", golden_cases("warp"), ids=lambda v: v if isinstance(v, str) else "")
 def test_warp_golden(sr, ctx, orc, name, z):
     """cv2.warpPerspective(INTER_NEAREST) goldens incl. half-pixel landings, strong perspective, (near-)singular M."""

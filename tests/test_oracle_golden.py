@@ -52,6 +52,30 @@ def test_outliers_full(orc):
     assert int((d != disp).sum()) == int(z["changed"])
 
 
+@pytest.mark.parametrize("name,z", golden_cases("warplin"), ids=lambda v: v if isinstance(v, str) else "")
+def test_warp_linear(orc, name, z):
+    """cv2.warpPerspective (INTER_LINEAR, BORDER_CONSTANT 0, CV_8UC3) goldens (rectification.cpp:486-493): all 1024
+    weight-table entries, borders, strong perspective, vanishing denominator, singular matrices, saturated coordinates,
+    a shipped-image crop."""
+    out = orc.warp_linear_bgr(z["src"], z["M"], (int(z["dw"]), int(z["dh"])))
+    np.testing.assert_array_equal(out, z["out"])
+
+
+def test_warp_linear_goldens_cover_every_table_entry():
+    """The `all_fractions` case lands on each of the 32 x 32 sub-pixel fractions at least once (recomputed here in the
+    same arithmetic), so the closed-form weights stand for the whole BilinearTab_i."""
+    z = dict(golden_cases("warplin"))["warplin_all_fractions"]
+    m = np.linalg.inv(z["M"])
+    seen = set()
+    for y in range(int(z["dh"])):
+        for x in range(int(z["dw"])):
+            w = m[2, 0] * x + m[2, 1] * y + m[2, 2]
+            X = int(np.rint((m[0, 0] * x + m[0, 1] * y + m[0, 2]) * 32 / w)); Y = int(np.rint((m[1, 0] * x + m[1, 1] * y + m[1, 2]) * 32 / w))
+            if 0 <= X >> 5 < z["src"].shape[1] - 1 and 0 <= Y >> 5 < z["src"].shape[0] - 1:
+                seen.add((Y & 31, X & 31))
+    assert len(seen) == 1024
+
+
 @pytest.mark.parametrize("name,z", golden_cases("warp"), ids=lambda v: v if isinstance(v, str) else "")
 def test_warp_nearest(orc, name, z):
     """cv2.warpPerspective(INTER_NEAREST) goldens (rectification.cpp:82-87): half-pixel landings, strong perspective,
