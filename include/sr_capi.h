@@ -122,6 +122,9 @@ typedef struct sr_pair sr_pair;
 int sr_pair_create(sr_ctx* ctx, int w1, int h1, int w2, int h2, sr_pair** out);
 void sr_pair_destroy(sr_ctx* ctx, sr_pair* pair);
 int sr_pair_upload(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_image* right);
+/* The same with the rectifying warp on the device: the un-rectified images go up, cv::warpPerspective(image, H) of
+ * rectification.cpp:486-493 (sr_warp_linear_bgr) fills the pair, whose sizes are the rectified sizes. */
+int sr_pair_upload_warped(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const double H[9], const sr_image* right, const double Hp[9]);
 /* Kernels only, asynchronous on the context stream; result stays in HBM.
  * rows [row0,row1) of the output are computed (pass 0,h for the full image; used for
  * row-band sharding -- a band needs smooth == 1). */

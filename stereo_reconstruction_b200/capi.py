@@ -54,7 +54,7 @@ SYMBOLS = [
     "sr_backproject", "sr_mesh_faces", "sr_reconstruct", "sr_pair_reconstruct", "sr_write_mesh",
     "sr_warp_nearest_f64", "sr_evaldisp", "sr_write_pfm", "sr_write_ply", "sr_band_rows", "sr_l2_flush",
     "sr_search_kernel_ms", "sr_int_peak", "sr_pair_reconstruct_warp", "sr_average_disparity", "sr_pfm_info", "sr_read_pfm",
-    "sr_read_calib", "sr_search_run_push", "sr_pair_peer_status", "sr_search_run_batch", "sr_box_blur_static", "sr_warp_linear_bgr",
+    "sr_read_calib", "sr_search_run_push", "sr_pair_peer_status", "sr_search_run_batch", "sr_box_blur_static", "sr_warp_linear_bgr", "sr_pair_upload_warped",
 ]
 
 _lib = None
@@ -227,6 +227,16 @@ class Pair:
         ra, ri = image(right)
         self.ctx.check(self.ctx._l.sr_pair_upload(self.ctx.h, self.h, C.byref(li), C.byref(ri)))
         self.ctx.sync()  # la/ra may be temporaries
+
+    def upload_warped(self, left, H, right, Hp):
+        """Un-rectified images up, rectifying warp (rectification.cpp:486-493) on the device into this pair, whose
+        sizes are the rectified sizes (sr_pair_upload_warped)."""
+        la, li = image(left)
+        ra, ri = image(right)
+        h = np.ascontiguousarray(H, np.float64).reshape(9); hp = np.ascontiguousarray(Hp, np.float64).reshape(9)
+        self.ctx.check(self.ctx._l.sr_pair_upload_warped(self.ctx.h, self.h, C.byref(li), C.c_void_p(h.ctypes.data),
+                                                         C.byref(ri), C.c_void_p(hp.ctypes.data)))
+        self.ctx.sync()
 
     def run(self, params, row0=0, row1=None):
         if row1 is None:

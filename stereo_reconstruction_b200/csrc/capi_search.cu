@@ -325,9 +325,15 @@ int sr_search_run_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const sr_sear
     }
     int handled = sr_launch_search_tile_multi(ctx, pairs, n, g, p->cost);
     if (handled <= 0) return handled;
-    for (int q = 0; q < n; q++) {
-        int rc = p->subpixel ? sr_launch_ext_subpix_out(ctx, pairs[q], p, 0, g.h2) : sr_launch_resolve_right(ctx, pairs[q], g, 1.0, 0, 0);
+    if (p->subpixel) {                                   // one launch for the group
+        int rc = sr_launch_ext_subpix_out_multi(ctx, pairs, n, p, 0, g.h2);
         if (rc != SR_OK) return rc;
+    }
+    for (int q = 0; q < n; q++) {
+        if (!p->subpixel) {
+            int rc = sr_launch_resolve_right(ctx, pairs[q], g, 1.0, 0, 0);
+            if (rc != SR_OK) return rc;
+        }
         pairs[q]->last_geom = g;
         pairs[q]->evals_valid = !p->subpixel;
     }

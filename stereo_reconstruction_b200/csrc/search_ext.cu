@@ -255,11 +255,19 @@ __global__ void __launch_bounds__(128) ext_from_planes_kernel(const uint32_t* __
 // parabola neighbours recomputed in ONE walk over the window (the right-image pixel is loaded once for both, packed
 // BGRx words, VABSDIFF4.ACC / IDP.4A), sub-pixel value written straight into the CV_64F map -- one kernel instead of
 // ext_from_planes_kernel (generic seven-moment window statistics, twice) + ext_finish_kernel.
-template <int COST>
-__global__ void __launch_bounds__(128) ext_subpix_out_kernel(const uint32_t* __restrict__ Lp, int pitchL,
-                                                             const uint32_t* __restrict__ Rp, int pitchR, ExtGeom g,
-                                                             const uint32_t* __restrict__ planes, size_t stride, int npass,
-                                                             int dbase, int shift, double* __restrict__ out) {
+// Several pairs of one shape in one launch (blockIdx.z = pair): batches of small pairs.
+struct SubpixPairs { const uint32_t* L[16]; const uint32_t* R[16]; const uint32_t* planes[16]; double* out[16]; };
+
+// HALF > 0: instantiated for that window; interior pixels (full 2*HALF x 2*HALF window) take a fully unrolled walk --
+// all loads of a window row are independent and in flight together (the generic loops below are latency-bound:
+// 27 -> 15 us on a 1280x720 pair with a 7x7 block).
+template <int COST, int HALF>
+__global__ void __launch_bounds__(128) ext_subpix_out_kernel(SubpixPairs pp, int pitchL, int pitchR, ExtGeom g,
+                                                             size_t stride, int npass, int dbase, int shift) {
+    const uint32_t* __restrict__ Lp = pp.L[blockIdx.z];
+    const uint32_t* __restrict__ Rp = pp.R[blockIdx.z];
+    const uint32_t* __restrict__ planes = pp.planes[blockIdx.z];
+    double* __restrict__ out = pp.out[blockIdx.z];
     int x = blockIdx.x * blockDim.x + threadIdx.x, y = g.row0 + blockIdx.y;
     if (x >= g.wr) return;
     size_t o = (size_t)y * g.wr + x;
@@ -275,20 +283,43 @@ __global__ void __launch_bounds__(128) ext_subpix_out_kernel(const uint32_t* __r
             const int l = min(x, g.half), r = min(g.wr - x - 1, g.half), u = min(y, g.half), dn = min(g.hr - y - 1, g.half);
             if (bd - 1 >= g.dlo && bd + 1 < g.dhi && x + bd + 1 + r < g.wo) {
                 uint32_t cm = 0, cp = 0;   // a window of < 2^14 pixels fits 32 bits for both costs
-                for (int rr = y - u; rr < y + dn; rr++) {
-                    const uint32_t* rrow = Rp + (size_t)rr * pitchR + (x - l);
-                    const uint32_t* lrow = Lp + (size_t)rr * pitchL + (x - l + bd);
-                    // the two windows are two columns apart: one left-image load per column feeds both (a three-word shift)
-                    uint32_t a = __ldg(lrow - 1), mid = __ldg(lrow), b;
-                    for (int i = 0; i < l + r; i++, a = mid, mid = b) {
-                        const uint32_t q = __ldg(rrow + i);
-                        b = __ldg(lrow + i + 1);
-                        if (COST == SR_COST_SAD) {
-                            asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(cm) : "r"(a), "r"(q));
-                            asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(cp) : "r"(b), "r"(q));
-                        } else {
-                            const uint32_t da = __vabsdiffu4(a, q), db = __vabsdiffu4(b, q);
-                            cm = __dp4a(da, da, cm); cp = __dp4a(db, db, cp);
+                if (HALF > 0 && l == HALF && r == HALF && u == HALF && dn == HALF) {
+#pragma unroll
+                    for (int rr = 0; rr < 2 * HALF; rr++) {
+                        const uint32_t* rrow = Rp + (size_t)(y - HALF + rr) * pitchR + (x - HALF);
+                        const uint32_t* lrow = Lp + (size_t)(y - HALF + rr) * pitchL + (x - HALF + bd);
+                        uint32_t lv[2 * HALF + 2], q[HALF > 0 ? 2 * HALF : 1];
+#pragma unroll
+                        for (int i = 0; i < 2 * HALF + 2; i++) lv[i] = __ldg(lrow + i - 1);
+#pragma unroll
+                        for (int i = 0; i < 2 * HALF; i++) q[i] = __ldg(rrow + i);
+#pragma unroll
+                        for (int i = 0; i < 2 * HALF; i++) {
+                            if (COST == SR_COST_SAD) {
+                                asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(cm) : "r"(lv[i]), "r"(q[i]));
+                                asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(cp) : "r"(lv[i + 2]), "r"(q[i]));
+                            } else {
+                                const uint32_t da = __vabsdiffu4(lv[i], q[i]), db = __vabsdiffu4(lv[i + 2], q[i]);
+                                cm = __dp4a(da, da, cm); cp = __dp4a(db, db, cp);
+                            }
+                        }
+                    }
+                } else {
+                    for (int rr = y - u; rr < y + dn; rr++) {
+                        const uint32_t* rrow = Rp + (size_t)rr * pitchR + (x - l);
+                        const uint32_t* lrow = Lp + (size_t)rr * pitchL + (x - l + bd);
+                        // the two windows are two columns apart: one left-image load per column feeds both (a three-word shift)
+                        uint32_t a = __ldg(lrow - 1), mid = __ldg(lrow), b;
+                        for (int i = 0; i < l + r; i++, a = mid, mid = b) {
+                            const uint32_t q = __ldg(rrow + i);
+                            b = __ldg(lrow + i + 1);
+                            if (COST == SR_COST_SAD) {
+                                asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(cm) : "r"(a), "r"(q));
+                                asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(cp) : "r"(b), "r"(q));
+                            } else {
+                                const uint32_t da = __vabsdiffu4(a, q), db = __vabsdiffu4(b, q);
+                                cm = __dp4a(da, da, cm); cp = __dp4a(db, db, cp);
+                            }
                         }
                     }
                 }
@@ -382,20 +413,44 @@ bool sr_ext_subpix_out_applies(const sr_search_params* p) {
     return p->subpixel && !p->lr_check && (p->cost == SR_COST_SAD || p->cost == SR_COST_SSD_L2) &&
            3ull * p->block * p->block * 65025ull < 0xFFFFFFFFull;
 }
-int sr_launch_ext_subpix_out(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1) {
+template <int COST>
+static void launch_subpix(sr_ctx* ctx, dim3 grid, const SubpixPairs& pp, sr_pair* pair, const ExtGeom& g) {
+#define SR_SUBPIX(H) ext_subpix_out_kernel<COST, H><<<grid, 128, 0, ctx->stream>>>(pp, pair->L.pitch, pair->R.pitch, g, pair->npx_cap, \
+                                                                                    pair->npass, pair->plane_dbase, pair->key_shift)
+    switch (g.half) {                                    // the common small windows get the unrolled interior walk
+        case 1: SR_SUBPIX(1); break;
+        case 2: SR_SUBPIX(2); break;
+        case 3: SR_SUBPIX(3); break;
+        case 4: SR_SUBPIX(4); break;
+        default: SR_SUBPIX(0); break;
+    }
+#undef SR_SUBPIX
+}
+
+// n pairs of one shape and one search (same planes layout): one launch
+int sr_launch_ext_subpix_out_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const sr_search_params* p, int row0, int row1) {
+    if (n < 1 || n > 16) return sr_fail(ctx, SR_E_BADARG, "sr_launch_ext_subpix_out_multi: 1..16 pairs");
+    sr_pair* pair = pairs[0];
     const int w1 = pair->w1, h1 = pair->h1, w2 = pair->w2, h2 = pair->h2, half = (p->block - 1) / 2;
     int dhi = p->max_disp, dlo = p->min_disp;
     if (dhi < dlo) dhi = dlo;
     ExtGeom g{w2, h2, w1, h1, h1 < h2 ? h1 : h2, half, dlo, dhi, 0, p->cost, row0};
-    dim3 grid(cdiv(w2, 128), row1 - row0);
-    if (p->cost == SR_COST_SAD)
-        ext_subpix_out_kernel<SR_COST_SAD><<<grid, 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, pair->planes,
-                                                                          pair->npx_cap, pair->npass, pair->plane_dbase, pair->key_shift, pair->out);
-    else
-        ext_subpix_out_kernel<SR_COST_SSD_L2><<<grid, 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, g, pair->planes,
-                                                                             pair->npx_cap, pair->npass, pair->plane_dbase, pair->key_shift, pair->out);
+    SubpixPairs pp;
+    for (int q = 0; q < n; q++) {
+        sr_pair* pq = pairs[q];
+        if (pq->L.pitch != pair->L.pitch || pq->R.pitch != pair->R.pitch || pq->npass != pair->npass || pq->key_shift != pair->key_shift ||
+            pq->plane_dbase != pair->plane_dbase || pq->npx_cap != pair->npx_cap)
+            return sr_fail(ctx, SR_E_BADARG, "sr_launch_ext_subpix_out_multi: pairs of different layout");
+        pp.L[q] = pq->L.px; pp.R[q] = pq->R.px; pp.planes[q] = pq->planes; pp.out[q] = pq->out;
+    }
+    dim3 grid(cdiv(w2, 128), row1 - row0, n);
+    if (p->cost == SR_COST_SAD) launch_subpix<SR_COST_SAD>(ctx, grid, pp, pair, g);
+    else launch_subpix<SR_COST_SSD_L2>(ctx, grid, pp, pair, g);
     SR_LAUNCHED(ctx);
     return SR_OK;
+}
+int sr_launch_ext_subpix_out(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1) {
+    return sr_launch_ext_subpix_out_multi(ctx, &pair, 1, p, row0, row1);
 }
 
 static int rows_fit_ext(int ho, int hr, int half) {

@@ -323,4 +323,29 @@ int sr_pair_upload(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const sr_im
     return upload_one(ctx, right, pair->rawR, &pair->R, 1);
 }
 
+// The un-rectified images go up, the rectified ones are made on the device (rectification.cpp:486-493: bilinear
+// warpPerspective by H_ / Hp_) straight into the pair's raw BGR buffers and packed there: the rectified images never
+// exist on the host.  The pair's sizes are the rectified sizes.
+static int upload_warped_one(sr_ctx* ctx, const sr_image* im, const double M[9], uint8_t* raw, int w, int h, PackedImage* pk, int slot) {
+    size_t row = (size_t)im->w * 3;
+    if (im->pitch < row) return sr_fail(ctx, SR_E_BADARG, "image pitch %zu smaller than a row (%zu)", im->pitch, row);
+    if (im->w >= 32768 || im->h >= 32768) return sr_fail(ctx, SR_E_SHAPE, "source beyond 32767 pixels (cv::remap's short coordinates)");
+    uint8_t* d_src = (uint8_t*)sr_scratch(ctx, 11 + slot, row * im->h);
+    if (!d_src) return SR_E_CUDA;
+    SR_CUDA(ctx, cudaMemcpy2DAsync(d_src, row, im->bgr, im->pitch, row, im->h, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = sr_launch_warp_linear_bgr(ctx, d_src, im->w, im->h, row, raw, w, h, (size_t)w * 3, M);
+    if (rc != SR_OK) return rc;
+    return sr_launch_pack(ctx, raw, (size_t)w * 3, w, h, pk);
+}
+
+int sr_pair_upload_warped(sr_ctx* ctx, sr_pair* pair, const sr_image* left, const double H[9], const sr_image* right, const double Hp[9]) {
+    if (!ctx || !pair || !left || !right || !left->bgr || !right->bgr || !H || !Hp)
+        return sr_fail(ctx, SR_E_BADARG, "sr_pair_upload_warped: NULL argument");
+    if (left->w <= 0 || left->h <= 0 || right->w <= 0 || right->h <= 0) return sr_fail(ctx, SR_E_BADARG, "sr_pair_upload_warped: empty image");
+    SR_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = upload_warped_one(ctx, left, H, pair->rawL, pair->w1, pair->h1, &pair->L, 0);
+    if (rc != SR_OK) return rc;
+    return upload_warped_one(ctx, right, Hp, pair->rawR, pair->w2, pair->h2, &pair->R, 1);
+}
+
 }  // extern "C"

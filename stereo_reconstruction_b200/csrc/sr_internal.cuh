@@ -196,5 +196,6 @@ int sr_launch_count_evals(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g);
 int sr_launch_search_ncc(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, float** pscore, int** pdisp, void** tab);
 bool sr_ext_subpix_out_applies(const sr_search_params* p);
 int sr_launch_ext_subpix_out(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1);
+int sr_launch_ext_subpix_out_multi(sr_ctx* ctx, sr_pair* const* pairs, int n, const sr_search_params* p, int row0, int row1);
 // NCC / sub-pixel / LR-check extension path (search_ext.cu)
 int sr_search_run_ext(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row0, int row1);
