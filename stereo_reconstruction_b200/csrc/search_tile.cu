@@ -154,6 +154,7 @@ struct TileArgs {
     // i = off - d ascending (= d descending: the smallest i of equal costs is the LARGEST d, :76) with per-column
     // bounds max(dlo, lo_a - x) <= i < min(dhi, lim_a - x).  w2 = width of the reference (output) image.
     int lmode, hwin;     // hwin: window size H2 (2*half, or 2*half + 1 in lmode)
+    int pw;              // candidates per pass: 64 (16 warps, one CTA per SM) or 32 (8 warps, two CTAs per SM)
     int cmax, rmax, lim_a, lo_a;
 };
 
@@ -221,11 +222,15 @@ __device__ __forceinline__ uint32_t lds32(uint32_t saddr) {
 }
 
 template <int H2, int COST, int NW, bool LM = false>
-__global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
+__global__ void __launch_bounds__(NW * 32, NW <= 8 ? 2 : 1) search_tile_kernel(TileArgs a) {
     constexpr int NSLOT = H2 + PF + 1;   // +1: half of the warps subtract the leaving row one iteration late
     constexpr uint32_t SLOT_B = SLOT_U4 * 16, RING_B = NSLOT * SLOT_B, KEYROW_B = KEY_U4 * 16, KEYBUF_B = NW * KEYROW_B;
-    static_assert(RCH + LCH <= NW * 32, "one staged chunk per thread");
-    static_assert(TILE_OUT <= NW * 32, "one output column per thread in the key reduction");
+    // NW = 16: one CTA per SM, 64 candidates per pass.  NW = 8: two CTAs per SM that are not synchronised with each other
+    // (their phases drift apart and fill each other's barrier / single-pipe phases), 32 candidates per pass; every thread
+    // then stages up to two chunks per row and owns two columns of the key reduction.
+    constexpr int NST = (RCH + LCH + NW * 32 - 1) / (NW * 32);   // staged chunks per thread and row
+    constexpr int NRG = 32 / (2 * NW) > 0 ? 32 / (2 * NW) : 1;   // 16-column groups per half-warp in the key reduction
+    static_assert(NST * NW * 32 >= RCH + LCH && NRG * 2 * NW * XT >= TILE_OUT, "staging / key reduction cover the tile");
     extern __shared__ __align__(128) uint4 smem4[];   // ring: NSLOT x SLOT_U4, then keys: 2 x NW x KEY_U4
 
     const int tid = threadIdx.x, lane = tid & 31;
@@ -297,45 +302,59 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
 
     // staging: thread t copies chunk t of every row (right chunks first, then left chunks)
     const int y_start = yb0 - (H2 - 1);
-    const bool ld_on = tid < RCH + LCH;
-    const bool ld_right = tid < RCH;
-    const uint32_t ld_dst = smem_base + 16u * (ld_right ? padpos(tid) : RPOS + padpos(tid - RCH));
-    const int ld_pitch = ld_right ? a.pitchR : a.pitchL;
     int r_pf = y_start + e_in;                                 // next row to stage
-    const uint32_t* ld_ptr = (ld_right ? imgR : imgL + dcta) + (ptrdiff_t)r_pf * ld_pitch + CB + 4 * (ld_right ? tid : tid - RCH);
+    bool ld_on[NST]; uint32_t ld_dst[NST]; int ld_pitch[NST]; const uint32_t* ld_ptr[NST];
+#pragma unroll
+    for (int c = 0; c < NST; c++) {
+        const int ch = tid + c * NW * 32;
+        const bool ld_right = ch < RCH;
+        ld_on[c] = ch < RCH + LCH;
+        ld_dst[c] = smem_base + 16u * (ld_right ? padpos(ch) : RPOS + padpos(ch - RCH));
+        ld_pitch[c] = ld_right ? a.pitchR : a.pitchL;
+        ld_ptr[c] = (ld_right ? imgR : imgL + dcta) + (ptrdiff_t)r_pf * ld_pitch[c] + CB + 4 * (ld_right ? ch : ch - RCH);
+    }
     uint32_t slot_pf = slot_of(r_pf);
     auto issue_row = [&]() {
-        if (row_ok(r_pf) && ld_on) cp_async16_s(slot_pf + ld_dst, ld_ptr);
+        const bool ok = row_ok(r_pf);
+#pragma unroll
+        for (int c = 0; c < NST; c++) {
+            if (ok && ld_on[c]) cp_async16_s(slot_pf + ld_dst[c], ld_ptr[c]);
+            ld_ptr[c] += ld_pitch[c];
+        }
         cp_async_commit();
-        r_pf++; ld_ptr += ld_pitch; slot_pf = next_slot(slot_pf);
+        r_pf++; slot_pf = next_slot(slot_pf);
     };
 
     // key reduction: each half-warp owns one 16-column group (= one thread's columns in the key row,
     // 20 words apart because of the padding).  The two groups of a warp are 4 apart: their bank
     // ranges [20g, 20g+16) and [20g+80, 20g+96) mod 32 are disjoint, so the LDS is conflict-free.
-    const int rgrp = (warp >> 2) * 8 + (warp & 3) + ((lane >> 4) << 2);
+    const int rgrp = (warp >> 2) * 8 + (warp & 3) + ((lane >> 4) << 2);   // + 16 for the second group (NW = 8)
     const int rq = XT * rgrp + (lane & 15);
     const int xq = CB + h + rq;
-    const bool red_on = rgrp < 31 && xq >= 0 && xq < a.w2;
+    bool red_on[NRG];
+#pragma unroll
+    for (int r = 0; r < NRG; r++) red_on[r] = rgrp + 16 * r < 31 && xq + 16 * XT * r >= 0 && xq + 16 * XT * r < a.w2;
     const uint32_t red_b = keys_base + 4u * (20 * rgrp + (lane & 15));
     // merged: 2^(shift-6) consecutive passes share a plane (key = cost << shift | index within the plane's range)
-    uint32_t* pl = planes + (size_t)(a.merged ? pass >> (a.shift - 6) : pass) * a.plane_stride + (size_t)yb0 * a.w2 + xq;
+    uint32_t* pl = planes + (size_t)(a.merged ? (pass * (DT * NW)) >> a.shift : pass) * a.plane_stride + (size_t)yb0 * a.w2 + xq;
     const bool merged = a.merged != 0;
     const int mshift = a.shift - 6;
-    const uint32_t mpass = (uint32_t)(pass & ((1 << mshift) - 1)) * (DT * NW);
+    const uint32_t mpass = (uint32_t)((pass * (DT * NW)) & ((64 << mshift) - 1));   // first candidate of the pass within its plane
     auto reduce_row = [&](uint32_t buf) {
-        if (red_on) {
-            uint32_t kk[NW];
 #pragma unroll
-            for (int w = 0; w < NW; w++) kk[w] = lds32(red_b + buf + w * KEYROW_B);
-            uint32_t k = 0xFFFFFFFFu;
+        for (int r = 0; r < NRG; r++)
+            if (red_on[r]) {
+                uint32_t kk[NW];
 #pragma unroll
-            for (int w = 0; w < NW; w++) k = min(k, kk[w]);
-            // merged: the key carries the global candidate index, so the first minimum over all passes is one
-            // fire-and-forget RED.MIN in L2 (the plane is preset to "none")
-            if (merged) { if (k != 0xFFFFFFFFu) atomicMin(pl, ((k & ~63u) << mshift) + (mpass + (k & 63u))); }
-            else *pl = k;
-        }
+                for (int w = 0; w < NW; w++) kk[w] = lds32(red_b + 4u * (20 * 16 * r) + buf + w * KEYROW_B);
+                uint32_t k = 0xFFFFFFFFu;
+#pragma unroll
+                for (int w = 0; w < NW; w++) k = min(k, kk[w]);
+                // merged: the key carries the global candidate index, so the first minimum over all passes is one
+                // fire-and-forget RED.MIN in L2 (the plane is preset to "none")
+                if (merged) { if (k != 0xFFFFFFFFu) atomicMin(pl + 16 * XT * r, ((k & ~63u) << mshift) + (mpass + (k & 63u))); }
+                else pl[16 * XT * r] = k;
+            }
         pl += a.w2;
     };
 
@@ -388,9 +407,8 @@ __global__ void __launch_bounds__(NW * 32, 1) search_tile_kernel(TileArgs a) {
     reduce_row(((yb1 - 1) & 1) ? KEYBUF_B : 0u);
 }
 
-template <int H2, int COST, bool LM = false>
+template <int H2, int COST, bool LM = false, int NW = 16>
 int launch(sr_ctx* ctx, const TileArgs& a, int nwork) {
-    constexpr int NW = 16;
     size_t smem = ((size_t)(H2 + PF + 1) * SLOT_U4 + 2 * NW * KEY_U4) * sizeof(uint4);
     static DeviceOnce configured;
     if (configured.need(ctx->device)) {
@@ -408,11 +426,11 @@ int launch(sr_ctx* ctx, const TileArgs& a, int nwork) {
 template <int COST>
 int dispatch_h2(sr_ctx* ctx, const TileArgs& a, int nwork) {
     switch (2 * a.half) {
-        case 2: return launch<2, COST>(ctx, a, nwork);
-        case 4: return launch<4, COST>(ctx, a, nwork);
-        case 6: return launch<6, COST>(ctx, a, nwork);
-        case 8: return launch<8, COST>(ctx, a, nwork);
-        case 10: return launch<10, COST>(ctx, a, nwork);
+        case 2: return a.pw == 32 ? launch<2, COST, false, 8>(ctx, a, nwork) : launch<2, COST>(ctx, a, nwork);
+        case 4: return a.pw == 32 ? launch<4, COST, false, 8>(ctx, a, nwork) : launch<4, COST>(ctx, a, nwork);
+        case 6: return a.pw == 32 ? launch<6, COST, false, 8>(ctx, a, nwork) : launch<6, COST>(ctx, a, nwork);
+        case 8: return a.pw == 32 ? launch<8, COST, false, 8>(ctx, a, nwork) : launch<8, COST>(ctx, a, nwork);
+        case 10: return a.pw == 32 ? launch<10, COST, false, 8>(ctx, a, nwork) : launch<10, COST>(ctx, a, nwork);
         case 12: return launch<12, COST>(ctx, a, nwork);
         case 14: return launch<14, COST>(ctx, a, nwork);
         case 16: return launch<16, COST>(ctx, a, nwork);
@@ -457,7 +475,7 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
     const int no_tail = ctx->more_chunks_follow ? 1 : 0;   // row-chunk pipeline: the next chunk's CTAs fill the end of this launch
     TileWork key;
     const int kv[TileWork::NKEY] = {a.lmode ? a.lim_a : g.w1, g.w2, g.half, a.dlo, a.dhi, a.row0, a.row1, a.merged, order, f_pct * 64 + f_div, f_nb,
-                                    no_tail + 2 * npairs + 64 * a.lmode};
+                                    no_tail + 2 * npairs + 64 * a.lmode + 128 * (a.pw == 32)};
     for (int i = 0; i < TileWork::NKEY; i++) key.key[i] = kv[i];
     for (TileWork& t : ctx->tile_work)
         if (!memcmp(t.key, key.key, sizeof key.key)) { t.stamp = ++ctx->tile_work_clock; *work = t.dev; *nwork = t.n; return SR_OK; }
@@ -469,7 +487,7 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
         return g.w1 - x - r < a.dhi ? g.w1 - x - r : a.dhi;
     };
     auto x_first_of = [&](int tile) { int x = -XT + TILE_OUT * tile + g.half; return x < 0 ? 0 : x; };
-    auto has_candidates = [&](int tile, int pass) { return a.dbase + 64 * pass < dlim_at(x_first_of(tile & 0xFFFF)); };
+    auto has_candidates = [&](int tile, int pass) { return a.dbase + a.pw * pass < dlim_at(x_first_of(tile & 0xFFFF)); };
     // (tile, pass) columns in launch order within a band, with their relative cost per row
     struct Col { int tile, pass; };
     std::vector<Col> cols;
@@ -517,11 +535,12 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
     std::vector<int2> best_bands;
     if (!cols.empty()) {
         const int maxnb = rows / minband < 1 ? 1 : (rows / minband > 256 ? 256 : rows / minband);
+        const int slots = ctx->sms * (a.pw == 32 ? 2 : 1);     // CTAs resident at a time
         int nb_best = 1;
         double best = -1;
         for (int nb = 1; nb <= maxnb; nb++) {
             int bnd = (rows + nb - 1) / nb, nbe = (rows + bnd - 1) / bnd;
-            double c = ((double)cols.size() * nbe + ctx->sms) / ctx->sms * (bnd + warm + 2);
+            double c = ((double)cols.size() * nbe + slots) / slots * (bnd + warm + 2);
             if (best < 0 || c < best) { best = c; nb_best = nbe; }
         }
         if (f_nb > 0) nb_best = f_nb < maxnb ? f_nb : maxnb;
@@ -623,7 +642,20 @@ int tile_launch_impl(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom
         if (pairs[q]->L.pitch != a.pitchL || pairs[q]->R.pitch != a.pitchR || pairs[q]->npx_cap != pair->npx_cap) return 0;
     a.w1 = g.w1; a.h1 = g.h1; a.w2 = g.w2; a.h2 = g.h2; a.half = g.half;
     a.dlo = g.dlo; a.dhi = g.dhi; a.dbase = g.dlo & ~3;
-    a.npass = (g.dhi - a.dbase + 63) / 64;
+    // 8 warps per CTA, 32 candidates per pass and two CTAs per SM (possible where two rings + key buffers fit the SM's shared
+    // memory: windows up to 10 rows).  Measured 4-5 % SLOWER than 16 warps / one CTA per SM at equal work (4K / 512 SAD:
+    // kernel 1.776 vs 1.693 ms; the two unsynchronised CTAs do not make up for twice the passes), so it is taken only where
+    // the narrower pass saves a tenth of the candidates or more (145 candidates: 160 instead of 192 -- 0.182 -> 0.173 ms
+    // on 1436x992, block 11).  SR_TILE_NW=16 / 8 overrides (A/B measurements, tools/ab_tile.py).
+    static const char* nw_env = getenv("SR_TILE_NW");
+    const int span = g.dhi - a.dbase;
+    int nw = 16;
+    if (!lm && 2 * g.half <= 10 && span > 0) {
+        if (10 * ((span + 31) / 32 * 32) <= 9 * ((span + 63) / 64 * 64)) nw = 8;
+        if (nw_env) nw = atoi(nw_env) == 8 ? 8 : 16;
+    }
+    a.pw = 4 * nw;
+    a.npass = (g.dhi - a.dbase + a.pw - 1) / a.pw;
     a.row0 = g.row0; a.row1 = r1; a.k64 = 64u; a.nk64 = (uint32_t)-64; a.merged = 0; a.shift = 6; a.km1 = 0xFFFFFFFFu;
     a.lmode = 0; a.hwin = 2 * g.half; a.cmax = a.rmax = a.lim_a = a.lo_a = 0;
     if (lm) {
@@ -650,15 +682,15 @@ int tile_launch_impl(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom
     // kernel's DRAM writes drop from 209 to ~55 MB and the resolve pass reads 2 planes instead of 8).  The planes stay in
     // L2; a plane's candidate range is [dbase + (p << shift), +2^shift).  shift == 6: one plane per pass, plain stores.
     int full = 6;
-    while ((64 << (full - 6)) < a.npass * 64) full++;
+    while ((64 << (full - 6)) < a.npass * a.pw) full++;
     unsigned long long cmax = (unsigned long long)g.block * g.block * 3ull * (cost == SR_COST_SAD ? 255ull : 65025ull);
     static const char* mg_env = getenv("SR_TILE_MERGE");    // tuning / test override: 0 = never merge
     int shift = 6;
     if (!(mg_env && atoi(mg_env) == 0))
         while (shift < full && ((cmax + 1) << (shift + 1)) < 0xFFFFFFFFull) shift++;
-    a.merged = shift > 6;
+    a.merged = shift > 6 || a.pw < 64;                  // several passes per plane: RED.MIN into a preset plane
     a.shift = shift;
-    const int planes_per_pair = (a.npass + (1 << (shift - 6)) - 1) >> (shift - 6);
+    const int planes_per_pair = (a.npass * a.pw + (1 << shift) - 1) >> shift;
     uint32_t* base = (uint32_t*)sr_scratch(ctx, 0, (size_t)n * planes_per_pair * pair->npx_cap * sizeof(uint32_t));
     if (!base) return SR_E_CUDA;
     PairPtrs hp[MAXP];
