@@ -726,18 +726,20 @@ __global__ void __launch_bounds__(U8R_T) u8_rowsum_kernel(const double* __restri
     for (int x = t; x < w; x += U8R_T) o[x] = pi[x + k - 1] - (x > 0 ? pi[x - 1] : 0);
 }
 #define U8_NSEG 64
+// Latency-bound (each thread walks ~40 rows of one column): eight independent loads in flight per thread in the
+// segment sums (17.1 -> 13.6 us on the 4K map; the same in the prefix kernel below measured slower, 19.5 against 17.3 us).
 __global__ void u8_cols_seg_kernel(const int* __restrict__ rows, int w, int h, int k, int* __restrict__ seg) {
     int x = blockIdx.x * blockDim.x + threadIdx.x, sgi = blockIdx.y;
     if (x >= w) return;
     const int a = k / 2, he = h + k - 1, SL = (he + U8_NSEG - 1) / U8_NSEG;
     const int j0 = sgi * SL, j1 = min(j0 + SL, he);
-    int a0 = 0, a1 = 0, a2 = 0, a3 = 0, j = j0;
-    for (; j + 3 < j1; j += 4) {
-        a0 += rows[(size_t)reflect101(j - a, h) * w + x]; a1 += rows[(size_t)reflect101(j + 1 - a, h) * w + x];
-        a2 += rows[(size_t)reflect101(j + 2 - a, h) * w + x]; a3 += rows[(size_t)reflect101(j + 3 - a, h) * w + x];
+    int acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, j = j0;
+    for (; j + 7 < j1; j += 8) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) acc[u] += rows[(size_t)reflect101(j + u - a, h) * w + x];
     }
-    for (; j < j1; j++) a0 += rows[(size_t)reflect101(j - a, h) * w + x];
-    seg[(size_t)sgi * w + x] = (a0 + a1) + (a2 + a3);
+    for (; j < j1; j++) acc[0] += rows[(size_t)reflect101(j - a, h) * w + x];
+    seg[(size_t)sgi * w + x] = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
 }
 __global__ void u8_cols_prefix_kernel(const int* __restrict__ rows, int w, int h, int k, const int* __restrict__ seg, int* __restrict__ pe) {
     int x = blockIdx.x * blockDim.x + threadIdx.x, sgi = blockIdx.y;
