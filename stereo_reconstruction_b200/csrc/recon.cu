@@ -380,14 +380,31 @@ int recon_depth_backproject(sr_ctx* ctx, const float* d_disp, const float* d_dep
 // Grid cells in row-major order, per cell the upper-left triangle (a,b,c) then the lower-right
 // (b,d,c).  Validity is embarrassingly parallel; the reference's face ORDER is kept with an
 // ordered stream compaction: per-block counts -> exclusive scan of block totals -> scatter.
-__device__ __forceinline__ float edge_len(const float4& a, const float4& b) {
+// The reference compares sqrtf(s) > thr with s = dx^2 + dy^2 + dz^2 (:53-65).  sqrtf is correctly rounded and monotone,
+// so there is one float S(thr) = max{ s : sqrtf(s) <= thr } and the test is s > S(thr), exactly -- no square root per
+// edge (three per pixel in the fused kernel, which is issue-bound: 71 % issue-active at 43 % of the DRAM peak).  S(thr)
+// is found on the host (sqrt_threshold below) from thr * thr by stepping neighbouring floats.
+__device__ __forceinline__ float edge_sq(const float4& a, const float4& b) {
     float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z;
-    return sqrtf(dx * dx + dy * dy + dz * dz);  // powf(v,2) == v*v; sums left to right; no FMA
+    return dx * dx + dy * dy + dz * dz;  // powf(v,2) == v*v; sums left to right; no FMA
 }
-__device__ __forceinline__ bool tri_valid(const float4& a, const float4& b, const float4& c, float thr) {
+__device__ __forceinline__ bool tri_valid(const float4& a, const float4& b, const float4& c, float thr_sq) {
     if (a.x == -INFINITY || b.x == -INFINITY || c.x == -INFINITY) return false;
-    float l1 = edge_len(a, b), l2 = edge_len(a, c), l3 = edge_len(b, c);
-    return !(l1 > thr || l2 > thr || l3 > thr);
+    float l1 = edge_sq(a, b), l2 = edge_sq(a, c), l3 = edge_sq(b, c);
+    return !(l1 > thr_sq || l2 > thr_sq || l3 > thr_sq);
+}
+static float sqrt_threshold(float thr) {
+    if (thr != thr) return INFINITY;                   // l > NaN: never
+    if (thr < 0.0f) return -INFINITY;                  // l >= 0 > thr: always (s is NaN for no edge of an accepted triangle)
+    if (thr == INFINITY) return INFINITY;
+    float c = thr * thr;
+    while (sqrtf(c) > thr) c = nextafterf(c, -INFINITY);
+    for (;;) {
+        const float n = nextafterf(c, INFINITY);
+        if (n == c || !(sqrtf(n) <= thr)) break;
+        c = n;
+    }
+    return c;
 }
 
 #define FACE_THREADS 256
@@ -402,19 +419,19 @@ struct PosFromVertices {
 };
 // flags of cell `cell`: bit0 = upper-left triangle valid, bit1 = lower-right valid
 template <class Pos>
-__device__ __forceinline__ uint32_t cell_flags(const Pos& pos, int w, unsigned cell, float thr) {
+__device__ __forceinline__ uint32_t cell_flags(const Pos& pos, int w, unsigned cell, float thr_sq) {
     unsigned cw = (unsigned)(w - 1);
     unsigned y = cell / cw, x = cell - y * cw;
     const float4 pa = pos(x, y, w), pb = pos(x, y + 1, w), pc = pos(x + 1, y, w), pd = pos(x + 1, y + 1, w);
-    return (tri_valid(pa, pb, pc, thr) ? 1u : 0u) | (tri_valid(pb, pd, pc, thr) ? 2u : 0u);
+    return (tri_valid(pa, pb, pc, thr_sq) ? 1u : 0u) | (tri_valid(pb, pd, pc, thr_sq) ? 2u : 0u);
 }
 
 template <class Pos>
-__global__ void __launch_bounds__(FACE_THREADS) face_count_kernel(Pos pos, int w, float thr, unsigned ncells,
+__global__ void __launch_bounds__(FACE_THREADS) face_count_kernel(Pos pos, int w, float thr_sq, unsigned ncells,
                                                                   uint8_t* __restrict__ flags, uint32_t* __restrict__ block_total) {
     __shared__ uint32_t wsum[FACE_THREADS / 32];
     unsigned cell = blockIdx.x * FACE_THREADS + threadIdx.x;
-    uint32_t f = cell < ncells ? cell_flags(pos, w, cell, thr) : 0u;
+    uint32_t f = cell < ncells ? cell_flags(pos, w, cell, thr_sq) : 0u;
     if (cell < ncells) flags[cell] = (uint8_t)f;
     uint32_t n = __popc(f);
     for (int o = 16; o; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
@@ -459,7 +476,7 @@ struct DispFromU8Blur {
 template <class Disp>
 __global__ void __launch_bounds__(DBF_T) depth_backproject_faces_kernel(
     Disp disp, const uint8_t* __restrict__ bgr, size_t bgr_pitch, int w, int h, float focal,
-    float baseline, float fx, float fy, float cx, float cy, float thr, float* __restrict__ depth_out,
+    float baseline, float fx, float fy, float cx, float cy, float thr /* S(thrMesh): squared-length threshold */, float* __restrict__ depth_out,
     sr_vertex* __restrict__ vert, uint8_t* __restrict__ flags) {
     __shared__ float4 spos[2][DBF_T];
     __shared__ float svert[2][DBF_T];
@@ -476,7 +493,7 @@ __global__ void __launch_bounds__(DBF_T) depth_backproject_faces_kernel(
         cn = (uint32_t)p[2] | ((uint32_t)p[1] << 8) | ((uint32_t)p[0] << 16) | 0xFF000000u;
     }
     float4 prev = make_float4(0.f, 0.f, 0.f, 0.f), prev_right = prev;
-    float top = 0.f;                                         // |pos(x,y-1) - pos(x+1,y-1)|
+    float top = 0.f;                                         // |pos(x,y-1) - pos(x+1,y-1)|^2 (all edge values are squared lengths)
     for (int r = 0; r <= DBF_ROWS; r++) {
         const int y = y0 + r;
         if (y >= h) break;                                   // uniform over the CTA
@@ -508,17 +525,17 @@ __global__ void __launch_bounds__(DBF_T) depth_backproject_faces_kernel(
         // Edge lengths are symmetric bit for bit ((a-b)^2 == (b-a)^2), so each is computed once: the vertical edge
         // of this column here (the left-hand neighbour reads it as its cell's right side), the horizontal edge of
         // this row (top side of the cell below, bottom side of the cell above) and the diagonal.
-        const float vert_edge = edge_len(prev, cur);
+        const float vert_edge = edge_sq(prev, cur);
         spos[r & 1][t] = cur;
         svert[r & 1][t] = vert_edge;
         __syncthreads();
         const float4 cur_right = t < DBF_T - 1 ? spos[r & 1][t + 1] : cur;
         const float vert_right = t < DBF_T - 1 ? svert[r & 1][t + 1] : 0.f;
-        const float bottom = edge_len(cur, cur_right);
+        const float bottom = edge_sq(cur, cur_right);
         if (r > 0 && own && x < w - 1) {
             // cell (x, y - 1): a = prev, b = cur, c = prev_right, d = cur_right (reconstruction.cpp:92-113);
             // triangle (a,b,c): edges ab, ac, bc; triangle (b,d,c): edges bd, bc, dc (:46-69)
-            const float diag = edge_len(cur, prev_right);
+            const float diag = edge_sq(cur, prev_right);
             const bool t1 = !(prev.x == -INFINITY || cur.x == -INFINITY || prev_right.x == -INFINITY) &&
                             !(vert_edge > thr || top > thr || diag > thr);
             const bool t2 = !(cur.x == -INFINITY || cur_right.x == -INFINITY || prev_right.x == -INFINITY) &&
@@ -651,7 +668,7 @@ int recon_mesh_faces(sr_ctx* ctx, const sr_vertex* d_vert, int w, int h, float t
     uint32_t* block_total = nullptr;
     uint8_t* flags = face_buffers(ctx, ncells, nblocks, &block_total);
     if (!flags) return SR_E_CUDA;
-    if (d_vert) face_count_kernel<PosFromVertices><<<nblocks, FACE_THREADS, 0, ctx->stream>>>(PosFromVertices{d_vert}, w, thr, ncells, flags, block_total);
+    if (d_vert) face_count_kernel<PosFromVertices><<<nblocks, FACE_THREADS, 0, ctx->stream>>>(PosFromVertices{d_vert}, w, sqrt_threshold(thr), ncells, flags, block_total);
     else face_blocktotal_kernel<<<cdiv((int)nblocks, 16), 256, 0, ctx->stream>>>(flags, ncells, nblocks, block_total);
     SR_LAUNCHED(ctx);
     face_scan_kernel<<<1, 1024, 0, ctx->stream>>>(block_total, nblocks);
@@ -676,7 +693,7 @@ int recon_depth_backproject_faces(sr_ctx* ctx, const float* d_disp, const uint8_
     if (!flags) return SR_E_CUDA;
     dim3 grid(cdiv(w, DBF_T - 1), cdiv(h, DBF_ROWS));
     depth_backproject_faces_kernel<DispFromMap><<<grid, DBF_T, 0, ctx->stream>>>(DispFromMap{d_disp}, d_bgr, bgr_pitch, w, h, focal, baseline,
-                                                                                 fx, fy, cx, cy, thr, d_depth_out, d_vert, flags);
+                                                                                 fx, fy, cx, cy, sqrt_threshold(thr), d_depth_out, d_vert, flags);
     SR_LAUNCHED(ctx);
     return SR_OK;
 }
@@ -797,7 +814,7 @@ int recon_u8_pipeline(sr_ctx* ctx, const double* d_disp64, const uint8_t* d_bgr,
     DispFromU8Blur src{q8, pe, k, 1.0 / ((double)k * (double)k), thr_front, thr_back, d_disp_out};
     dim3 grid(cdiv(w, DBF_T - 1), cdiv(h, DBF_ROWS));
     depth_backproject_faces_kernel<DispFromU8Blur><<<grid, DBF_T, 0, ctx->stream>>>(src, d_bgr, bgr_pitch, w, h, focal, baseline, fx, fy, cx,
-                                                                                    cy, thr, d_depth_out, d_vert, flags);
+                                                                                    cy, sqrt_threshold(thr), d_depth_out, d_vert, flags);
     SR_LAUNCHED(ctx);
     return SR_OK;
 }

@@ -516,6 +516,34 @@ def test_box_blur_order_free_and_sequential_paths(sr, ctx, orc, case):
 
 
 
+@pytest.mark.parametrize("thr", [0.37, 1.0, 2.0, 3.0000002, 1e-3, 7.5e5, 0.0, -1.0, float("inf"), float("nan"), 1e-30, 3e19])
+def test_mesh_validity_threshold_is_exact_without_square_roots(sr, ctx, orc, thr):
+    """CheckTriangularValidity (reconstruction.cpp:46-69) compares sqrtf(dx^2 + dy^2 + dz^2) > thr; the kernels compare the
+    squared length with S(thr) = max{s : sqrtf(s) <= thr}.  Vertices whose edge lengths crowd around thr within a few
+    ulps (both sides), plus exact hits, must give the oracle's face list for ordinary, tiny, huge, zero, negative,
+    infinite and NaN thresholds."""
+    R = sr.reconstruction
+    rng = np.random.default_rng(99)
+    w, h = 257, 129
+    v = np.zeros(w * h, sr.capi.VERTEX_DTYPE)
+    t = np.float32(thr) if np.isfinite(thr) and 0 < thr < 1e18 else np.float32(1.0)
+    # a 0.8 thr x 0.6 thr grid: the diagonal of every cell is thr up to rounding (3-4-5), the sides are shorter -- so
+    # validity hangs on sqrtf(s) > thr with s within a few ulps of thr^2, on both sides
+    gx, gy = np.meshgrid(np.arange(w, dtype=np.float64), np.arange(h, dtype=np.float64))
+    pos = np.stack([gx * 0.8 * float(t), gy * 0.6 * float(t), np.zeros_like(gx), np.ones_like(gx)], -1)
+    p32 = pos.astype(np.float32)
+    # nudge a third of the x coordinates by +-1..3 ulps
+    nud = rng.integers(-3, 4, (h, w)).astype(np.int32) * (rng.random((h, w)) < 0.33)
+    p32[..., 0] = (p32[..., 0].view(np.int32) + nud).view(np.float32)
+    p32[rng.random((h, w)) < 0.02] = -np.inf             # a few invalid vertices
+    v["pos"] = p32.reshape(-1, 4)
+    got = R.meshFaces(v, w, h, thr, ctx=ctx)
+    want = orc.mesh_faces(v, w, h, thr)
+    np.testing.assert_array_equal(got, want)
+    if np.isfinite(thr) and 1e-3 <= thr <= 1e6:
+        assert 0.1 < len(want) / (2.0 * (w - 1) * (h - 1)) < 0.9      # the threshold really cuts through this set
+
+
 def test_mesh_faces_large_map(sr, ctx, orc):
     """Face list of a map with more than 4096 scan blocks (several sweeps of the block-total scan, ragged tail)."""
     R = sr.reconstruction
