@@ -398,11 +398,13 @@ int sr_search_run(sr_ctx* ctx, sr_pair* pair, const sr_search_params* p, int row
         SearchGeom gt = g;
         if (smoothing) gt.dlo = 1 > g.dlo ? 1 : g.dlo;
         if (gt.dhi < gt.dlo) gt.dhi = gt.dlo;
-        handled = sr_launch_search_tile(ctx, pair, gt, p->cost, 0);
+        handled = sr_launch_search_tile(ctx, pair, gt, p->cost, 0, smoothing);
         if (handled < 0) return handled;
         if (handled) {
             ctx->last_kernel = "tile";
-            if (smoothing && (rc = sr_launch_cost0(ctx, pair, g, p->cost)) != SR_OK) return rc;
+            // the d == 0 costs come out of the tile kernel (warp 0 of pass 0 holds those sums); the separable box-sum
+            // kernels only where it could not (range not starting in the first pass, nothing searched)
+            if (smoothing && !(pair->c0_from_tile && pair->npass > 0) && (rc = sr_launch_cost0(ctx, pair, g, p->cost)) != SR_OK) return rc;
             rc = sr_launch_resolve_right(ctx, pair, g, p->smooth, 0, smoothing ? 2 : 0);   // 2: c0 is the u32 plane of sr_launch_cost0
         }
     }

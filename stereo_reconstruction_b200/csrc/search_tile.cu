@@ -155,6 +155,8 @@ struct TileArgs {
     // bounds max(dlo, lo_a - x) <= i < min(dhi, lim_a - x).  w2 = width of the reference (output) image.
     int lmode, hwin;     // hwin: window size H2 (2*half, or 2*half + 1 in lmode)
     int pw;              // candidates per pass: 64 (16 warps, one CTA per SM) or 32 (8 warps, two CTAs per SM)
+    uint32_t* c0;        // != NULL (needs dbase == 0): the raw window cost at d == 0 of every pixel goes to this u32 plane -- the
+                         // smoothing rule treats d == 0 apart (BlockSearch.cpp:160-165) and the sums are warp 0's anyway
     int cmax, rmax, lim_a, lo_a;
 };
 
@@ -212,6 +214,25 @@ __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32
     }
 }
 
+// Window sums of this warp's first disparity for the thread's 16 output columns -> one row of the d == 0 cost plane
+// (warp 0 of pass 0 only: ~50 instructions per row for one warp in sixteen of one pass; replaces the separable box-sum
+// kernels cost0_vertical / cost0_horizontal, 40 us on a 1436x992 pair).
+template <int H2>
+__device__ __forceinline__ void emit_c0(const uint32_t (&col)[XT][DT], uint32_t* __restrict__ c0row, int x0, int w2, int lane) {
+    // no halo array: the neighbour lane's columns are fetched where the window reaches them (the kernel sits at its
+    // register limit)
+    auto colv = [&](int i) { return i < XT ? col[i < XT ? i : 0][0] : __shfl_down_sync(0xffffffffu, col[i >= XT ? i - XT : 0][0], 1); };
+    uint32_t S = 0;
+#pragma unroll
+    for (int i = 0; i < H2; i++) S += colv(i);
+#pragma unroll
+    for (int j = 0; j < XT; j++) {
+        const int x = x0 + j;
+        if (lane < 31 && x >= 0 && x < w2) c0row[x] = S;
+        if (j + 1 < XT) S += colv(j + H2) - col[j][0];
+    }
+}
+
 __device__ __forceinline__ void sts128(uint32_t saddr, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
     asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(saddr), "r"(x), "r"(y), "r"(z), "r"(w));
 }
@@ -221,7 +242,7 @@ __device__ __forceinline__ uint32_t lds32(uint32_t saddr) {
     return v;
 }
 
-template <int H2, int COST, int NW, bool LM = false>
+template <int H2, int COST, int NW, bool LM = false, bool C0 = false>
 __global__ void __launch_bounds__(NW * 32, NW <= 8 ? 2 : 1) search_tile_kernel(TileArgs a) {
     constexpr int NSLOT = H2 + PF + 1;   // +1: half of the warps subtract the leaving row one iteration late
     constexpr uint32_t SLOT_B = SLOT_U4 * 16, RING_B = NSLOT * SLOT_B, KEYROW_B = KEY_U4 * 16, KEYBUF_B = NW * KEYROW_B;
@@ -392,6 +413,8 @@ __global__ void __launch_bounds__(NW * 32, NW <= 8 ? 2 : 1) search_tile_kernel(T
 #pragma unroll
                 for (int k = 0; k < 4; k++)
                     sts128(key_st + buf + 16 * k, keys[4 * k], keys[4 * k + 1], keys[4 * k + 2], keys[4 * k + 3]);
+                // (a template flag and kernels of its own: with this line in the common kernel every shape ran 0.5 - 3 % slower)
+                if (C0 && d0 == 0) emit_c0<H2>(col, a.c0 + (size_t)y * a.w2, cb + h, a.w2, lane);
                 if (!late_sub && y + 1 < yb1 && row_ok(y - h) && colmask != 0)
                     vertical_update<COST, false, false>(col, smem_base + s_out, lane_b, uo, colmask, km1);
             }
@@ -407,16 +430,16 @@ __global__ void __launch_bounds__(NW * 32, NW <= 8 ? 2 : 1) search_tile_kernel(T
     reduce_row(((yb1 - 1) & 1) ? KEYBUF_B : 0u);
 }
 
-template <int H2, int COST, bool LM = false, int NW = 16>
+template <int H2, int COST, bool LM = false, int NW = 16, bool C0 = false>
 int launch(sr_ctx* ctx, const TileArgs& a, int nwork) {
     size_t smem = ((size_t)(H2 + PF + 1) * SLOT_U4 + 2 * NW * KEY_U4) * sizeof(uint4);
     static DeviceOnce configured;
     if (configured.need(ctx->device)) {
-        SR_CUDA(ctx, cudaFuncSetAttribute(search_tile_kernel<H2, COST, NW, LM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(ctx, cudaFuncSetAttribute(search_tile_kernel<H2, COST, NW, LM, C0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured.done(ctx->device);
     }
     SR_CUDA(ctx, cudaEventRecord(ctx->kev0, ctx->stream));
-    search_tile_kernel<H2, COST, NW, LM><<<nwork, NW * 32, smem, ctx->stream>>>(a);
+    search_tile_kernel<H2, COST, NW, LM, C0><<<nwork, NW * 32, smem, ctx->stream>>>(a);
     SR_LAUNCHED(ctx);
     SR_CUDA(ctx, cudaEventRecord(ctx->kev1, ctx->stream));
     ctx->kev_valid = true;
@@ -425,6 +448,19 @@ int launch(sr_ctx* ctx, const TileArgs& a, int nwork) {
 
 template <int COST>
 int dispatch_h2(sr_ctx* ctx, const TileArgs& a, int nwork) {
+    if (a.c0 != nullptr) {                                // d == 0 cost plane wanted (smoothing rule): kernels of their own
+        switch (2 * a.half) {
+            case 2: return launch<2, COST, false, 16, true>(ctx, a, nwork);
+            case 4: return launch<4, COST, false, 16, true>(ctx, a, nwork);
+            case 6: return launch<6, COST, false, 16, true>(ctx, a, nwork);
+            case 8: return launch<8, COST, false, 16, true>(ctx, a, nwork);
+            case 10: return launch<10, COST, false, 16, true>(ctx, a, nwork);
+            case 12: return launch<12, COST, false, 16, true>(ctx, a, nwork);
+            case 14: return launch<14, COST, false, 16, true>(ctx, a, nwork);
+            case 16: return launch<16, COST, false, 16, true>(ctx, a, nwork);
+            default: return 0;
+        }
+    }
     switch (2 * a.half) {
         case 2: return a.pw == 32 ? launch<2, COST, false, 8>(ctx, a, nwork) : launch<2, COST>(ctx, a, nwork);
         case 4: return a.pw == 32 ? launch<4, COST, false, 8>(ctx, a, nwork) : launch<4, COST>(ctx, a, nwork);
@@ -628,7 +664,7 @@ int tile_work_list(sr_ctx* ctx, const SearchGeom& g, const TileArgs& a, int ntx,
 namespace {
 // Left variant (lmode): images and bounds of the launch (see TileArgs)
 struct LeftMode { const uint32_t* searched; int pitch; int cmax, rmax, lim_a, lo_a; };
-int tile_launch_impl(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom& g, int cost, const LeftMode* lm) {
+int tile_launch_impl(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom& g, int cost, const LeftMode* lm, bool want_c0 = false) {
     if (n < 1 || n > MAXP) return 0;
     sr_pair* pair = pairs[0];
     if (g.half < 1 || g.half > 8) return 0;
@@ -650,7 +686,7 @@ int tile_launch_impl(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom
     static const char* nw_env = getenv("SR_TILE_NW");
     const int span = g.dhi - a.dbase;
     int nw = 16;
-    if (!lm && 2 * g.half <= 10 && span > 0) {
+    if (!lm && !want_c0 && 2 * g.half <= 10 && span > 0) {
         if (10 * ((span + 31) / 32 * 32) <= 9 * ((span + 63) / 64 * 64)) nw = 8;
         if (nw_env) nw = atoi(nw_env) == 8 ? 8 : 16;
     }
@@ -658,6 +694,8 @@ int tile_launch_impl(sr_ctx* ctx, sr_pair* const* pairs, int n, const SearchGeom
     a.npass = (g.dhi - a.dbase + a.pw - 1) / a.pw;
     a.row0 = g.row0; a.row1 = r1; a.k64 = 64u; a.nk64 = (uint32_t)-64; a.merged = 0; a.shift = 6; a.km1 = 0xFFFFFFFFu;
     a.lmode = 0; a.hwin = 2 * g.half; a.cmax = a.rmax = a.lim_a = a.lo_a = 0;
+    a.c0 = (want_c0 && !lm && n == 1 && a.dbase == 0) ? (uint32_t*)pair->c0 : nullptr;
+    pair->c0_from_tile = a.c0 != nullptr;
     if (lm) {
         // reference image (window centre, output) = the LEFT image, searched image = the shifted copy of the right one
         a.lmode = 1; a.hwin = 2 * g.half + 1;
@@ -760,7 +798,8 @@ int sr_launch_search_tile_leftvariant(sr_ctx* ctx, sr_pair* pair, int block, int
     return tile_launch_impl(ctx, &pair, 1, g, SR_COST_SSD_L2, &lm);
 }
 
-int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref) {
+// want_c0: also leave the raw d == 0 window costs in pair->c0 as a u32 plane (pair->c0_from_tile says whether it did)
+int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref, int want_c0) {
     if (left_ref) return 0;
-    return sr_launch_search_tile_multi(ctx, &pair, 1, g, cost);
+    return tile_launch_impl(ctx, &pair, 1, g, cost, nullptr, want_c0 != 0);
 }

@@ -91,6 +91,7 @@ struct sr_pair {
     int key_shift = 6;                    // key = cost << key_shift | candidate index within the plane's range
     unsigned long long* best = nullptr;   // (cost << 32 | d) first minimum over the searched range
     unsigned long long* c0 = nullptr;     // cost at d == 0 (SR_NONE64 when not a candidate)
+    bool c0_from_tile = false;            // the last tile search left the raw d == 0 costs in c0 as a u32 plane
     unsigned long long* cr = nullptr;     // wide-cost first minimum (direct kernels)
     int* dr = nullptr;
     int* nwin = nullptr;                  // window pixel count; -1 = skipped (black) pixel
@@ -163,7 +164,7 @@ int sr_launch_pack_rows2(sr_ctx* ctx, const uint8_t* rawa, size_t pitcha, int wa
 
 // Fast path: fixed window, SSD/SAD, first minimum over [dlo,dhi) -> pair->best.
 // Returns 1 when it handled the request, 0 when the shape is not supported (caller falls back).
-int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref);
+int sr_launch_search_tile(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, int cost, int left_ref, int want_c0 = 0);
 // Left variant's unbiased winners through the tile kernel (odd blocks 3..17): key planes over the index i = *off - d
 int sr_launch_search_tile_leftvariant(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, int* off);
 // The same in ONE launch over n <= 16 pairs of one shape (batches of small pairs: more work items per band).
