@@ -355,85 +355,70 @@ __global__ void __launch_bounds__(32) smooth_raster_warp_kernel(int rows, int wo
 // the one thing that bounds it -- the dependent chain from one row's result to the next (300 -> ~150 cycles per row):
 //  * the lane's KW words are ONE multi-word addition per possible carry-in (add-with-carry from word to word instead of
 //    extracting bit 31 and starting a new 64-bit addition per word): z = carry-out of every bit of F0 + F1 + cin;
-//  * F0 = a0 ^ (up & (a0 ^ a1)), F1 = a1 ^ (up & (a1 ^ a2)): the XORs are formed when the row's planes arrive, one LOP3
-//    per word is left on the chain;
-//  * planes and results move through running pointers (no 64-bit index arithmetic in the loop); words beyond the row
-//    are zero in the ring (all-kill: they neither generate nor propagate), so the loop has no bounds tests.
+//  * F0 = a0 ^ (up & (a0 ^ a1)), F1 = a1 ^ (up & (a1 ^ a2)): one LOP3 per word on the chain;
+//  * no shared-memory ring: the planes of the next 16 / KW rows are ordinary loads into registers, issued while the
+//    current rows are resolved; results through a running pointer; words beyond the row are zero (all-kill: they
+//    neither generate nor propagate).
 template <int KW>
 __global__ void __launch_bounds__(32) smooth_raster_mono_kernel(int rows, int words, const uint32_t* __restrict__ bits,
                                                                 uint32_t* __restrict__ zbits) {
-    extern __shared__ uint32_t ring[];   // RASTER_PF x (32*KW*3) words
+    // The planes of the next U rows are loaded into registers (plain loads, nothing volatile: the compiler is free to
+    // spread them over the stalls of the chain) while the current U rows are resolved.
+    constexpr int U = 16 / KW;
     const int lane = threadIdx.x;
     const int w0 = lane * KW;
-    constexpr int ROWW = 32 * KW * 3;
-    for (int i = lane; i < RASTER_PF * ROWW; i += 32) ring[i] = 0u;   // slots of words past the row stay zero for good
-    __syncwarp();
-    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(ring);
-    int nvalid = words - w0;                          // words of this lane inside the row
+    int nvalid = words - w0;                          // words of this lane inside the row; the others are all-kill (zero)
     nvalid = nvalid < 0 ? 0 : (nvalid > KW ? KW : nvalid);
-    const uint32_t* src = bits + (size_t)w0 * 3;      // this lane's planes of the next row to prefetch
-    int pf_y = 0;
-    uint32_t pf_slot = sbase + 4u * (w0 * 3);
-    auto prefetch = [&]() {
-        if (pf_y < rows) {
+    const size_t rowstride = (size_t)words * 3;
+    const uint32_t* src = bits + (size_t)w0 * 3;
+    uint32_t cur[U][KW * 3], nxt[U][KW * 3];
+    auto load_block = [&](uint32_t (&dst)[U][KW * 3], int y0) {
 #pragma unroll
-            for (int i = 0; i < 3 * KW; i++)
-                if (i < 3 * nvalid) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(pf_slot + 4u * i), "l"(src + i) : "memory");
-        }
-        asm volatile("cp.async.commit_group;\n" ::: "memory");
-        pf_y++; src += (size_t)words * 3;
-        pf_slot += 4u * ROWW;
-        if (pf_slot >= sbase + 4u * (RASTER_PF * ROWW)) pf_slot -= 4u * (RASTER_PF * ROWW);
+        for (int u = 0; u < U; u++)
+#pragma unroll
+            for (int i = 0; i < KW * 3; i++) dst[u][i] = (y0 + u < rows && i < 3 * nvalid) ? __ldg(src + (size_t)u * rowstride + i) : 0u;
+        src += (size_t)U * rowstride;
     };
-#pragma unroll 1
-    for (int y = 0; y < RASTER_PF - 1; y++) prefetch();
+    load_block(cur, 0);
     uint32_t up[KW];
 #pragma unroll
     for (int k = 0; k < KW; k++) up[k] = 0;           // y == 0 has no row above: the rule needs y >= 1
-    const uint32_t* r = ring + w0 * 3;
-    const uint32_t* rend = ring + RASTER_PF * ROWW;
     uint32_t* zo = zbits + w0;
-    // the planes of row y sit in registers before its chain starts: they are read from the ring during row y - 1
-    uint32_t a0[KW], a1[KW], x01[KW], x12[KW];
-    auto fetch = [&]() {                              // next ring row -> registers (waits for its cp.async group)
-        prefetch();
-        asm volatile("cp.async.wait_group %0;\n" ::"n"(RASTER_PF - 1) : "memory");
-#pragma unroll
-        for (int k = 0; k < KW; k++) {
-            a0[k] = r[3 * k]; a1[k] = r[3 * k + 1];
-            const uint32_t a2 = r[3 * k + 2];
-            x01[k] = a0[k] ^ a1[k]; x12[k] = a1[k] ^ a2;
-        }
-        r += ROWW;
-        if (r >= rend) r -= RASTER_PF * ROWW;
-    };
-    fetch();
 #pragma unroll 1
-    for (int y = 0; y < rows; y++) {
-        // --- the chain from the previous row ---
-        uint32_t F0[KW], F1[KW], s0[KW], s1[KW];
-        uint32_t c0 = 0, c1 = 1;
+    for (int yb = 0; yb < rows; yb += U) {
+        load_block(nxt, yb + U);
 #pragma unroll
-        for (int k = 0; k < KW; k++) {
-            F0[k] = a0[k] ^ (up[k] & x01[k]);
-            F1[k] = a1[k] ^ (up[k] & x12[k]);
-            const unsigned long long t0 = (unsigned long long)F0[k] + F1[k] + c0, t1 = (unsigned long long)F0[k] + F1[k] + c1;
-            s0[k] = (uint32_t)t0; c0 = (uint32_t)(t0 >> 32);
-            s1[k] = (uint32_t)t1; c1 = (uint32_t)(t1 >> 32);
-        }
-        const uint32_t G = __ballot_sync(0xffffffffu, c0), P = __ballot_sync(0xffffffffu, c1);
-        if (y + 1 < rows) fetch();                    // off the chain: overlaps the ballots' latency
-        const unsigned long long sum = (unsigned long long)G + (unsigned long long)P;      // lane x == 0 has carry-in 0
-        const uint32_t zz = (G & P) | ((G ^ P) & ((uint32_t)sum ^ G ^ P));                // carry out of every lane
-        const bool cin = ((zz << 1) >> lane) & 1u;                                         // carry into this lane
+        for (int u = 0; u < U; u++) {
+            if (yb + u < rows) {                      // (uniform)
+                uint32_t F0[KW], F1[KW], s0[KW], s1[KW];
+                uint32_t c0 = 0, c1 = 1;
 #pragma unroll
-        for (int k = 0; k < KW; k++) {
-            const uint32_t sm = cin ? s1[k] : s0[k];
-            const uint32_t z = (F0[k] & F1[k]) | ((F0[k] ^ F1[k]) & (sm ^ F0[k] ^ F1[k]));   // carry out of every bit
-            up[k] = z;
-            if (k < nvalid) zo[k] = z;
+                for (int k = 0; k < KW; k++) {
+                    const uint32_t a0 = cur[u][3 * k], a1 = cur[u][3 * k + 1], a2 = cur[u][3 * k + 2];
+                    F0[k] = a0 ^ (up[k] & (a0 ^ a1));
+                    F1[k] = a1 ^ (up[k] & (a1 ^ a2));
+                    const unsigned long long t0 = (unsigned long long)F0[k] + F1[k] + c0, t1 = (unsigned long long)F0[k] + F1[k] + c1;
+                    s0[k] = (uint32_t)t0; c0 = (uint32_t)(t0 >> 32);
+                    s1[k] = (uint32_t)t1; c1 = (uint32_t)(t1 >> 32);
+                }
+                const uint32_t G = __ballot_sync(0xffffffffu, c0), P = __ballot_sync(0xffffffffu, c1);
+                const unsigned long long sum = (unsigned long long)G + (unsigned long long)P;      // lane x == 0 has carry-in 0
+                const uint32_t zz = (G & P) | ((G ^ P) & ((uint32_t)sum ^ G ^ P));                // carry out of every lane
+                const bool cin = ((zz << 1) >> lane) & 1u;                                         // carry into this lane
+#pragma unroll
+                for (int k = 0; k < KW; k++) {
+                    const uint32_t sm = cin ? s1[k] : s0[k];
+                    const uint32_t z = (F0[k] & F1[k]) | ((F0[k] ^ F1[k]) & (sm ^ F0[k] ^ F1[k]));   // carry out of every bit
+                    up[k] = z;
+                    if (k < nvalid) zo[k] = z;
+                }
+                zo += words;
+            }
         }
-        zo += words;
+#pragma unroll
+        for (int u = 0; u < U; u++)
+#pragma unroll
+            for (int i = 0; i < KW * 3; i++) cur[u][i] = nxt[u][i];
     }
 }
 
@@ -441,7 +426,7 @@ template <int KW>
 static void launch_raster_warp(cudaStream_t st, int rows, int words, const uint32_t* bits, uint32_t* zb, int monotone) {
     const size_t smem = RASTER_PF * 32 * KW * 3 * sizeof(uint32_t);
     static const char* old_env = getenv("SR_RASTER_GENERIC");   // test hook: 1 = the generic kernel for monotone factors too
-    if (monotone && !(old_env && atoi(old_env) != 0)) smooth_raster_mono_kernel<KW><<<1, 32, smem, st>>>(rows, words, bits, zb);
+    if (monotone && !(old_env && atoi(old_env) != 0)) smooth_raster_mono_kernel<KW><<<1, 32, 0, st>>>(rows, words, bits, zb);
     else smooth_raster_warp_kernel<KW><<<1, 32, smem, st>>>(rows, words, bits, zb, monotone);
 }
 
