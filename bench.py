@@ -276,9 +276,9 @@ def recon_roofline(ctx, pair, w, h, iters=5):
     alg = w * h * 99
     return {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
             "frac": alg / (ms * 1e-3) / 1e9 / peak, "ms": ms, "algorithmic_bytes": alg, "algorithmic_bytes_per_pixel": 99,
-            "implementation_bytes_per_pixel": 125, "faces": int(nf.value), "peak_source": src,
+            "implementation_bytes_per_pixel": 75, "faces": int(nf.value), "peak_source": src,
             "what": "sr_pair_reconstruct on the resident search result: u8 hand-off, outliers k=500, depth, vertices, "
-                    "face count (main.cpp:41-65); per-kernel figures in DESIGN.md 4.2c / profiles/r01_recon_4k_hbm.jsonl"}
+                    "face count (main.cpp:41-65); per-kernel figures in DESIGN.md 4.2c / profiles/r02_recon_4k_hbm.jsonl"}
 
 
 def cpu_baseline(args, L, R, w, h, D, block, cost):
