@@ -245,13 +245,15 @@ __global__ void __launch_bounds__(LEFT_WARPS * 32, 1) left_raster_kernel(const u
         // entries of a chunk are fetched one chunk ahead (they do not depend on the raster)
         int nd3[3] = {-2, -1, -1};
         double nq3[3] = {0.0, 0.0, 0.0};
+        const int* td_row = td + (size_t)y * w1;                  // row bases: no 64-bit index arithmetic per chunk
+        const double* tq_row = tq + (size_t)y * w1;
+        double* out_row = out + (size_t)y * w1;
         auto fetch = [&](int xf) {
             nd3[0] = -2; nd3[1] = -1; nd3[2] = -1;
             if (xf < xend) {
-                const size_t of = (size_t)y * w1 + xf;
 #pragma unroll
                 for (int i = 0; i < 3; i++)
-                    if (i < ntop) { nd3[i] = __ldg(td + i * npx + of); nq3[i] = __ldg(tq + i * npx + of); }
+                    if (i < ntop) { nd3[i] = __ldg(td_row + i * npx + xf); nq3[i] = __ldg(tq_row + i * npx + xf); }
             }
         };
         fetch(h + pi);
@@ -259,23 +261,21 @@ __global__ void __launch_bounds__(LEFT_WARPS * 32, 1) left_raster_kernel(const u
             const int n = min(K, xend - x0);
             const int x = x0 + pi;
             const bool on = pi < n;
-            const size_t o = (size_t)y * w1 + x;
             int d3[3]; double q3[3];
 #pragma unroll
             for (int i = 0; i < 3; i++) { d3[i] = nd3[i]; q3[i] = nq3[i]; }
             fetch(x + K);
             int dup = 0;
             if (y - 1 >= h) {                                     // rows above h are border rows: always 0
+                // every lane polls the same word (one broadcast access, no divergent branch to reconverge)
                 if (smem_leader) {
-                    if (lane == 0) while (vprog[warp - 1] < (round << 20) + x0 + n) { }
-                    __syncwarp();
+                    while (vprog[warp - 1] < (round << 20) + x0 + n) { }
                     __threadfence_block();
                     if (on) dup = s_ring[warp - 1][x & (LEFT_RING - 1)];
                 } else {
-                    if (lane == 0) while (done[y - 1] < x0 + n) { }
-                    __syncwarp();
+                    while (done[y - 1] < x0 + n) { }
                     __threadfence();                              // acquire side of the writer's store -> fence -> flag
-                    if (on) dup = (int)__ldcg(out + o - w1);
+                    if (on) dup = (int)__ldcg(out_row - w1 + x);
                 }
             }
             // window cost of the upper neighbour's disparity, where it is a valid candidate the entries do not hold
@@ -334,14 +334,13 @@ __global__ void __launch_bounds__(LEFT_WARPS * 32, 1) left_raster_kernel(const u
                 if (pi == i) mine = result;
                 dleft = result;
             }
-            if (on && q == 0) out[o] = (double)mine;
+            if (on && q == 0) out_row[x] = (double)mine;
             if (smem_follower) {
                 // the follower must have consumed what this chunk overwrites: the same row RING pixels back, or (start
                 // of a row) its whole previous row
                 const int back = x0 + n - LEFT_RING;
                 const int need = has_follower && back > h ? (round << 20) + back : (round - 1) * (1 << 20) + xend;
-                if (lane == 0) while (vprog[warp + 1] < need) { }
-                __syncwarp();
+                while (vprog[warp + 1] < need) { }
                 if (on && q == 0) s_ring[warp][x & (LEFT_RING - 1)] = mine;
             } else {
                 // the follower is in another CTA: store -> fence -> flag through L2.  (Publishing once per 32 pixels
