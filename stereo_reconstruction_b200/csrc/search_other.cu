@@ -121,7 +121,8 @@ __global__ void __launch_bounds__(128) left_top3_kernel(const uint32_t* __restri
 __global__ void __launch_bounds__(128) left_top1_from_planes_kernel(const uint32_t* __restrict__ Lp, int pitchL, int w1, int height, int h,
                                                                     const uint32_t* __restrict__ planes, size_t stride, int npass,
                                                                     int dbase, int shift, int off,
-                                                                    double* __restrict__ tq, int* __restrict__ td) {
+                                                                    double* __restrict__ tq, int* __restrict__ td,
+                                                                    double* __restrict__ out_direct) {
     int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
     if (x >= w1) return;
     size_t o = (size_t)y * w1 + x;
@@ -137,6 +138,12 @@ __global__ void __launch_bounds__(128) left_top1_from_planes_kernel(const uint32
                 bd = off - (dbase + (p << shift) + (int)(k & ((1u << shift) - 1u)));
             }
         }
+    }
+    if (out_direct) {
+        // smoothFactor == 1: the two multiplications (:68-73) change nothing, the unbiased winner IS the result
+        // (x - 0 where no candidate was valid, :50,:82); no raster pass
+        out_direct[o] = skip ? 0.0 : (bd > 0 ? (double)bd : (double)x);
+        return;
     }
     tq[o] = sqrt((double)bc);                                     // the raster pass compares distances (:65)
     td[o] = skip ? -2 : bd;
@@ -378,8 +385,10 @@ int sr_launch_search_left(sr_ctx* ctx, sr_pair* pair, int block, int max_disp, d
     const int h = (block - 1) / 2;
     if (handled) {
         left_top1_from_planes_kernel<<<dim3(cdiv(w1, 128), h1), 128, 0, ctx->stream>>>(
-            pair->L.px, pair->L.pitch, w1, height, h, pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase, pair->key_shift, off, tc, td);
+            pair->L.px, pair->L.pitch, w1, height, h, pair->planes, pair->npx_cap, pair->npass, pair->plane_dbase, pair->key_shift, off, tc, td,
+            smooth == 1.0 ? pair->out : nullptr);
         SR_LAUNCHED(ctx);
+        if (smooth == 1.0) return SR_OK;
     } else {
         left_top3_kernel<<<dim3(cdiv(w1, 128), h1), 128, 0, ctx->stream>>>(pair->L.px, pair->L.pitch, pair->R.px, pair->R.pitch, w1, w2,
                                                                             height, block, max_disp, tc, td, npx);
