@@ -60,10 +60,14 @@ static int pipeline_chunks(const sr_pair* pair, const sr_search_params* p, int r
     const char* env = getenv("SR_PIPE_CHUNKS");   // tuning / test override
     int c = env ? atoi(env) : 0;
     if (c <= 0) {
-        // small pairs: one chunk (launch overheads dominate); large pairs: ~0.8 M right pixels per chunk
-        // (4K pair, three compute streams: 6 chunks 2.46 ms, 8 -> 2.36, 10 -> 2.32, 12 -> 2.31)
+        // large pairs: ~0.8 M right pixels per chunk (4K pair, three compute streams: 6 chunks 2.46 ms, 8 -> 2.36,
+        // 10 -> 2.32, 12 -> 2.31).  Medium and small pairs pay for overlap too -- measured from and to pinned buffers
+        // (tools/trace_e2e_c1.py), 1 / 2 / 3 / 4 chunks: 1436x992 (145, block 17) 0.82 / 0.67 / 0.59 / 0.61 ms;
+        // 1920x1080 (256) 0.79 / 0.79 / 0.67 / 0.72; 1280x720 0.42 / 0.36 / 0.32 / 0.32; 900x750 0.52 / 0.43 / 0.43 / 0.45;
+        // 640x480 0.20 / 0.17 / 0.17 / 0.19 -- so three chunks from ~0.8 M pixels, two below.
         double px = (double)pair->w2 * rows;
         c = (int)(px / 0.8e6);
+        if (c < 3) c = px >= 0.8e6 ? 3 : (px >= 0.15e6 ? 2 : 1);
         if (c > 12) c = 12;
     }
     int maxc = rows / (4 * p->block + 16);
