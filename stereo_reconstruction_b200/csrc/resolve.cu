@@ -212,7 +212,7 @@ __global__ void smooth_prepare_kernel(SearchGeom g, int from_direct, int have_c0
     if ((threadIdx.x & 31) == 0) {
         int wi = x >> 5;
         if (wi < words) {
-            size_t o = ((size_t)(y - g.row0) * words + wi) * 3;
+            size_t o = ((size_t)y * words + wi) * 3;     // planes are laid out by absolute output row (row chunks share them)
             bits[o] = w0; bits[o + 1] = w1; bits[o + 2] = w2;
         }
     }
@@ -254,7 +254,8 @@ __global__ void __launch_bounds__(SMOOTH_THREADS) smooth_raster_kernel(int rows,
             if (wi < words) {
                 const uint32_t* b = bits + ((size_t)y * words + wi) * 3;
                 uint32_t a0 = b[0], a1 = b[1], a2 = b[2];
-                uint32_t up = (y > 0 || first_row_has_up) ? (y > 0 ? zbits[(size_t)(y - 1) * words + wi] : 0u) : 0u;
+                // first_row_has_up: zbits points at a later row chunk, the row above its first row is the previous chunk's last
+                uint32_t up = (y > 0 || first_row_has_up) ? zbits[((ptrdiff_t)y - 1) * words + wi] : 0u;
                 F0 = (up & a1) | (~up & a0);
                 F1 = (up & a2) | (~up & a1);
             }
@@ -296,7 +297,7 @@ __global__ void __launch_bounds__(SMOOTH_THREADS) smooth_raster_kernel(int rows,
 #define RASTER_PF 8
 template <int KW>
 __global__ void __launch_bounds__(32) smooth_raster_warp_kernel(int rows, int words, const uint32_t* __restrict__ bits,
-                                                                uint32_t* __restrict__ zbits, int monotone) {
+                                                                uint32_t* __restrict__ zbits, int monotone, int first_row_has_up) {
     extern __shared__ uint32_t ring[];   // RASTER_PF x (32*KW*3) words
     const int lane = threadIdx.x;
     const int w0 = lane * KW;
@@ -316,7 +317,8 @@ __global__ void __launch_bounds__(32) smooth_raster_warp_kernel(int rows, int wo
     for (int y = 0; y < RASTER_PF - 1; y++) prefetch(y);
     uint32_t up[KW];
 #pragma unroll
-    for (int k = 0; k < KW; k++) up[k] = 0;   // y == 0 has no row above: the rule needs y >= 1
+    for (int k = 0; k < KW; k++)   // y == 0 has no row above (the rule needs y >= 1); a later row chunk starts from the row before it
+        up[k] = (first_row_has_up && w0 + k < words) ? zbits[(ptrdiff_t)(w0 + k) - words] : 0u;
 #pragma unroll 1
     for (int y = 0; y < rows; y++) {
         prefetch(y + RASTER_PF - 1);
@@ -361,7 +363,7 @@ __global__ void __launch_bounds__(32) smooth_raster_warp_kernel(int rows, int wo
 //    neither generate nor propagate).
 template <int KW>
 __global__ void __launch_bounds__(32) smooth_raster_mono_kernel(int rows, int words, const uint32_t* __restrict__ bits,
-                                                                uint32_t* __restrict__ zbits) {
+                                                                uint32_t* __restrict__ zbits, int first_row_has_up) {
     // The planes of the next U rows are loaded into registers (plain loads, nothing volatile: the compiler is free to
     // spread them over the stalls of the chain) while the current U rows are resolved.
     constexpr int U = 16 / KW;
@@ -382,7 +384,8 @@ __global__ void __launch_bounds__(32) smooth_raster_mono_kernel(int rows, int wo
     load_block(cur, 0);
     uint32_t up[KW];
 #pragma unroll
-    for (int k = 0; k < KW; k++) up[k] = 0;           // y == 0 has no row above: the rule needs y >= 1
+    for (int k = 0; k < KW; k++)   // y == 0 has no row above (the rule needs y >= 1); a later row chunk starts from the row before it
+        up[k] = (first_row_has_up && k < nvalid) ? zbits[(ptrdiff_t)(w0 + k) - words] : 0u;
     uint32_t* zo = zbits + w0;
 #pragma unroll 1
     for (int yb = 0; yb < rows; yb += U) {
@@ -423,11 +426,11 @@ __global__ void __launch_bounds__(32) smooth_raster_mono_kernel(int rows, int wo
 }
 
 template <int KW>
-static void launch_raster_warp(cudaStream_t st, int rows, int words, const uint32_t* bits, uint32_t* zb, int monotone) {
+static void launch_raster_warp(cudaStream_t st, int rows, int words, const uint32_t* bits, uint32_t* zb, int monotone, int has_up) {
     const size_t smem = RASTER_PF * 32 * KW * 3 * sizeof(uint32_t);
     static const char* old_env = getenv("SR_RASTER_GENERIC");   // test hook: 1 = the generic kernel for monotone factors too
-    if (monotone && !(old_env && atoi(old_env) != 0)) smooth_raster_mono_kernel<KW><<<1, 32, 0, st>>>(rows, words, bits, zb);
-    else smooth_raster_warp_kernel<KW><<<1, 32, smem, st>>>(rows, words, bits, zb, monotone);
+    if (monotone && !(old_env && atoi(old_env) != 0)) smooth_raster_mono_kernel<KW><<<1, 32, 0, st>>>(rows, words, bits, zb, has_up);
+    else smooth_raster_warp_kernel<KW><<<1, 32, smem, st>>>(rows, words, bits, zb, monotone, has_up);
 }
 
 __global__ void smooth_expand_kernel(SearchGeom g, int words, const uint32_t* __restrict__ zbits,
@@ -436,7 +439,7 @@ __global__ void smooth_expand_kernel(SearchGeom g, int words, const uint32_t* __
     int y = g.row0 + blockIdx.y;
     if (x >= g.w2 || y >= g.row1) return;
     size_t i = (size_t)y * g.w2 + x;
-    uint32_t z = (zbits[(size_t)(y - g.row0) * words + (x >> 5)] >> (x & 31)) & 1u;
+    uint32_t z = (zbits[(size_t)y * words + (x >> 5)] >> (x & 31)) & 1u;
     out[i] = z ? 0.0 : alt[i];
 }
 
@@ -479,7 +482,12 @@ int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, dou
         SR_CUDA(ctx, cudaMalloc((void**)&pair->bits, maxwords * 4 * sizeof(uint32_t)));
         SR_CUDA(ctx, cudaMalloc((void**)&pair->alt, pair->npx_cap * sizeof(double)));
     }
-    uint32_t* zb = pair->bits + (size_t)rows * words * 3;
+    // planes and z bits by absolute output row: the rows of one call (a row chunk of the one-shot pipeline) are a slice
+    const int oh_total = pair->oh > 0 ? pair->oh : g.h2;
+    uint32_t* zb_all = pair->bits + (size_t)oh_total * words * 3;
+    const uint32_t* bits_c = pair->bits + (size_t)g.row0 * words * 3;
+    uint32_t* zb = zb_all + (size_t)g.row0 * words;
+    const int has_up = g.row0 > 0 ? 1 : 0;             // the chunk above has been resolved (stream order / ctx->raster_wait)
     dim3 gridw(words, rows);
     smooth_prepare_kernel<<<dim3(cdiv(words * 32, 128), rows), 128, 0, ctx->stream>>>(
         g, from_direct, have_c0, smooth, pl, pair->c0, pair->cr, pair->dr, pair->nwin, pair->R.px, pair->R.pitch, pair->bits,
@@ -487,13 +495,14 @@ int sr_launch_resolve_right(sr_ctx* ctx, sr_pair* pair, const SearchGeom& g, dou
     SR_LAUNCHED(ctx);
     // s <= 1 makes a0 <= a1 <= a2 (more multiplications -> smaller cost): adder-style carries
     int monotone = (smooth >= 0.0 && smooth <= 1.0) ? 1 : 0;
-    if (words <= 32) launch_raster_warp<1>(ctx->stream, rows, words, pair->bits, zb, monotone);
-    else if (words <= 64) launch_raster_warp<2>(ctx->stream, rows, words, pair->bits, zb, monotone);
-    else if (words <= 128) launch_raster_warp<4>(ctx->stream, rows, words, pair->bits, zb, monotone);
-    else if (words <= 256) launch_raster_warp<8>(ctx->stream, rows, words, pair->bits, zb, monotone);
-    else smooth_raster_kernel<<<1, SMOOTH_THREADS, 0, ctx->stream>>>(rows, words, 0, pair->bits, zb, monotone);
+    if (ctx->raster_wait) SR_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->raster_wait, 0));   // previous chunk's raster (other stream)
+    if (words <= 32) launch_raster_warp<1>(ctx->stream, rows, words, bits_c, zb, monotone, has_up);
+    else if (words <= 64) launch_raster_warp<2>(ctx->stream, rows, words, bits_c, zb, monotone, has_up);
+    else if (words <= 128) launch_raster_warp<4>(ctx->stream, rows, words, bits_c, zb, monotone, has_up);
+    else if (words <= 256) launch_raster_warp<8>(ctx->stream, rows, words, bits_c, zb, monotone, has_up);
+    else smooth_raster_kernel<<<1, SMOOTH_THREADS, 0, ctx->stream>>>(rows, words, has_up, bits_c, zb, monotone);
     SR_LAUNCHED(ctx);
-    smooth_expand_kernel<<<grid, 128, 0, ctx->stream>>>(g, words, zb, pair->alt, pair->out);
+    smooth_expand_kernel<<<grid, 128, 0, ctx->stream>>>(g, words, zb_all, pair->alt, pair->out);
     SR_LAUNCHED(ctx);
     return SR_OK;
 }

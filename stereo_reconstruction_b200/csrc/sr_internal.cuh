@@ -57,6 +57,8 @@ struct sr_ctx {
     std::vector<TileWork> tile_work;   // schedules of the tile kernel, by geometry
     uint64_t tile_work_clock = 0;
     bool more_chunks_follow = false;   // set by the row-chunk pipeline around all launches but the last chunk's
+    bool chunked_smoothing = false;    // ... and while it runs the smoothing rule chunk by chunk (rows above are resolved)
+    cudaEvent_t raster_wait = nullptr; // the raster pass of the current chunk waits for this event (previous chunk, other stream)
     void* nccl_comm = nullptr;
     int rank = 0, nranks = 1;
 };

@@ -328,3 +328,32 @@ def test_peer_memory_band_gather_protocol(sr, orc, w):
             q.close()
         for c in ctxs:
             c.close()
+
+
+@pytest.mark.parametrize("chunks", ["2", "5"])
+@pytest.mark.parametrize("smooth", [0.9, 1.3])
+def test_one_shot_call_chunks_the_smoothing_rule(sr, ctx, orc, monkeypatch, chunks, smooth):
+    """sr_block_search with smoothFactor != 1 runs as a row-chunk pipeline too: search, bit planes and copies of
+    different chunks overlap, the raster passes resolve in row order (each starts from the last row of the chunk above).
+    Same map as the oracle's, from pinned and from pageable buffers, for a bonus (adder-style chain) and a penalty
+    (generic chain) factor, incl. a width of more than 32 words per row."""
+    monkeypatch.setenv("SR_PIPE_CHUNKS", chunks)
+    capi = sr.capi
+    w, h, D = 1100, 230, 40
+    L, R = orc.synth_pair(0xB200, 21, w, h, 0, D, True)
+    R[100:108, 300:420] = 0
+    want = orc.block_search_right_fast(L, R, 9, 0, D, smooth)
+    p = capi.search_params(block=9, min_disp=0, max_disp=D, smooth=smooth)
+    got = capi.block_search(ctx, L, R, p)                      # pageable buffers (staging threads)
+    np.testing.assert_array_equal(got, want)
+    Lp, a1 = capi.pinned_empty(L.shape, np.uint8); Lp[...] = L
+    Rp, a2 = capi.pinned_empty(R.shape, np.uint8); Rp[...] = R
+    o, a3 = capi.pinned_empty((h, w), np.float64); o[...] = -3.0
+    try:
+        capi.block_search(ctx, Lp, Rp, p, out=o)
+        np.testing.assert_array_equal(np.asarray(o), want)
+        capi.block_search(ctx, Lp, Rp, p, out=o)               # again: buffers of the first call are reused
+        np.testing.assert_array_equal(np.asarray(o), want)
+    finally:
+        for a in (a1, a2, a3):
+            capi.free_pinned(a)

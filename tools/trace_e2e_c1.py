@@ -10,7 +10,7 @@ L, R = synth.synth_pair(0xB200, 0, w, h, 0, D)
 Lp, a1 = capi.pinned_empty(L.shape, np.uint8); Lp[...] = L
 Rp, a2 = capi.pinned_empty(R.shape, np.uint8); Rp[...] = R
 o, a3 = capi.pinned_empty((h, w), np.float64)
-p = capi.search_params(block=B, min_disp=0, max_disp=D, smooth=1.0)
+p = capi.search_params(block=B, min_disp=0, max_disp=D, smooth=float(os.environ.get("SR_TRACE_SMOOTH", "1.0")))
 for _ in range(4):
     capi.block_search(ctx, Lp, Rp, p, out=o)
 ts = []
