@@ -168,10 +168,11 @@ struct TileArgs {
 //                  (K += in*64; K += out*(-64); FMA pipe) -- no ALU instruction but the min.
 // With the leaving-row subtract on the FMA pipe (pcost_sub) a SAD evaluation is 3.5 ALU + 2 FMA instructions
 // without ZMODE and 2.5 + 3 with it; one warp in four without ZMODE balances the pipes at 2.75 each.
-// MASKED: candidates outside [dlo, dlim(x)) are discarded (tiles that touch the break rule or the range ends).
+// MASKED: candidates outside [dlo, dlim(x)) are discarded (tiles that touch the break rule or the range ends); which
+// ones does not depend on the row, so the kernel forms the 64 validity bits of a thread once per CTA (vm).
 template <int H2, bool MASKED, bool ZMODE, bool LM = false>
 __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32_t (&keys)[XT], uint32_t k64,
-                                           uint32_t nk64, uint32_t dl0, int d0, int x0, const TileArgs& a) {
+                                           uint32_t nk64, uint32_t dl0, const uint32_t (&vm)[2]) {
     constexpr int HALO = H2 - 1;
 #pragma unroll
     for (int tp = 0; tp < DT; tp += 2) {
@@ -193,12 +194,9 @@ __device__ __forceinline__ void window_wta(const uint32_t (&col)[XT][DT], uint32
             uint32_t ka, kb;
             if (ZMODE) { ka = S0; kb = S1; }
             else { ka = S0 * k64 + dla; kb = S1 * k64 + dlb; }
-            if (MASKED) {
-                int x = x0 + j;
-                int lim = LM ? min(a.dhi, a.lim_a - x) : min(a.dhi, a.w1 - x - min(a.w2 - x - 1, a.half));
-                int lo = LM ? max(a.dlo, a.lo_a - x) : a.dlo;
-                if (d0 + tp < lo || d0 + tp >= lim) ka = 0xFFFFFFFFu;
-                if (d0 + tp + 1 < lo || d0 + tp + 1 >= lim) kb = 0xFFFFFFFFu;
+            if (MASKED) {                                   // validity bits of (column j, disparity tp / tp + 1): see the kernel
+                if (!((vm[tp >> 1] >> j) & 1u)) ka = 0xFFFFFFFFu;
+                if (!((vm[tp >> 1] >> (16 + j)) & 1u)) kb = 0xFFFFFFFFu;
             }
             keys[j] = min(min(keys[j], ka), kb);
             if (j + 1 < XT) {
@@ -325,6 +323,19 @@ __global__ void __launch_bounds__(NW * 32, NW <= 8 ? 2 : 1) search_tile_kernel(T
         }
     }
     const bool needmask = __any_sync(0xffffffffu, d0 < dlo_max || d0 + DT - 1 >= dlim_min);
+    // bit (t & 1) * 16 + j of vm[t >> 1]: candidate d0 + t is valid for output column cb + h + j (break rule :148, range
+    // ends; the Left variant's per-column lower bound) -- row-independent, formed once
+    uint32_t vm[2] = {0u, 0u};
+    if (needmask) {
+#pragma unroll
+        for (int j = 0; j < XT; j++) {
+            const int x = cb + h + j;
+            const int lim = lim_of(x), lo = LM ? max(a.dlo, a.lo_a - x) : a.dlo;
+#pragma unroll
+            for (int t = 0; t < DT; t++)
+                if (d0 + t >= lo && d0 + t < lim) vm[t >> 1] |= 1u << ((t & 1) * 16 + j);
+        }
+    }
     // The break rule cuts a triangle off the (x, d) plane at the right image edge: the largest limit of
     // the tile (its first output column) decides which warps / whole CTAs have no candidate at all.
     const int x_first = max(CB + h, 0);                         // first output column of the tile inside the image (the limit never grows with x)
@@ -440,9 +451,9 @@ __global__ void __launch_bounds__(NW * 32, NW <= 8 ? 2 : 1) search_tile_kernel(T
                 uint32_t keys[XT];
 #pragma unroll
                 for (int j = 0; j < XT; j++) keys[j] = 0xFFFFFFFFu;
-                if (needmask) window_wta<H2, true, false, LM>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
-                else if (COST == SR_COST_SAD && zmode) window_wta<H2, false, true>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
-                else if (COST == SR_COST_SAD) window_wta<H2, false, false>(col, keys, k64, nk64, dkey0, d0, cb + h, a);
+                if (needmask) window_wta<H2, true, false, LM>(col, keys, k64, nk64, dkey0, vm);
+                else if (COST == SR_COST_SAD && zmode) window_wta<H2, false, true>(col, keys, k64, nk64, dkey0, vm);
+                else if (COST == SR_COST_SAD) window_wta<H2, false, false>(col, keys, k64, nk64, dkey0, vm);
                 else window_wta4<H2, false>(col, keys, k64, nk64, dkey0);
 #pragma unroll
                 for (int k = 0; k < 4; k++)
