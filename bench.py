@@ -42,7 +42,7 @@ WORKLOADS = {
 OPS_PER_EVAL = {"ssd": 8, "sad": 7}
 # dram__bytes_read.sum + dram__bytes_write.sum of the search kernel from the committed ncu capture
 # (profiles/), per launch, keyed by workload; None = not captured for this workload
-NCU_TRAFFIC = {"4k512": 105639680 + 13473792}   # profiles/r02_tile_sad_4k512_ncu_full.csv (read + write bytes, N=1 launch)
+NCU_TRAFFIC = {"4k512": 105734144 + 12579584}   # profiles/r02_tile_sad_4k512_ncu_full.csv (read + write bytes, N=1 launch)
 
 
 def host_threads():
